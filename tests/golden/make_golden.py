@@ -122,7 +122,9 @@ def oracle_vectors():
     case = synth.decode_case(ids, n_audio=3, beam=5, step_kind="mixed", seed=11)
     res = od.decode_step_reference(case, ids)
     for k, v in res.items():
-        out[f"decode_{k}"] = np.asarray(v)
+        if k != "masked_logits":      # R x V floats: regenerated from the seed instead of stored
+            out[f"decode_{k}"] = np.asarray(v)
+    out["decode_case"] = np.array([3, 5, 11])   # n_audio, beam, seed of synth.decode_case(step_kind="mixed")
     np.savez_compressed(os.path.join(HERE, "oracle_vectors.npz"), **out)
     print("oracle_vectors.npz:", sorted(out.keys()))
 

@@ -1,0 +1,64 @@
+// Internal declarations shared by the translation units of libwrs_b200.so (not part of the ABI).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+
+#include "../../include/wrs.h"
+
+namespace wrs {
+
+// Banded form of an [80,201] filterbank: row m has nonzeros only in [lo, lo+n).
+struct MelBank {
+    static constexpr int kMaxWeights = 1024;
+    int lo[WRS_N_MELS];
+    int n[WRS_N_MELS];
+    int off[WRS_N_MELS];
+    float w[kMaxWeights];
+    int total;
+};
+
+// Device-side status word written by kernels (bounded-wait expiry, NaN); read by wrs_ctx_check.
+struct DevStatus {
+    int timeout;
+    int nan_rows;
+};
+
+}  // namespace wrs
+
+struct wrs_ctx {
+    int device = 0;
+    int sm_count = 0;
+    std::string err;
+    // log-mel
+    wrs::MelBank* d_bank = nullptr;        // device copy of the active filterbank
+    int* d_seg_state = nullptr;            // [2][cap] : max keys, arrival counters
+    int64_t seg_cap = 0;
+    wrs::DevStatus* d_status = nullptr;
+    int opt_logmel_fused = -1;             // -1 auto, 0 two-pass, 1 fused
+    int64_t stat_last_logmel_mode = -1;
+    int64_t stat_last_logmel_grid = 0;
+    int logmel_max_ctas_per_sm = 0;
+    // host staging for *_host entry points
+    float* d_stage_in = nullptr; size_t stage_in_bytes = 0;
+    float* d_stage_out = nullptr; size_t stage_out_bytes = 0;
+    cudaStream_t own_stream = nullptr;
+};
+
+namespace wrs {
+
+void set_thread_error(const std::string& s);
+int fail(wrs_ctx* ctx, int code, const std::string& msg);
+int cuda_fail(wrs_ctx* ctx, cudaError_t e, const char* what);
+void mel_filter_slaney(float* out_80x201);
+bool build_mel_bank(const float* dense_80x201, MelBank* bank);
+
+#define WRS_CUDA(ctx, expr)                                              \
+    do {                                                                 \
+        cudaError_t _e = (expr);                                         \
+        if (_e != cudaSuccess) return ::wrs::cuda_fail(ctx, _e, #expr);  \
+    } while (0)
+
+}  // namespace wrs
