@@ -1,0 +1,123 @@
+"""Parity of the CUDA decode step (through the C ABI) with the oracle -- reference src/decode/filter/*.rs,
+src/decode/extractor/*.rs, src/decode/sequencer/*.rs, src/decode/mod.rs:257-270.
+
+Bars (north_star): masks and selected token ids bit-exact with lowest-index ties; log-probs 1e-5 relative."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from conftest import GOLDEN
+from oracle import decode as od
+from whisper_rs_b200 import _lib, synth
+from whisper_rs_b200 import constants as C
+from whisper_rs_b200 import decode as wd
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-5
+VEC = np.load(os.path.join(GOLDEN, "oracle_vectors.npz"))
+
+
+def fused_step(ids, case, opt=None, greedy=False, row_stride=None):
+    k = case["beam"]
+    mode = wd.TokenExtractMode.Greedy(1) if greedy else wd.TokenExtractMode.BeamSearch(k, 1.0)
+    opt = opt or wd.DecodeOptions(token_extract_mode=mode)
+    prompt = wd.DecodePrompt(None, ids)
+    prompt.sample_begin = case["sample_begin"]
+    step = wd.FusedDecodeStep(opt, ids, [prompt], max_rows=case["logits"].shape[0])
+    step.reset()
+    logits = torch.from_numpy(case["logits"]).cuda()
+    if row_stride:
+        buf = torch.full((logits.shape[0], row_stride), 1e30, dtype=torch.float32, device="cuda")   # poison beyond V
+        buf[:, :logits.shape[1]] = logits
+        logits = buf[:, :ids.n_vocab]
+    out = step.step(torch.from_numpy(case["tokens"]).cuda(), logits, torch.from_numpy(case["sum_logprobs"]).cuda(),
+                    debug=True)
+    torch.cuda.synchronize()
+    step.decoder.ctx.check()
+    return {k_: (v.cpu().numpy() if isinstance(v, torch.Tensor) else v) for k_, v in out.items()}, step
+
+
+def assert_beam_parity(got, want, k):
+    assert np.array_equal(got["row_flags"], want["row_flags"])                      # which mask rules fired
+    assert np.array_equal(got["cand_token"], want["cand_token"])                    # ids, ties lowest first
+    assert np.allclose(got["cand_logprob"], want["cand_logprob"], rtol=RTOL, atol=0)
+    assert np.array_equal(got["next_tokens"], want["next_tokens"])
+    assert np.array_equal(got["source_idx"], want["source_idx"])
+    assert np.allclose(got["sum_logprobs"], want["sum_logprobs"], rtol=RTOL, atol=0)
+    assert np.array_equal(got["fin_count"], want["fin_count"])
+    for a in range(len(want["fin_count"])):
+        n = want["fin_count"][a]
+        assert np.allclose(got["fin_score"][a, :n], want["fin_score"][a, :n], rtol=RTOL, atol=0)
+    assert int(got["completed"][0]) == int(want["completed"])
+
+
+def test_golden_decode_vectors():
+    n_audio, beam, seed = [int(v) for v in VEC["decode_case"]]
+    case = synth.decode_case(C.MULTILINGUAL, n_audio, beam, "mixed", seed)
+    got, _ = fused_step(C.MULTILINGUAL, case)
+    for key in ("cand_token", "next_tokens", "source_idx", "row_flags", "fin_count"):
+        assert np.array_equal(got[key], VEC[f"decode_{key}"]), key
+    assert np.allclose(got["cand_logprob"], VEC["decode_cand_logprob"], rtol=RTOL, atol=0)
+    assert np.allclose(got["sum_logprobs"], VEC["decode_sum_logprobs"], rtol=RTOL, atol=0)
+
+
+@pytest.mark.parametrize("ids", [C.MULTILINGUAL, C.GPT2_EN], ids=["v51865", "v51864"])
+@pytest.mark.parametrize("step_kind,prompt_len", [("first", 0), ("first", 7), ("second", 0), ("mixed", 0), ("mixed", 12)])
+def test_beam_step_matches_oracle(ids, step_kind, prompt_len):
+    case = synth.decode_case(ids, 4, 5, step_kind, seed=31, prompt_len=prompt_len)
+    want = od.decode_step_reference(case, ids)
+    got, _ = fused_step(ids, case)
+    assert_beam_parity(got, want, 5)
+    if step_kind == "first":
+        assert np.all(want["n_finite"] == 51)          # only timestamps 0..50 survive
+
+
+@pytest.mark.parametrize("step_kind", ["first", "mixed"])
+def test_planted_ties_lowest_index_wins(step_kind):
+    ids = C.MULTILINGUAL
+    case = synth.decode_case(ids, 3, 5, step_kind, seed=5, planted_ties=True)
+    want = od.decode_step_reference(case, ids)
+    got, _ = fused_step(ids, case)
+    assert_beam_parity(got, want, 5)
+    tied = got["cand_logprob"][:, 0] == got["cand_logprob"][:, 1]
+    assert tied.any()
+    assert np.all(got["cand_token"][tied, 0] < got["cand_token"][tied, 1])
+
+
+@pytest.mark.parametrize("beam", [1, 2, 5, 8, 12])
+def test_beam_sizes(beam):
+    ids = C.MULTILINGUAL
+    case = synth.decode_case(ids, 2, beam, "mixed", seed=77 + beam)
+    want = od.decode_step_reference(case, ids, od.DecodeOptions(beam_size=beam))
+    got, _ = fused_step(ids, case)
+    assert_beam_parity(got, want, beam)
+
+
+def test_row_stride_view():
+    # logits is logits[:, -1] of [R, T, V] in the reference (decode/mod.rs:258): a strided view
+    ids = C.MULTILINGUAL
+    case = synth.decode_case(ids, 2, 5, "mixed", seed=3)
+    want = od.decode_step_reference(case, ids)
+    got, _ = fused_step(ids, case, row_stride=ids.n_vocab + 3)      # rows are only 4-byte aligned
+    assert_beam_parity(got, want, 5)
+
+
+@pytest.mark.parametrize("timestamps,suppress_blank,non_speech,mit", [
+    (False, True, True, 1.0), (True, False, False, 1.0), (True, True, True, None), (False, False, False, None)])
+def test_option_combinations(timestamps, suppress_blank, non_speech, mit):
+    ids = C.MULTILINGUAL
+    for kind in ("first", "mixed"):
+        case = synth.decode_case(ids, 2, 5, kind, seed=13)
+        oopt = od.DecodeOptions(beam_size=5, timestamps=timestamps, suppress_blank=suppress_blank,
+                                suppress_non_speech=non_speech, max_initial_timestamp=mit,
+                                suppress_tokens=None if non_speech else ([11, 13, 50257] if suppress_blank else None))
+        wopt = wd.DecodeOptions(token_extract_mode=wd.TokenExtractMode.BeamSearch(5, 1.0), timestamps=timestamps,
+                                suppress_blank=suppress_blank, suppress_non_speech=non_speech,
+                                max_initial_timestamp=mit, suppress_tokens=oopt.suppress_tokens)
+        want = od.decode_step_reference(case, ids, oopt)
+        got, _ = fused_step(ids, case, wopt)
+        if not timestamps:
+            want["row_flags"] = np.zeros_like(got["row_flags"])
+        assert_beam_parity(got, want, 5)
