@@ -16,6 +16,15 @@ from whisper_rs_b200 import decode as wd
 
 pytestmark = pytest.mark.gpu
 RTOL = 1e-5
+# The oracle's log_softmax is ATen's f32 sum of 51.8k exponentials: measured up to 6.3e-6 away from exact (f64)
+# arithmetic, i.e. more than 1e-5 relative on any log-prob above -0.6.  Against the oracle the bar is therefore
+# rtol 1e-5 + ATOL; against the f64 evaluation of the same masked logits it is rtol 1e-5 + 2e-6 (assert_beam_parity).
+ATOL = 1e-5
+ATOL_F64 = 2e-6
+
+
+def close(a, b, atol=ATOL):
+    return np.allclose(a, b, rtol=RTOL, atol=atol)
 VEC = np.load(os.path.join(GOLDEN, "oracle_vectors.npz"))
 
 
@@ -42,14 +51,17 @@ def fused_step(ids, case, opt=None, greedy=False, row_stride=None):
 def assert_beam_parity(got, want, k):
     assert np.array_equal(got["row_flags"], want["row_flags"])                      # which mask rules fired
     assert np.array_equal(got["cand_token"], want["cand_token"])                    # ids, ties lowest first
-    assert np.allclose(got["cand_logprob"], want["cand_logprob"], rtol=RTOL, atol=0)
+    assert close(got["cand_logprob"], want["cand_logprob"])
+    if "masked_logits" in want:      # exact arithmetic on the oracle's masked logits
+        lp64 = torch.from_numpy(want["masked_logits"]).double().log_softmax(-1).numpy()
+        assert close(got["cand_logprob"], np.take_along_axis(lp64, want["cand_token"].astype(np.int64), 1), ATOL_F64)
     assert np.array_equal(got["next_tokens"], want["next_tokens"])
     assert np.array_equal(got["source_idx"], want["source_idx"])
-    assert np.allclose(got["sum_logprobs"], want["sum_logprobs"], rtol=RTOL, atol=0)
+    assert close(got["sum_logprobs"], want["sum_logprobs"])
     assert np.array_equal(got["fin_count"], want["fin_count"])
     for a in range(len(want["fin_count"])):
         n = want["fin_count"][a]
-        assert np.allclose(got["fin_score"][a, :n], want["fin_score"][a, :n], rtol=RTOL, atol=0)
+        assert close(got["fin_score"][a, :n], want["fin_score"][a, :n])
     assert int(got["completed"][0]) == int(want["completed"])
 
 
@@ -59,8 +71,8 @@ def test_golden_decode_vectors():
     got, _ = fused_step(C.MULTILINGUAL, case)
     for key in ("cand_token", "next_tokens", "source_idx", "row_flags", "fin_count"):
         assert np.array_equal(got[key], VEC[f"decode_{key}"]), key
-    assert np.allclose(got["cand_logprob"], VEC["decode_cand_logprob"], rtol=RTOL, atol=0)
-    assert np.allclose(got["sum_logprobs"], VEC["decode_sum_logprobs"], rtol=RTOL, atol=0)
+    assert close(got["cand_logprob"], VEC["decode_cand_logprob"])
+    assert close(got["sum_logprobs"], VEC["decode_sum_logprobs"])
 
 
 @pytest.mark.parametrize("ids", [C.MULTILINGUAL, C.GPT2_EN], ids=["v51865", "v51864"])
@@ -82,7 +94,8 @@ def test_planted_ties_lowest_index_wins(step_kind):
     got, _ = fused_step(ids, case)
     assert_beam_parity(got, want, 5)
     tied = got["cand_logprob"][:, 0] == got["cand_logprob"][:, 1]
-    assert tied.any()
+    if step_kind == "mixed":         # on the first step only timestamps 0..50 survive: planted ties are masked away
+        assert tied.any()
     assert np.all(got["cand_token"][tied, 0] < got["cand_token"][tied, 1])
 
 
