@@ -1,15 +1,17 @@
-// K2: the fused per-step logit processing (filters + log-softmax + top-k + beam merge) for sm_100a, ONE launch.
+// K2: the fused per-step logit processing (filters + log-softmax + top-k + beam merge) for sm_100a, ONE launch,
+// no block-level barrier.
 //
-//   decode_step_kernel<MODE>  grid (chunks, rows), 512 threads.  Every CTA scans one chunk of one row
-//       (decode_scan.cuh: one read of the logits, masks as predicates, {max, sum-exp, top-K} partial to global),
-//       then arrives on its group's counter.  The LAST CTA to arrive for a group runs the group's tail:
-//   MODE_BEAM    group = audio (beam rows): per row merge of the chunk partials, the timestamp-vs-text rule
-//                (src/decode/filter/timestamp_tokens.rs:83-96) on the partition sums, log-softmax of the K
-//                candidates; then BeamSearchTokenExtractor::update's host loop
-//                (src/decode/extractor/beam_search.rs:49-146) on device
-//   MODE_GREEDY  group = row: the same row merge followed by GreedyTokenExtractor::update (greedy.rs:24-50)
-//   MODE_FILTER  group = row: the row merge, then the in-place fills of TimestampTokens::apply
-//                (LogitFilter::apply equivalents, src/decode/filter/*.rs)
+//   decode_step_kernel<MODE>  persistent grid (<= one 512-thread CTA per SM).  The R x units_per_row units of the
+//       batch are dealt to the warps of the grid in contiguous runs (decode_scan.cuh: one read of the logits, masks
+//       as predicates, register double-buffering so the next unit is in flight while this one is reduced).  At the
+//       end of every (row, partition) run the warp leaves a Partial in global memory and arrives on the row's
+//       counter.  The LAST warp to arrive for a row merges the row (timestamp-vs-text rule on the partition sums,
+//       src/decode/filter/timestamp_tokens.rs:83-96, log-softmax of the K candidates), then
+//   MODE_BEAM    arrives on the audio's counter; the last row of an audio runs BeamSearchTokenExtractor::update's
+//                host loop (src/decode/extractor/beam_search.rs:49-146) on device, one warp
+//   MODE_GREEDY  runs GreedyTokenExtractor::update for the row (greedy.rs:24-50)
+//   MODE_FILTER  does the in-place fills of TimestampTokens::apply (LogitFilter::apply equivalents,
+//                src/decode/filter/*.rs)
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -17,25 +19,29 @@
 #include "decode_scan.cuh"
 #include "wrs_internal.cuh"
 
+namespace wrs { struct RowResult; }
+
 struct wrs_decoder {
     wrs_ctx* ctx = nullptr;
     wrs_decode_cfg cfg{};
     int max_rows = 0, max_audio = 0, max_cand = 0;
-    int ts_split = 0, n_text = 0, text_len = 0, n_ts = 0, ts_len = 0, chunks = 0;   // chunk geometry of a row
+    int ts_split = 0, n_text_units = 0, n_ts_units = 0, upr = 0;   // unit geometry of a row
     int bm_words = 0;
     uint32_t* d_bm_base = nullptr;    // suppress list (+ no_timestamps when timestamps are on)
     uint32_t* d_bm_first = nullptr;   // base + blank ids (first step, suppress_blank)
     uint32_t* d_bm_ts = nullptr;      // only no_timestamps (in-place timestamp filter)
     int32_t* d_suppress = nullptr; int n_suppress = 0;   // raw list for the in-place sparse fill
     int32_t* d_blank = nullptr;       // the two blank ids, for the in-place sparse fill
-    wrs::Partial* d_partials = nullptr;   // [max_rows][chunks]
-    int32_t* d_arrive = nullptr;      // [max_rows] self-resetting arrival counters
+    wrs::Partial* d_partials = nullptr;   // [max_rows][upr]
+    wrs::RowResult* d_rowres = nullptr;   // [max_rows]
+    int32_t* d_arrive = nullptr;      // [max_rows + max_audio] self-resetting arrival counters (rows, then audios)
     // finished-sequence store (BeamSearchTokenExtractor::finished_sequences, beam_search.rs:13)
     int64_t* d_fin_tokens = nullptr;  // [max_audio][max_cand][max_len]
     int32_t* d_fin_len = nullptr;     // [max_audio][max_cand]
     double* d_fin_score = nullptr;    // [max_audio][max_cand]
     int32_t* d_fin_n = nullptr;       // [max_audio]
     int32_t* d_sync = nullptr;        // [2] arrive counter, full counter
+    bool smem_attr_set = false;
 };
 
 namespace wrs {
@@ -43,16 +49,25 @@ namespace wrs {
 enum { MODE_BEAM = 0, MODE_GREEDY = 1, MODE_FILTER = 2 };
 constexpr int kMaxBeam = 15;
 constexpr int kMaxCandAudio = kMaxBeam * kMaxK;          // 240
-constexpr int kRowEntries = kMaxChunks * kMaxK;          // 144 staged candidates per row
+constexpr int kScratchBytes = 4608;                      // per-warp shared scratch (WarpBuf, or the beam tail's tables)
+
+// what the row merge leaves for the audio-level tail
+struct __align__(16) RowResult {
+    float lp[kMaxK];
+    int tok[kMaxK];
+    unsigned flags;
+    unsigned same;         // bit j2: beam j2 (> this row's beam index) holds an identical token prefix
+    int pad[2];
+};
 
 struct StepParams {
     float* logits; int64_t row_stride;                   // read-only except MODE_FILTER
     const int64_t* tokens; int64_t tok_stride;
     int cur_len, sample_begin, n_rows, K, beam, n_groups;
     RuleCfg rc;
-    int ts_split, n_text, text_len, n_ts, ts_len, chunks;
-    const uint32_t* bm; const uint32_t* bm_first;
-    Partial* partials; int32_t* arrive;
+    int ts_split, n_text_units, n_ts_units, upr, bm_words;
+    const uint32_t* bm;
+    Partial* partials; RowResult* rowres; int32_t* row_arrive; int32_t* audio_arrive;
     int eot, max_cand, max_len, no_timestamps;
     const float* sum_in; float* sum_out;
     int64_t* next_tokens; int64_t next_stride; int32_t* source_idx; int32_t* completed;
@@ -61,192 +76,328 @@ struct StepParams {
     DevStatus* status;
 };
 
-struct TailSmem {
-    float cv[kScanWarps][kRowEntries];
-    int ci[kScanWarps][kRowEntries];
-    float sel_v[kScanWarps][kMaxK];
-    int sel_i[kScanWarps][kMaxK];
-    float lp[kMaxBeam][kMaxK];
-    int tok[kMaxBeam][kMaxK];
-    unsigned char same[kMaxBeam][kMaxBeam];
-    double c_score[kMaxCandAudio];
-    short c_row[kMaxCandAudio], c_shadow[kMaxCandAudio], order[kMaxCandAudio];
-    int c_tok[kMaxCandAudio];
-    int sel_src[kMaxBeam], sel_tok[kMaxBeam], fin_src[kMaxBeam];
-    double sel_score[kMaxBeam], fin_sc[kMaxBeam];
-    int n_fin, store_base, n_store, nan_seen;
-    unsigned flags;
+// geometry of one unit as a warp sees it (all warp-uniform)
+struct Geom {
+    int row, part;      // part 0 = text ids, 1 = timestamp ids
+    int lo, hi;         // surviving ids of the unit [lo, hi) after the row's rules (hi <= lo: nothing to read)
+    int a0;             // id of the first loaded element (lo rounded down to a 16-byte boundary of the row's memory)
 };
 
-// ---- row finish (one full warp per row): merge chunk partials, the timestamp-vs-text rule, K log-probs.
-// Lane i < K returns candidate i; `flags` is the same on every lane.
-struct RowResult { float lp; int tok; unsigned flags; };
+// the running statistics of the (row, partition) run a warp is reducing; its candidates sit in WarpBuf[0, n)
+struct Run { float m, s; int n; };
 
-__device__ __forceinline__ RowResult finish_row(const StepParams& p, const Partial* __restrict__ parts, unsigned rule_flags,
-                                                TailSmem& ts) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+// Fold one unit (already in registers, masked ranges loaded as -inf) into the run.
+__device__ __forceinline__ void reduce_unit(float (&x)[kNV][4], const Geom& g, uint32_t bmw, int wbase, int K, WarpBuf& wb,
+                                            Run& run) {
+    const int lane = threadIdx.x & 31;
+    // ---- 1. suppress bitmap -> -inf (bit set = masked); most units hold no suppressed id at all
+    if (__any_sync(0xffffffffu, bmw != 0u)) {
+#pragma unroll
+        for (int j = 0; j < kNV; ++j) {
+            const int e = g.a0 + 4 * (lane + 32 * j);
+            const int rel = max((e >> 5) - wbase, 0);
+            const uint32_t w0 = __shfl_sync(0xffffffffu, bmw, rel), w1 = __shfl_sync(0xffffffffu, bmw, rel + 1);
+            // e < 0 (row start not 16-byte aligned): ids e..-1 do not exist, ids 0..e+3 take the low bits of word 0
+            const uint32_t bits = (e >= 0 ? __funnelshift_r(w0, w1, e & 31) : (w0 << (-e))) & 0xFu;
+            if (bits) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    if (bits & (1u << i)) x[j][i] = -CUDART_INF_F;
+            }
+        }
+    }
+    // ---- 2. lane max, warp max, sum of exp(x - warp max)
+    float tmax = -CUDART_INF_F;
+#pragma unroll
+    for (int j = 0; j < kNV; ++j)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) tmax = fmaxf(tmax, x[j][i]);
+    const float wmax = warp_max(tmax);
+    const float ref = (wmax == -CUDART_INF_F) ? 0.0f : wmax;
+    const float nref = -ref * kLog2e;
+    float s0 = 0.0f, s1 = 0.0f;
+#pragma unroll
+    for (int j = 0; j < kNV; ++j) {
+        s0 += ex2(fmaf(x[j][0], kLog2e, nref)) + ex2(fmaf(x[j][1], kLog2e, nref));   // NaN inputs keep the sum NaN
+        s1 += ex2(fmaf(x[j][2], kLog2e, nref)) + ex2(fmaf(x[j][3], kLog2e, nref));
+    }
+    float ssum = s0 + s1;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) ssum += __shfl_xor_sync(0xffffffffu, ssum, o);
+    if (ssum != ssum) run.s = ssum;                      // keep NaN visible
+    else if (wmax > run.m) { run.s = run.s * exp_diff(run.m, wmax) + ssum; run.m = wmax; }
+    else if (wmax > -CUDART_INF_F) run.s += ssum * ex2((wmax - run.m) * kLog2e);
+    if (wmax == -CUDART_INF_F) return;                   // nothing finite in this unit
+    // ---- 3. threshold: at least K elements of {unit} reach tau_u; nothing below the run's K-th best can matter
+    const float tau_u = kth_threshold(tmax, K);
+    const int n0 = run.n;
+    const float tau_r = (n0 >= K) ? wb.v[K - 1] : -CUDART_INF_F;
+    const float tau = fmaxf(tau_u, tau_r);
+    if (lane == 0) wb.n = n0;
+    __syncwarp();
+    // ---- 4. gather everything at or above the threshold
+    if (tmax >= tau) {
+#pragma unroll
+        for (int j = 0; j < kNV; ++j)
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                if (x[j][i] >= tau && x[j][i] > -CUDART_INF_F) {
+                    const int pos = atomicAdd(&wb.n, 1);
+                    if (pos < kCandCap) { wb.v[pos] = x[j][i]; wb.id[pos] = g.a0 + 4 * (lane + 32 * j) + i; }
+                }
+    }
+    __syncwarp();
+    const int n = wb.n;
+    if (n <= kCandCap) { run.n = warp_compact(wb, n, K); return; }
+    // ---- 5. massive ties: K rounds of exact warp-wide selection over {old list} U {unit}, each strictly after the last pick
+    const float ov = lane < n0 ? wb.v[lane] : -CUDART_INF_F; const int oi = lane < n0 ? wb.id[lane] : INT32_MAX;
+    __syncwarp();
+    float pv = CUDART_INF_F; int pi = -1, cnt = 0;
+    for (int r = 0; r < K; ++r) {
+        float bv = -CUDART_INF_F; int bi = INT32_MAX;
+        {
+            const bool after = ov < pv || (ov == pv && oi > pi);
+            if (after && ov > -CUDART_INF_F) { bv = ov; bi = oi; }
+        }
+#pragma unroll
+        for (int j = 0; j < kNV; ++j)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const float v = x[j][i]; const int id = g.a0 + 4 * (lane + 32 * j) + i;
+                const bool after = v < pv || (v == pv && id > pi);
+                if (after && v > -CUDART_INF_F && better(v, id, bv, bi)) { bv = v; bi = id; }
+            }
+        warp_pick(bv, bi);
+        if (bi == INT32_MAX) break;
+        if (lane == 0) { wb.v[r] = bv; wb.id[r] = bi; }
+        pv = bv; pi = bi; ++cnt;
+    }
+    __syncwarp();
+    run.n = cnt;
+}
+
+// ---- which warp of the grid owns unit u, when N units are dealt to Wt warps in contiguous runs [g N / Wt, (g+1) N / Wt)
+__device__ __forceinline__ int unit_owner(int64_t u, int64_t Wt, int64_t N) { return (int)(((u + 1) * Wt - 1) / N); }
+
+struct RowPartials { int first_owner[2], count[2], base[2]; };
+
+__device__ __forceinline__ RowPartials row_partials(const StepParams& p, int row, int64_t Wt, int64_t N) {
+    RowPartials rp;
+    const int64_t u0 = (int64_t)row * p.upr;
+    rp.base[0] = 0; rp.base[1] = p.n_text_units;
+    const int64_t ua[2] = {u0, u0 + p.n_text_units}, ub[2] = {u0 + p.n_text_units, u0 + p.upr};
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+        if (ub[q] > ua[q]) { rp.first_owner[q] = unit_owner(ua[q], Wt, N); rp.count[q] = unit_owner(ub[q] - 1, Wt, N) - rp.first_owner[q] + 1; }
+        else { rp.first_owner[q] = 0; rp.count[q] = 0; }
+    }
+    return rp;
+}
+
+// ---- row merge (one full warp): partials of the row -> K log-probs.  Lane i < K ends with candidate i.
+struct RowOut { float lp; int tok; unsigned flags; };
+
+__device__ __forceinline__ RowOut merge_row(const StepParams& p, int row, unsigned rule_flags, const RowPartials& rpz, WarpBuf& wb) {
+    const int lane = threadIdx.x & 31;
     const int K = p.K;
-    const bool mine = lane < p.chunks, text = lane < p.n_text;
-    const float m_c = mine ? __ldcg(&parts[lane].m) : -CUDART_INF_F;
-    const float s_c = mine ? __ldcg(&parts[lane].s) : 0.0f;
-    float Tm = (mine && text) ? m_c : -CUDART_INF_F, Sm = (mine && !text) ? m_c : -CUDART_INF_F;
+    const Partial* __restrict__ parts = p.partials + (int64_t)row * p.upr;
+    // partition maxima and sums (text = 0, timestamps = 1)
+    float M[2], S[2];
+    bool nan_seen = false;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        Tm = fmaxf(Tm, __shfl_xor_sync(0xffffffffu, Tm, o));
-        Sm = fmaxf(Sm, __shfl_xor_sync(0xffffffffu, Sm, o));
-    }
-    float Ts = (mine && text) ? s_c * exp_diff(m_c, Tm) : 0.0f, Ss = (mine && !text) ? s_c * exp_diff(m_c, Sm) : 0.0f;
-    if (s_c != s_c) { Ts = text ? s_c : Ts; Ss = text ? Ss : s_c; }
+    for (int q = 0; q < 2; ++q) {
+        float m = -CUDART_INF_F;
+        for (int i = lane; i < rpz.count[q]; i += 32) m = fmaxf(m, __ldcg(&parts[rpz.base[q] + i].m));
+        m = warp_max(m);
+        float s = 0.0f;
+        for (int i = lane; i < rpz.count[q]; i += 32) {
+            const float pm = __ldcg(&parts[rpz.base[q] + i].m), ps = __ldcg(&parts[rpz.base[q] + i].s);
+            if (ps != ps) nan_seen = true;
+            else s += ps * exp_diff(pm, m);
+        }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        Ts += __shfl_xor_sync(0xffffffffu, Ts, o);
-        Ss += __shfl_xor_sync(0xffffffffu, Ss, o);
+        for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        M[q] = m; S[q] = s;
     }
-    RowResult r;
+    nan_seen = __any_sync(0xffffffffu, nan_seen);
+    RowOut r;
     r.flags = rule_flags;
-    if (Ts != Ts || Ss != Ss) r.flags |= 128u;
+    if (nan_seen) r.flags |= 128u;
+    float Tm = M[0], Ts = S[0];
+    const float Sm = M[1], Ss = S[1];
     // logsumexp(timestamps) > max(text): both sides carry the same -logsumexp(all), which cancels
     const float lse_s = (Ss > 0.0f) ? Sm + logf(Ss) : -CUDART_INF_F;
     const bool ts_over_text = p.rc.timestamps && (lse_s > Tm);
     if (ts_over_text) { r.flags |= 8u; Tm = -CUDART_INF_F; Ts = 0.0f; }
     // final log-softmax over what survived: (x - M) - log(sum exp(x - M)), the order ATen uses
-    const float M = fmaxf(Tm, Sm);
-    const float tot = Ts * exp_diff(Tm, M) + Ss * exp_diff(Sm, M);
-    const float logtot = logf(tot);
-    if (M == -CUDART_INF_F) r.flags |= 128u;   // everything masked: the reference yields NaN log-probs
-    // stage the surviving chunks' candidates, then rank-count select the best K
-    const int nent = p.chunks * kMaxK;
-    float* cv = ts.cv[warp]; int* ci = ts.ci[warp];
-    for (int e = lane; e < nent; e += 32) {
-        const int c = e / kMaxK, i = e - c * kMaxK;
-        const bool dead = (ts_over_text && c < p.n_text) || i >= K;
-        cv[e] = dead ? -CUDART_INF_F : __ldcg(&parts[c].v[i]);
-        ci[e] = dead ? INT32_MAX : __ldcg(&parts[c].id[i]);
-    }
-    if (lane < kMaxK) { ts.sel_v[warp][lane] = -CUDART_INF_F; ts.sel_i[warp][lane] = INT32_MAX; }
+    const float Mx = fmaxf(Tm, Sm);
+    const float tot = Ts * exp_diff(Tm, Mx) + Ss * exp_diff(Sm, Mx);
+    const float logtot = nan_seen ? CUDART_NAN_F : logf(tot);
+    if (Mx == -CUDART_INF_F) r.flags |= 128u;   // everything masked: the reference yields NaN log-probs
+    // candidates: threshold on the partials' maxima (v[0]), gather, rank-sort
+    const int q_lo = ts_over_text ? 1 : 0;
+    float lmax = -CUDART_INF_F;
+    for (int q = q_lo; q < 2; ++q)
+        for (int i = lane; i < rpz.count[q]; i += 32) lmax = fmaxf(lmax, __ldcg(&parts[rpz.base[q] + i].v[0]));
+    const float tau = kth_threshold(lmax, K);
+    if (lane == 0) wb.n = 0;
     __syncwarp();
-    for (int e = lane; e < nent; e += 32) {
-        const float v = cv[e]; const int id = ci[e];
-        if (id == INT32_MAX) continue;
-        int rank = 0;
-        for (int d = 0; d < nent; ++d) rank += better(cv[d], ci[d], v, id) ? 1 : 0;
-        if (rank < K) { ts.sel_v[warp][rank] = v; ts.sel_i[warp][rank] = id; }
-    }
+    for (int q = q_lo; q < 2; ++q)
+        for (int i = lane; i < rpz.count[q]; i += 32) {
+            const Partial* pp = parts + rpz.base[q] + i;
+            const int pn = min(__ldcg(&pp->n), K);
+            for (int e = 0; e < pn; ++e) {
+                const float v = __ldcg(&pp->v[e]);
+                if (!(v >= tau) || v == -CUDART_INF_F) break;      // sorted: nothing further can qualify
+                const int pos = atomicAdd(&wb.n, 1);
+                if (pos < kCandCap) { wb.v[pos] = v; wb.id[pos] = __ldcg(&pp->id[e]); }
+            }
+        }
     __syncwarp();
-    const float x = lane < K ? ts.sel_v[warp][lane] : -CUDART_INF_F;
-    r.tok = lane < K ? ts.sel_i[warp][lane] : INT32_MAX;
-    r.lp = (x - M) - logtot;
+    int n = wb.n;
+    if (n <= kCandCap) n = warp_compact(wb, n, K);
+    else {
+        // massive ties across many partials: K rounds of exact selection straight from the partials
+        float pv = CUDART_INF_F; int pi = -1; n = 0;
+        for (int rr = 0; rr < K; ++rr) {
+            float bv = -CUDART_INF_F; int bi = INT32_MAX;
+            for (int q = q_lo; q < 2; ++q)
+                for (int i = lane; i < rpz.count[q]; i += 32) {
+                    const Partial* pp = parts + rpz.base[q] + i;
+                    const int pn = min(__ldcg(&pp->n), K);
+                    for (int e = 0; e < pn; ++e) {
+                        const float v = __ldcg(&pp->v[e]); const int id = __ldcg(&pp->id[e]);
+                        const bool after = v < pv || (v == pv && id > pi);
+                        if (after && v > -CUDART_INF_F && better(v, id, bv, bi)) { bv = v; bi = id; }
+                    }
+                }
+            warp_pick(bv, bi);
+            if (bi == INT32_MAX) break;
+            if (lane == 0) { wb.v[rr] = bv; wb.id[rr] = bi; }
+            pv = bv; pi = bi; ++n;
+        }
+        __syncwarp();
+    }
+    const float x = lane < n ? wb.v[lane] : -CUDART_INF_F;
+    r.tok = lane < n ? wb.id[lane] : INT32_MAX;
+    r.lp = (x - Mx) - logtot;
     __syncwarp();
     return r;
 }
 
-// ---- MODE_BEAM tail: BeamSearchTokenExtractor::update for one audio (beam_search.rs:49-146), whole CTA ----
-__device__ __forceinline__ void beam_tail(const StepParams& p, int audio, TailSmem& ts) {
-    const int k = p.beam, K = p.K;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+// per-warp tables of the beam tail (alias the WarpBuf: the warp's run has been flushed when a tail starts)
+struct TailScratch {
+    double score[kMaxCandAudio];
+    int tok[kMaxCandAudio];
+    unsigned short order[kMaxCandAudio];
+    unsigned char shadow[kMaxCandAudio];
+    double sel_score[kMaxBeam], fin_sc[kMaxBeam];
+    int sel_src[kMaxBeam], sel_tok[kMaxBeam], fin_src[kMaxBeam];
+};
+static_assert(sizeof(TailScratch) <= kScratchBytes, "tail scratch does not fit the per-warp slice");
+static_assert(sizeof(WarpBuf) <= kScratchBytes, "candidate buffer does not fit the per-warp slice");
+
+// ---- MODE_BEAM tail: BeamSearchTokenExtractor::update for one audio (beam_search.rs:49-146), ONE warp ----
+__device__ __forceinline__ void beam_tail(const StepParams& p, int audio, TailScratch& ts) {
+    const int k = p.beam, K = p.K, n_c = k * K;
+    const int lane = threadIdx.x & 31;
     const int row0 = audio * k;
-    if (tid == 0) ts.nan_seen = 0;
-    for (int i = tid; i < k * k; i += kScanThreads) ts.same[i / k][i % k] = 1;
-    __syncthreads();
-    // 1. which beams share an identical prefix (HashMap key = whole sequence, beam_search.rs:74-77): all pairs,
-    //    all positions in parallel
-    {
-        const int npairs = k * (k - 1) / 2, total = npairs * p.cur_len;
-        for (int idx = tid; idx < total; idx += kScanThreads) {
-            const int pr = idx / p.cur_len, pos = idx - pr * p.cur_len;
-            int a = 0, q = pr;
-            while (q >= k - 1 - a) { q -= k - 1 - a; ++a; }
-            const int b = a + 1 + q;
-            if (p.tokens[(int64_t)(row0 + a) * p.tok_stride + pos] != p.tokens[(int64_t)(row0 + b) * p.tok_stride + pos]) {
-                ts.same[a][b] = 0; ts.same[b][a] = 0;
-            }
-        }
-    }
-    // 2. per-row finish (one warp per row)
-    for (int j = warp; j < k; j += kScanWarps) {
-        const int row = row0 + j;
-        const RowRules rr = row_rules(p.rc, p.tokens + (int64_t)row * p.tok_stride, p.cur_len, p.sample_begin);
-        const RowResult r = finish_row(p, p.partials + (int64_t)row * p.chunks, rr.flags, ts);
-        if (lane < K) {
-            ts.lp[j][lane] = r.lp; ts.tok[j][lane] = r.tok;
-            if (p.dbg_lp) p.dbg_lp[(int64_t)row * K + lane] = r.lp;
-            if (p.dbg_tok) p.dbg_tok[(int64_t)row * K + lane] = r.tok;
-        }
-        if (lane == 0) {
-            if (r.flags & 128u) ts.nan_seen = 1;
-            if (p.dbg_flags) p.dbg_flags[row] = (uint8_t)r.flags;
-        }
-    }
-    __syncthreads();
-    // 3. candidates: score = f64(sum_logprobs[row]) + f64(logprob)   (beam_search.rs:70-71)
-    const int n_c = k * K;
-    for (int c = tid; c < n_c; c += kScanThreads) {
+    const unsigned lt = (1u << lane) - 1u;
+    // 1. candidates: score = f64(sum_logprobs[row]) + f64(logprob)   (beam_search.rs:70-71)
+    bool nan_seen = false;
+    for (int c = lane; c < n_c; c += 32) {
         const int j = c / K, i = c - j * K;
-        const int tok = ts.tok[j][i];
-        // a later beam with the same prefix proposing the same token overwrites this map entry (:77)
-        bool shadowed = false;
-        for (int j2 = j + 1; j2 < k; ++j2)
-            if (ts.same[j][j2])
-                for (int i2 = 0; i2 < K; ++i2) shadowed |= (ts.tok[j2][i2] == tok);
-        ts.c_score[c] = (double)p.sum_in[row0 + j] + (double)ts.lp[j][i];
-        ts.c_row[c] = (short)j; ts.c_shadow[c] = (short)((shadowed || tok == INT32_MAX) ? 1 : 0); ts.c_tok[c] = tok;
+        const RowResult* rr = p.rowres + row0 + j;
+        const float lp = __ldcg(&rr->lp[i]);
+        ts.tok[c] = __ldcg(&rr->tok[i]);
+        ts.score[c] = (double)p.sum_in[row0 + j] + (double)lp;
+        if (i == 0 && (__ldcg(&rr->flags) & 128u)) nan_seen = true;
     }
-    __syncthreads();
-    // 4. rank sort by (score desc, source row asc, token asc); shadowed entries go last
-    for (int c = tid; c < n_c; c += kScanThreads) {
+    const unsigned same_mine = lane < k ? __ldcg(&p.rowres[row0 + lane].same) : 0u;
+    nan_seen = __any_sync(0xffffffffu, nan_seen);
+    __syncwarp();
+    // 2. a later beam with the same prefix proposing the same token overwrites this map entry (:74-77)
+    for (int c0 = 0; c0 < n_c; c0 += 32) {
+        const int c = c0 + lane;
+        const int j = min(c, n_c - 1) / K;
+        const unsigned same = __shfl_sync(0xffffffffu, same_mine, j);
+        if (c < n_c) {
+            const int tok = ts.tok[c];
+            bool shadowed = false;
+            for (int j2 = j + 1; j2 < k; ++j2)
+                if ((same >> j2) & 1u)
+                    for (int i2 = 0; i2 < K; ++i2) shadowed |= (ts.tok[j2 * K + i2] == tok);
+            ts.shadow[c] = (unsigned char)((shadowed || tok == INT32_MAX) ? 1 : 0);
+        }
+    }
+    __syncwarp();
+    // 3. rank sort by (score desc, source row asc, token asc); shadowed entries go last
+    for (int c = lane; c < n_c; c += 32) {
         int rank = 0;
-        const double sc = ts.c_score[c];
+        const double sc = ts.score[c]; const int sh = ts.shadow[c], rw = c / K, tk = ts.tok[c];
         for (int d = 0; d < n_c; ++d) {
             if (d == c) continue;
+            const int shd = ts.shadow[d];
             bool before;
-            if (ts.c_shadow[d] != ts.c_shadow[c]) before = ts.c_shadow[d] < ts.c_shadow[c];
-            else if (ts.c_score[d] != sc) before = ts.c_score[d] > sc;
-            else if (ts.c_row[d] != ts.c_row[c]) before = ts.c_row[d] < ts.c_row[c];
-            else before = ts.c_tok[d] < ts.c_tok[c] || (ts.c_tok[d] == ts.c_tok[c] && d < c);
+            if (shd != sh) before = shd < sh;
+            else if (ts.score[d] != sc) before = ts.score[d] > sc;
+            else if (d / K != rw) before = d / K < rw;
+            else before = ts.tok[d] < tk || (ts.tok[d] == tk && d < c);
             rank += before ? 1 : 0;
         }
-        ts.order[rank] = (short)c;
+        ts.order[rank] = (unsigned short)c;
     }
-    __syncthreads();
-    // 5. walk (beam_search.rs:87-104): EOT-terminated -> finished, others kept until k are saved
-    if (tid == 0) {
-        int saved = 0, nf = 0;
-        for (int o = 0; o < n_c && saved < k; ++o) {
-            const int c = ts.order[o];
-            if (ts.c_shadow[c]) break;   // only shadowed entries remain
-            if (ts.c_tok[c] == p.eot) { if (nf < kMaxBeam) { ts.fin_src[nf] = ts.c_row[c]; ts.fin_sc[nf] = ts.c_score[c]; ++nf; } }
-            else { ts.sel_src[saved] = ts.c_row[c]; ts.sel_tok[saved] = ts.c_tok[c]; ts.sel_score[saved] = ts.c_score[c]; ++saved; }
-        }
-        // fewer than k live candidates cannot happen with >= k+1 finite logits per row; keep the row count anyway
-        for (; saved < k; ++saved) { ts.sel_src[saved] = 0; ts.sel_tok[saved] = p.eot; ts.sel_score[saved] = -CUDART_INF; }
-        ts.n_fin = nf;
-        // finished store: append in descending score until round(patience*k) entries (:124-138)
-        const int have = p.fin_n[audio];
-        const int add = min(nf, max(0, p.max_cand - have));
-        ts.store_base = have; ts.n_store = add;
-        p.fin_n[audio] = have + add;
+    __syncwarp();
+    // 4. walk (beam_search.rs:87-104): EOT-terminated -> finished, others kept until k are saved.  An entry is
+    //    visited iff fewer than k live entries precede it; shadowed entries sort last and end the walk.
+    int saved = 0, nf = 0;
+    for (int base = 0; base < n_c && saved < k; base += 32) {
+        const int o = base + lane;
+        const bool valid = o < n_c;
+        const int c = valid ? ts.order[o] : 0;
+        const bool ok = valid && !ts.shadow[c];
+        const bool live = ok && ts.tok[c] != p.eot, fin = ok && ts.tok[c] == p.eot;
+        const unsigned lm = __ballot_sync(0xffffffffu, live);
+        const int live_before = saved + __popc(lm & lt);
+        const bool visited = live_before < k;
+        const unsigned vm = __ballot_sync(0xffffffffu, visited);
+        const unsigned fm = __ballot_sync(0xffffffffu, fin && visited);
+        if (live && visited) { ts.sel_src[live_before] = c / K; ts.sel_tok[live_before] = ts.tok[c]; ts.sel_score[live_before] = ts.score[c]; }
+        const int fidx = nf + __popc(fm & lt);
+        if (fin && visited && fidx < kMaxBeam) { ts.fin_src[fidx] = c / K; ts.fin_sc[fidx] = ts.score[c]; }
+        saved += __popc(lm & vm);
+        nf = min(nf + __popc(fm), kMaxBeam);
+    }
+    __syncwarp();
+    // fewer than k live candidates cannot happen with >= k+1 finite logits per row; keep the row count anyway
+    if (lane >= saved && lane < k) { ts.sel_src[lane] = 0; ts.sel_tok[lane] = p.eot; ts.sel_score[lane] = -CUDART_INF; }
+    // finished store: append in descending score until round(patience*k) entries (:124-138)
+    int have = 0;
+    if (lane == 0) {
+        have = p.fin_n[audio];
+        p.fin_n[audio] = have + min(nf, max(0, p.max_cand - have));
         if (p.dbg_fin_count) p.dbg_fin_count[audio] = nf;
-        for (int i = 0; i < k; ++i) {
-            if (p.dbg_fin_source) p.dbg_fin_source[audio * k + i] = i < nf ? row0 + ts.fin_src[i] : -1;
-            if (p.dbg_fin_score) p.dbg_fin_score[audio * k + i] = i < nf ? ts.fin_sc[i] : 0.0;
-        }
-        if (ts.nan_seen) atomicAdd(&p.status->nan_rows, 1);
+        if (nan_seen) atomicAdd(&p.status->nan_rows, 1);
     }
-    __syncthreads();
-    // 6. outputs: all rows in parallel
-    for (int i = tid; i < k; i += kScanThreads) {
-        p.source_idx[row0 + i] = row0 + ts.sel_src[i];
-        p.sum_out[row0 + i] = (float)ts.sel_score[i];   // index_put_(.., score as f32) :91-95
+    have = __shfl_sync(0xffffffffu, have, 0);
+    const int n_store = min(nf, max(0, p.max_cand - have));
+    __syncwarp();
+    if (lane < k) {
+        if (p.dbg_fin_source) p.dbg_fin_source[audio * k + lane] = lane < nf ? row0 + ts.fin_src[lane] : -1;
+        if (p.dbg_fin_score) p.dbg_fin_score[audio * k + lane] = lane < nf ? ts.fin_sc[lane] : 0.0;
+        p.source_idx[row0 + lane] = row0 + ts.sel_src[lane];
+        p.sum_out[row0 + lane] = (float)ts.sel_score[lane];   // index_put_(.., score as f32) :91-95
     }
+    // 5. outputs
     const int L1 = p.cur_len + 1;
-    for (int idx = tid; idx < k * L1; idx += kScanThreads) {
+    for (int idx = lane; idx < k * L1; idx += 32) {
         const int i = idx / L1, t = idx - i * L1;
         p.next_tokens[(int64_t)(row0 + i) * p.next_stride + t] =
             t < p.cur_len ? p.tokens[(int64_t)(row0 + ts.sel_src[i]) * p.tok_stride + t] : (int64_t)ts.sel_tok[i];
     }
-    for (int idx = tid; idx < ts.n_store * L1; idx += kScanThreads) {
+    for (int idx = lane; idx < n_store * L1; idx += 32) {
         const int i = idx / L1, t = idx - i * L1;
-        const int slot = ts.store_base + i;
+        const int slot = have + i;
         p.fin_tokens[((int64_t)audio * p.max_cand + slot) * p.max_len + t] =
             t < p.cur_len ? p.tokens[(int64_t)(row0 + ts.fin_src[i]) * p.tok_stride + t] : (int64_t)p.eot;
         if (t == 0) {
@@ -254,9 +405,9 @@ __device__ __forceinline__ void beam_tail(const StepParams& p, int audio, TailSm
             p.fin_score[audio * p.max_cand + slot] = ts.fin_sc[i];
         }
     }
-    // 7. completed = all audios hold max_cand finished sequences (:141-146); last audio to arrive publishes
-    if (tid == 0) {
-        const int full = (ts.store_base + ts.n_store >= p.max_cand) ? 1 : 0;
+    // 6. completed = all audios hold max_cand finished sequences (:141-146); last audio to arrive publishes
+    if (lane == 0) {
+        const int full = (have + n_store >= p.max_cand) ? 1 : 0;
         if (full) atomicAdd(p.sync + 1, 1);
         __threadfence();
         const int arrived = atomicAdd(p.sync, 1);
@@ -267,25 +418,20 @@ __device__ __forceinline__ void beam_tail(const StepParams& p, int audio, TailSm
             atomicExch(p.sync, 0);
         }
     }
+    __syncwarp();
 }
 
-// ---- MODE_GREEDY tail: GreedyTokenExtractor::update for one row (src/decode/extractor/greedy.rs:24-50) ----
-__device__ __forceinline__ void greedy_tail(const StepParams& p, int row, TailSmem& ts) {
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+// ---- MODE_GREEDY tail: GreedyTokenExtractor::update for one row (src/decode/extractor/greedy.rs:24-50), one warp ----
+__device__ __forceinline__ void greedy_tail(const StepParams& p, int row, const RowOut& r) {
+    const int lane = threadIdx.x & 31;
     const int64_t* rt = p.tokens + (int64_t)row * p.tok_stride;
     int64_t* dst = p.next_tokens + (int64_t)row * p.next_stride;
-    for (int t = tid; t < p.cur_len; t += kScanThreads) dst[t] = rt[t];
-    if (warp != 0) return;
-    const RowRules rr = row_rules(p.rc, rt, p.cur_len, p.sample_begin);
-    const RowResult r = finish_row(p, p.partials + (int64_t)row * p.chunks, rr.flags, ts);
+    for (int t = lane; t < p.cur_len; t += 32) dst[t] = rt[t];
     if (lane != 0) return;
     const bool last_eot = rt[p.cur_len - 1] == p.eot;                       // greedy.rs:37-38
     const int next = last_eot ? p.eot : r.tok;                               // :41-45
     p.sum_out[row] = p.sum_in[row] + (last_eot ? 0.0f : r.lp);               // :39
     dst[p.cur_len] = next;
-    if (p.dbg_lp) p.dbg_lp[row] = r.lp;
-    if (p.dbg_tok) p.dbg_tok[row] = r.tok;
-    if (p.dbg_flags) p.dbg_flags[row] = (uint8_t)r.flags;
     if (r.flags & 128u) atomicAdd(&p.status->nan_rows, 1);
     if (next == p.eot) atomicAdd(p.sync + 1, 1);
     __threadfence();
@@ -298,66 +444,185 @@ __device__ __forceinline__ void greedy_tail(const StepParams& p, int row, TailSm
     }
 }
 
-// ---- MODE_FILTER tail: timestamp_tokens.rs:37-96 in place for one row.  The statistics were taken on the
-// logits as they are (earlier filters already wrote their -inf), so the decision sees what the reference's
-// log_softmax sees.  Every chunk of the row has been read by now: the fills cannot race the scan.
-__device__ __forceinline__ void filter_tail(const StepParams& p, int row, TailSmem& ts) {
-    const int tid = threadIdx.x;
-    const RowRules rr = row_rules(p.rc, p.tokens + (int64_t)row * p.tok_stride, p.cur_len, p.sample_begin);
-    if (tid < 32) {
-        const RowResult r = finish_row(p, p.partials + (int64_t)row * p.chunks, rr.flags, ts);
-        if (tid == 0) {
-            ts.flags = r.flags;
-            if (p.dbg_flags) p.dbg_flags[row] = (uint8_t)r.flags;
-        }
-    }
-    __syncthreads();
-    const bool kill_text = (ts.flags & 8u) != 0;
+// ---- MODE_FILTER tail: timestamp_tokens.rs:37-96 in place for one row, one warp.  The statistics were taken on
+// the logits as they are (earlier filters already wrote their -inf), so the decision sees what the reference's
+// log_softmax sees.  Every unit of the row has been read by now: the fills cannot race the scan.
+__device__ __forceinline__ void filter_tail(const StepParams& p, int row, const RowRules& rr, unsigned flags) {
+    const int lane = threadIdx.x & 31;
+    const bool kill_text = (flags & 8u) != 0;
     float* rp = p.logits + (int64_t)row * p.row_stride;
     const int tsb = p.rc.ts_begin, V = p.rc.n_vocab;
-    // text side: surviving range is [t_lo, t_hi) unless the decision fired
     const int keep_lo = kill_text ? tsb : rr.t_lo, keep_hi = kill_text ? tsb : rr.t_hi;
-    for (int i = tid; i < tsb; i += kScanThreads)
-        if (i < keep_lo || i >= keep_hi) rp[i] = -CUDART_INF_F;
-    for (int i = tsb + tid; i < V; i += kScanThreads)
-        if (i < rr.s_lo || i >= rr.s_hi) rp[i] = -CUDART_INF_F;
-    if (tid == 0 && p.no_timestamps >= 0 && p.no_timestamps < V) rp[p.no_timestamps] = -CUDART_INF_F;
+    for (int i = lane; i < keep_lo; i += 32) rp[i] = -CUDART_INF_F;
+    for (int i = keep_hi + lane; i < tsb; i += 32) rp[i] = -CUDART_INF_F;
+    for (int i = tsb + lane; i < rr.s_lo; i += 32) rp[i] = -CUDART_INF_F;
+    for (int i = max(rr.s_hi, tsb) + lane; i < V; i += 32) rp[i] = -CUDART_INF_F;
+    if (lane == 0 && p.no_timestamps >= 0 && p.no_timestamps < V) rp[p.no_timestamps] = -CUDART_INF_F;
 }
 
 template <int MODE>
-__global__ void __launch_bounds__(kScanThreads, 2) decode_step_kernel(const StepParams p) {
-    __shared__ ScanSmem sm;
-    __shared__ TailSmem ts;
-    __shared__ int s_last;
-    const int row = blockIdx.y, chunk = blockIdx.x;
-    const int tid = threadIdx.x;
-    const RowRules rr = row_rules(p.rc, p.tokens + (int64_t)row * p.tok_stride, p.cur_len, p.sample_begin);
-    const uint32_t* bm = (p.cur_len == p.sample_begin) ? p.bm_first : p.bm;
-    int lo, hi;
-    if (chunk < p.n_text) {
-        const int c_lo = chunk * p.text_len;
-        lo = max(c_lo, rr.t_lo); hi = min(min(p.ts_split, c_lo + p.text_len), rr.t_hi);
-    } else {
-        const int c_lo = p.ts_split + (chunk - p.n_text) * p.ts_len;
-        lo = max(c_lo, rr.s_lo); hi = min(min(p.rc.n_vocab, c_lo + p.ts_len), rr.s_hi);
+__global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const StepParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned char* scratch = smem_raw + warp * kScratchBytes;
+    WarpBuf& wb = *reinterpret_cast<WarpBuf*>(scratch);
+
+    // N units are dealt to the first Wt = min(warps of the grid, N) warps: every active warp owns >= 1 unit, so the
+    // owners of consecutive units are consecutive warps (row_partials relies on that)
+    const int64_t N = (int64_t)p.n_rows * p.upr;
+    const int64_t Wt = min((int64_t)gridDim.x * kStepWarps, N);
+    const int64_t gw = (int64_t)blockIdx.x * kStepWarps + warp;
+    if (gw >= Wt) return;
+    const int64_t u_begin = gw * N / Wt, u_end = (gw + 1) * N / Wt;
+
+    // rules of the first two rows this warp touches are fetched up front (a later row change costs a bubble)
+    const int row_first = (int)(u_begin / p.upr);
+    int64_t tk_last[2], tk_pen[2];
+#pragma unroll
+    for (int q = 0; q < 2; ++q) {
+        const int r = min(row_first + q, p.n_rows - 1);
+        const int64_t* rt = p.tokens + (int64_t)r * p.tok_stride;
+        tk_last[q] = rt[p.cur_len - 1];
+        tk_pen[q] = p.cur_len >= 2 ? rt[p.cur_len - 2] : 0;
     }
-    scan_chunk(p.logits + (int64_t)row * p.row_stride, lo, hi, bm, p.K, sm, p.partials + (int64_t)row * p.chunks + chunk);
-    // arrive: the partial was written by warp 0 (or by threads 0..15 on the empty path)
-    const int group = (MODE == MODE_BEAM) ? row / p.beam : row;
-    const int expected = ((MODE == MODE_BEAM) ? p.beam : 1) * p.chunks;
-    __threadfence();
-    __syncthreads();
-    if (tid == 0) {
-        const int prev = atomicAdd(p.arrive + group, 1);
-        s_last = (prev == expected - 1) ? 1 : 0;
-        if (s_last) p.arrive[group] = 0;         // self-reset for the next launch (stream-ordered)
+    int rules_row = -1;
+    RowRules rules;
+    rules.t_lo = rules.t_hi = rules.s_lo = rules.s_hi = 0; rules.flags = 0;
+
+    auto rules_for = [&](int row) {
+        if (row == rules_row) return;
+        if (row == row_first) rules = row_rules_from(p.rc, tk_last[0], tk_pen[0], p.cur_len, p.sample_begin);
+        else if (row == row_first + 1) rules = row_rules_from(p.rc, tk_last[1], tk_pen[1], p.cur_len, p.sample_begin);
+        else rules = row_rules(p.rc, p.tokens + (int64_t)row * p.tok_stride, p.cur_len, p.sample_begin);
+        rules_row = row;
+    };
+    auto geom_of = [&](int64_t u) {
+        Geom g;
+        g.row = (int)(u / p.upr);
+        const int j = (int)(u - (int64_t)g.row * p.upr);
+        rules_for(g.row);
+        int plo, phi;
+        if (j < p.n_text_units) { g.part = 0; plo = j * kUnit; phi = min(p.ts_split, plo + kUnit); g.lo = max(plo, rules.t_lo); g.hi = min(phi, rules.t_hi); }
+        else { g.part = 1; plo = p.ts_split + (j - p.n_text_units) * kUnit; phi = min(p.rc.n_vocab, plo + kUnit); g.lo = max(plo, rules.s_lo); g.hi = min(phi, rules.s_hi); }
+        const float* rp = p.logits + (int64_t)g.row * p.row_stride;
+        const int mis = (int)((reinterpret_cast<uintptr_t>(rp + g.lo) >> 2) & 3);
+        g.a0 = g.lo - mis;
+        return g;
+    };
+    // loads of one unit: element base of slot j is a0 + 4 (lane + 32 j); everything outside [lo, hi) reads as -inf
+    auto load_unit = [&](const Geom& g, float (&x)[kNV][4], uint32_t& bmw) {
+        if (g.hi <= g.lo) { bmw = 0u; return; }
+        const float* __restrict__ rp = p.logits + (int64_t)g.row * p.row_stride;
+#pragma unroll
+        for (int j = 0; j < kNV; ++j) {
+            const int e = g.a0 + 4 * (lane + 32 * j);
+            if (e >= g.lo && e + 3 < g.hi) {
+                const float4 q = __ldcs(reinterpret_cast<const float4*>(rp + e));
+                x[j][0] = q.x; x[j][1] = q.y; x[j][2] = q.z; x[j][3] = q.w;
+            } else {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) x[j][i] = (e + i >= g.lo && e + i < g.hi) ? __ldcs(rp + e + i) : -CUDART_INF_F;
+            }
+        }
+        const int wbase = max(g.a0, 0) >> 5;
+        bmw = __ldg(p.bm + min(wbase + lane, p.bm_words - 1));
+    };
+
+    float xn[kNV][4];
+    uint32_t bm_n = 0u;
+    Geom gn = geom_of(u_begin);
+    load_unit(gn, xn, bm_n);
+    Run run;
+    run.m = -CUDART_INF_F; run.s = 0.0f; run.n = 0;
+
+    for (int64_t u = u_begin; u < u_end; ++u) {
+        const Geom g = gn;
+        float x[kNV][4];
+#pragma unroll
+        for (int j = 0; j < kNV; ++j)
+#pragma unroll
+            for (int i = 0; i < 4; ++i) x[j][i] = xn[j][i];
+        const uint32_t bmw = bm_n;
+        const bool has_next = u + 1 < u_end;
+        if (has_next) { gn = geom_of(u + 1); load_unit(gn, xn, bm_n); }
+        if (g.hi > g.lo) reduce_unit(x, g, bmw, max(g.a0, 0) >> 5, p.K, wb, run);
+        if (has_next && gn.row == g.row && gn.part == g.part) continue;
+
+        // ---- end of a (row, partition) run: leave the partial, arrive on the row
+        const RowPartials rpz = row_partials(p, g.row, Wt, N);
+        Partial* out = p.partials + (int64_t)g.row * p.upr + rpz.base[g.part] + (int)(gw - rpz.first_owner[g.part]);
+        if (lane < kMaxK) {
+            out->v[lane] = lane < run.n ? wb.v[lane] : -CUDART_INF_F;
+            out->id[lane] = lane < run.n ? wb.id[lane] : INT32_MAX;
+        }
+        if (lane == 0) { out->m = run.m; out->s = run.s; out->n = run.n; }
+        run.m = -CUDART_INF_F; run.s = 0.0f; run.n = 0;
+        __threadfence();
+        __syncwarp();
+        int last = 0;
+        if (lane == 0) {
+            const int expected = rpz.count[0] + rpz.count[1];
+            const int prev = atomicAdd(p.row_arrive + g.row, 1);
+            last = (prev == expected - 1) ? 1 : 0;
+            if (last) p.row_arrive[g.row] = 0;           // self-reset for the next launch (stream-ordered)
+        }
+        last = __shfl_sync(0xffffffffu, last, 0);
+        if (!last) continue;
+        __threadfence();
+
+        // ---- this warp completed the row: merge it
+        const int row = g.row;
+        RowRules rr_row;
+        {
+            const int keep = rules_row;                  // rules of the prefetched unit must survive
+            const RowRules keep_rules = rules;
+            rules_for(row);
+            rr_row = rules;
+            rules = keep_rules; rules_row = keep;
+        }
+        unsigned same = 0u;
+        if (MODE == MODE_BEAM) {
+            // which later beams of this audio hold an identical prefix (HashMap key = whole sequence, beam_search.rs:74-77)
+            const int j = row % p.beam, rbase = row - j;
+            const int64_t* mine = p.tokens + (int64_t)row * p.tok_stride;
+            for (int j2 = j + 1; j2 < p.beam; ++j2) {
+                const int64_t* other = p.tokens + (int64_t)(rbase + j2) * p.tok_stride;
+                bool diff = false;
+                for (int t = lane; t < p.cur_len; t += 32) diff |= (mine[t] != other[t]);
+                if (!__any_sync(0xffffffffu, diff)) same |= 1u << j2;
+            }
+        }
+        const RowOut r = merge_row(p, row, rr_row.flags, rpz, wb);
+        if (lane < p.K) {
+            if (p.dbg_lp) p.dbg_lp[(int64_t)row * p.K + lane] = r.lp;
+            if (p.dbg_tok) p.dbg_tok[(int64_t)row * p.K + lane] = r.tok;
+        }
+        if (lane == 0 && p.dbg_flags) p.dbg_flags[row] = (uint8_t)r.flags;
+        if (MODE == MODE_GREEDY) {
+            greedy_tail(p, row, r);
+            __syncwarp();
+        } else if (MODE == MODE_FILTER) {
+            filter_tail(p, row, rr_row, r.flags);
+        } else {
+            RowResult* res = p.rowres + row;
+            if (lane < kMaxK) { res->lp[lane] = r.lp; res->tok[lane] = lane < p.K ? r.tok : INT32_MAX; }
+            if (lane == 0) { res->flags = r.flags; res->same = same; }
+            __threadfence();
+            __syncwarp();
+            const int audio = row / p.beam;
+            int last_a = 0;
+            if (lane == 0) {
+                const int prev = atomicAdd(p.audio_arrive + audio, 1);
+                last_a = (prev == p.beam - 1) ? 1 : 0;
+                if (last_a) p.audio_arrive[audio] = 0;
+            }
+            last_a = __shfl_sync(0xffffffffu, last_a, 0);
+            if (last_a) {
+                __threadfence();
+                beam_tail(p, audio, *reinterpret_cast<TailScratch*>(scratch));
+            }
+        }
     }
-    __syncthreads();
-    if (!s_last) return;
-    __threadfence();
-    if (MODE == MODE_BEAM) beam_tail(p, group, ts);
-    else if (MODE == MODE_GREEDY) greedy_tail(p, group, ts);
-    else filter_tail(p, group, ts);
 }
 
 // ---- sparse in-place fills: logits.index_fill_(1, idx, -inf)   suppress_tokens.rs:22, suppress_blanks.rs:41
@@ -410,13 +675,33 @@ StepParams step_params(wrs_decoder* dec, const float* logits, int64_t row_stride
     p.cur_len = (int)cur_len; p.sample_begin = (int)sample_begin; p.n_rows = (int)n_rows; p.K = K; p.beam = beam;
     p.n_groups = (int)(n_rows / beam);
     p.rc = rule_cfg(dec->cfg);
-    p.ts_split = dec->ts_split; p.n_text = dec->n_text; p.text_len = dec->text_len; p.n_ts = dec->n_ts; p.ts_len = dec->ts_len;
-    p.chunks = dec->chunks;
-    p.bm = bm; p.bm_first = bm_first; p.partials = dec->d_partials; p.arrive = dec->d_arrive;
+    p.ts_split = dec->ts_split; p.n_text_units = dec->n_text_units; p.n_ts_units = dec->n_ts_units; p.upr = dec->upr;
+    p.bm_words = dec->bm_words;
+    p.bm = (cur_len == sample_begin) ? bm_first : bm;   // SuppressBlank acts on the first step only (suppress_blanks.rs:40)
+    p.partials = dec->d_partials; p.rowres = dec->d_rowres;
+    p.row_arrive = dec->d_arrive; p.audio_arrive = dec->d_arrive + dec->max_rows;
     p.eot = dec->cfg.eot; p.max_cand = dec->max_cand; p.max_len = dec->cfg.max_len; p.no_timestamps = dec->cfg.no_timestamps;
     p.fin_tokens = dec->d_fin_tokens; p.fin_len = dec->d_fin_len; p.fin_score = dec->d_fin_score; p.fin_n = dec->d_fin_n;
     p.sync = dec->d_sync; p.status = dec->ctx->d_status;
     return p;
+}
+
+// one persistent 512-thread CTA per SM at most; every warp gets at least one unit
+template <int MODE>
+int launch_step(wrs_decoder* dec, const StepParams& p, cudaStream_t stream) {
+    wrs_ctx* ctx = dec->ctx;
+    const size_t smem = (size_t)kStepWarps * kScratchBytes;
+    if (!dec->smem_attr_set) {
+        WRS_CUDA(ctx, cudaFuncSetAttribute(decode_step_kernel<MODE_BEAM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        WRS_CUDA(ctx, cudaFuncSetAttribute(decode_step_kernel<MODE_GREEDY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        WRS_CUDA(ctx, cudaFuncSetAttribute(decode_step_kernel<MODE_FILTER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        dec->smem_attr_set = true;
+    }
+    const int64_t units = (int64_t)p.n_rows * p.upr;
+    const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctx->sm_count, (units + kStepWarps - 1) / kStepWarps));
+    decode_step_kernel<MODE><<<grid, kStepThreads, smem, stream>>>(p);
+    WRS_CUDA(ctx, cudaGetLastError());
+    return WRS_OK;
 }
 
 void set_debug(StepParams& p, const wrs_step_debug* dbg) {
@@ -445,18 +730,11 @@ int wrs_decoder_create(wrs_ctx* ctx, const wrs_decode_cfg* cfg, const int32_t* s
     wrs_decoder* d = new wrs_decoder();
     d->ctx = ctx; d->cfg = c; d->max_rows = max_rows; d->max_audio = max_rows / c.beam_size;
     d->max_cand = std::max(1, (int)std::round(c.patience * (float)c.beam_size));   // f32::round, beam_search.rs:122
-    // chunk geometry: text ids [0, ts_split) and timestamp ids [ts_split, V) never share a CTA
+    // unit geometry: text ids [0, ts_split) and timestamp ids [ts_split, V) never share a unit
     d->ts_split = c.timestamps ? c.ts_begin : c.n_vocab;
-    d->n_text = (d->ts_split + kChunkCap - 1) / kChunkCap;
-    d->text_len = d->n_text ? ((((d->ts_split + d->n_text - 1) / d->n_text) + 3) & ~3) : 0;
-    const int n_tsid = c.n_vocab - d->ts_split;
-    d->n_ts = (n_tsid + kChunkCap - 1) / kChunkCap;
-    d->ts_len = d->n_ts ? ((((n_tsid + d->n_ts - 1) / d->n_ts) + 3) & ~3) : 0;
-    d->chunks = d->n_text + d->n_ts;
-    if (d->chunks > kMaxChunks || d->text_len > kChunkCap || d->ts_len > kChunkCap) {
-        delete d;
-        return fail(ctx, WRS_ERR_UNSUPPORTED, "wrs_decoder_create: vocabulary too large for 9 chunks of 14333 ids per row");
-    }
+    d->n_text_units = (d->ts_split + kUnit - 1) / kUnit;
+    d->n_ts_units = (c.n_vocab - d->ts_split + kUnit - 1) / kUnit;
+    d->upr = d->n_text_units + d->n_ts_units;
     d->bm_words = (c.n_vocab + 31) / 32 + 2;
     std::vector<uint32_t> base(d->bm_words, 0u), first, ts(d->bm_words, 0u);
     auto setbit = [&](std::vector<uint32_t>& b, int id) { if (id >= 0 && id < c.n_vocab) b[id >> 5] |= 1u << (id & 31); };
@@ -479,9 +757,10 @@ int wrs_decoder_create(wrs_ctx* ctx, const wrs_decode_cfg* cfg, const int32_t* s
     const size_t fin_tok = sizeof(int64_t) * (size_t)d->max_audio * d->max_cand * c.max_len;
     if ((n_suppress > 0 && ((e = cudaMalloc(&d->d_suppress, sizeof(int32_t) * n_suppress)) != cudaSuccess ||
                             (e = cudaMemcpy(d->d_suppress, suppress_ids, sizeof(int32_t) * n_suppress, cudaMemcpyHostToDevice)) != cudaSuccess)) ||
-        (e = cudaMalloc(&d->d_partials, sizeof(Partial) * d->chunks * (size_t)max_rows)) != cudaSuccess ||
-        (e = cudaMalloc(&d->d_arrive, sizeof(int32_t) * max_rows)) != cudaSuccess ||
-        (e = cudaMemset(d->d_arrive, 0, sizeof(int32_t) * max_rows)) != cudaSuccess ||
+        (e = cudaMalloc(&d->d_partials, sizeof(Partial) * d->upr * (size_t)max_rows)) != cudaSuccess ||
+        (e = cudaMalloc(&d->d_rowres, sizeof(RowResult) * (size_t)max_rows)) != cudaSuccess ||
+        (e = cudaMalloc(&d->d_arrive, sizeof(int32_t) * (max_rows + d->max_audio))) != cudaSuccess ||
+        (e = cudaMemset(d->d_arrive, 0, sizeof(int32_t) * (max_rows + d->max_audio))) != cudaSuccess ||
         (e = cudaMalloc(&d->d_blank, sizeof(int32_t) * 2)) != cudaSuccess ||
         (e = cudaMemcpy(d->d_blank, c.blank_ids, sizeof(int32_t) * 2, cudaMemcpyHostToDevice)) != cudaSuccess ||
         (e = cudaMalloc(&d->d_fin_tokens, fin_tok)) != cudaSuccess ||
@@ -502,7 +781,7 @@ void wrs_decoder_destroy(wrs_decoder* d) {
     if (!d) return;
     cudaSetDevice(d->ctx->device);
     cudaFree(d->d_bm_base); cudaFree(d->d_bm_first); cudaFree(d->d_bm_ts); cudaFree(d->d_arrive); cudaFree(d->d_blank);
-    cudaFree(d->d_suppress); cudaFree(d->d_partials); cudaFree(d->d_fin_tokens); cudaFree(d->d_fin_len);
+    cudaFree(d->d_suppress); cudaFree(d->d_partials); cudaFree(d->d_rowres); cudaFree(d->d_fin_tokens); cudaFree(d->d_fin_len);
     cudaFree(d->d_fin_score); cudaFree(d->d_fin_n); cudaFree(d->d_sync);
     delete d;
 }
@@ -512,7 +791,7 @@ int wrs_decoder_reset(wrs_decoder* d, wrs_stream_t stream) {
     WRS_CUDA(d->ctx, cudaSetDevice(d->ctx->device));
     WRS_CUDA(d->ctx, cudaMemsetAsync(d->d_fin_n, 0, sizeof(int32_t) * d->max_audio, (cudaStream_t)stream));
     WRS_CUDA(d->ctx, cudaMemsetAsync(d->d_sync, 0, sizeof(int32_t) * 2, (cudaStream_t)stream));
-    WRS_CUDA(d->ctx, cudaMemsetAsync(d->d_arrive, 0, sizeof(int32_t) * d->max_rows, (cudaStream_t)stream));
+    WRS_CUDA(d->ctx, cudaMemsetAsync(d->d_arrive, 0, sizeof(int32_t) * (d->max_rows + d->max_audio), (cudaStream_t)stream));
     return WRS_OK;
 }
 
@@ -540,8 +819,8 @@ int wrs_filter_apply(wrs_decoder* dec, int32_t which, float* logits, int64_t row
         StepParams p = step_params(dec, logits, row_stride, n_rows, tokens, tok_stride, cur_len, sample_begin, 1, 1,
                                    dec->d_bm_ts, dec->d_bm_ts);
         p.dbg_flags = row_flags;
-        decode_step_kernel<MODE_FILTER><<<dim3(dec->chunks, (unsigned)n_rows), kScanThreads, 0, stream>>>(p);
-        WRS_CUDA(ctx, cudaGetLastError());
+        rc = launch_step<MODE_FILTER>(dec, p, stream);
+        if (rc != WRS_OK) return rc;
     }
     return WRS_OK;
 }
@@ -565,9 +844,7 @@ int wrs_beam_step(wrs_decoder* dec, const float* logits, int64_t row_stride, int
     p.sum_in = sum_in; p.sum_out = sum_out; p.next_tokens = next_tokens; p.next_stride = next_stride;
     p.source_idx = source_idx; p.completed = completed;
     set_debug(p, dbg);
-    decode_step_kernel<MODE_BEAM><<<dim3(dec->chunks, (unsigned)n_rows), kScanThreads, 0, stream>>>(p);
-    WRS_CUDA(ctx, cudaGetLastError());
-    return WRS_OK;
+    return launch_step<MODE_BEAM>(dec, p, stream);
 }
 
 int wrs_greedy_step(wrs_decoder* dec, const float* logits, int64_t row_stride, int64_t n_rows, const int64_t* tokens,
@@ -585,9 +862,7 @@ int wrs_greedy_step(wrs_decoder* dec, const float* logits, int64_t row_stride, i
                                dec->d_bm_base, dec->d_bm_first);
     p.sum_in = sum_in; p.sum_out = sum_out; p.next_tokens = next_tokens; p.next_stride = next_stride; p.completed = completed;
     set_debug(p, dbg);
-    decode_step_kernel<MODE_GREEDY><<<dim3(dec->chunks, (unsigned)n_rows), kScanThreads, 0, stream>>>(p);
-    WRS_CUDA(ctx, cudaGetLastError());
-    return WRS_OK;
+    return launch_step<MODE_GREEDY>(dec, p, stream);
 }
 
 }  // extern "C"
