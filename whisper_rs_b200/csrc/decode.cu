@@ -80,29 +80,32 @@ struct StepParams {
 struct Geom {
     int row, part;      // part 0 = text ids, 1 = timestamp ids
     int lo, hi;         // surviving ids of the unit [lo, hi) after the row's rules (hi <= lo: nothing to read)
-    int a0;             // id of the first loaded element (lo rounded down to a 16-byte boundary of the row's memory)
+    int a0;             // id of the unit's first element slot (16-byte aligned in the row's memory; may be < lo)
 };
-
-// the running statistics of the (row, partition) run a warp is reducing; its candidates sit in WarpBuf[0, n)
-struct Run { float m, s; int n; };
 
 // Fold one unit (already in registers, masked ranges loaded as -inf) into the run.
 __device__ __forceinline__ void reduce_unit(float (&x)[kNV][4], const Geom& g, uint32_t bmw, int wbase, int K, WarpBuf& wb,
                                             Run& run) {
     const int lane = threadIdx.x & 31;
-    // ---- 1. suppress bitmap -> -inf (bit set = masked); most units hold no suppressed id at all
-    if (__any_sync(0xffffffffu, bmw != 0u)) {
+    // ---- 1. suppress bitmap -> -inf (bit set = masked).  Lane l holds bitmap word wbase + l; most 128-id slots
+    //         hold no suppressed id at all and are skipped on a warp-uniform test
+    const uint32_t nz = __ballot_sync(0xffffffffu, bmw != 0u);
+    if (nz) {
 #pragma unroll
         for (int j = 0; j < kNV; ++j) {
-            const int e = g.a0 + 4 * (lane + 32 * j);
-            const int rel = max((e >> 5) - wbase, 0);
-            const uint32_t w0 = __shfl_sync(0xffffffffu, bmw, rel), w1 = __shfl_sync(0xffffffffu, bmw, rel + 1);
-            // e < 0 (row start not 16-byte aligned): ids e..-1 do not exist, ids 0..e+3 take the low bits of word 0
-            const uint32_t bits = (e >= 0 ? __funnelshift_r(w0, w1, e & 31) : (w0 << (-e))) & 0xFu;
-            if (bits) {
+            const int e0 = g.a0 + 128 * j;                                   // first id of the slot (lane 0)
+            const int rel0 = max((e0 >> 5) - wbase, 0);
+            if ((nz >> rel0) & 0x1Fu) {                                      // 128 ids span at most 5 words
+                const int e = e0 + 4 * lane;
+                const int rel = max((e >> 5) - wbase, 0);
+                const uint32_t w0 = __shfl_sync(0xffffffffu, bmw, rel), w1 = __shfl_sync(0xffffffffu, bmw, rel + 1);
+                // e < 0 (row start not 16-byte aligned): ids e..-1 do not exist, ids 0..e+3 take the low bits of word 0
+                const uint32_t bits = (e >= 0 ? __funnelshift_r(w0, w1, e & 31) : (w0 << (-e))) & 0xFu;
+                if (bits) {
 #pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    if (bits & (1u << i)) x[j][i] = -CUDART_INF_F;
+                    for (int i = 0; i < 4; ++i)
+                        if (bits & (1u << i)) x[j][i] = -CUDART_INF_F;
+                }
             }
         }
     }
@@ -128,12 +131,12 @@ __device__ __forceinline__ void reduce_unit(float (&x)[kNV][4], const Geom& g, u
     else if (wmax > run.m) { run.s = run.s * exp_diff(run.m, wmax) + ssum; run.m = wmax; }
     else if (wmax > -CUDART_INF_F) run.s += ssum * ex2((wmax - run.m) * kLog2e);
     if (wmax == -CUDART_INF_F) return;                   // nothing finite in this unit
-    // ---- 3. threshold: at least K elements of {unit} reach tau_u; nothing below the run's K-th best can matter
+    // ---- 3. threshold: at least K elements of the unit reach tau_u; nothing below the run's K-th best can matter
     const float tau_u = kth_threshold(tmax, K);
-    const int n0 = run.n;
-    const float tau_r = (n0 >= K) ? wb.v[K - 1] : -CUDART_INF_F;
+    const float tau_r = __shfl_sync(0xffffffffu, run.rv, K - 1);     // -inf while the run holds fewer than K
     const float tau = fmaxf(tau_u, tau_r);
-    if (lane == 0) wb.n = n0;
+    if (!__any_sync(0xffffffffu, tmax >= tau)) return;
+    if (lane == 0) wb.n = 0;
     __syncwarp();
     // ---- 4. gather everything at or above the threshold
     if (tmax >= tau) {
@@ -143,37 +146,15 @@ __device__ __forceinline__ void reduce_unit(float (&x)[kNV][4], const Geom& g, u
             for (int i = 0; i < 4; ++i)
                 if (x[j][i] >= tau && x[j][i] > -CUDART_INF_F) {
                     const int pos = atomicAdd(&wb.n, 1);
-                    if (pos < kCandCap) { wb.v[pos] = x[j][i]; wb.id[pos] = g.a0 + 4 * (lane + 32 * j) + i; }
+                    if (pos < kCandCap - kMaxK) { wb.v[pos] = x[j][i]; wb.id[pos] = g.a0 + 4 * (lane + 32 * j) + i; }
                 }
     }
     __syncwarp();
-    const int n = wb.n;
-    if (n <= kCandCap) { run.n = warp_compact(wb, n, K); return; }
-    // ---- 5. massive ties: K rounds of exact warp-wide selection over {old list} U {unit}, each strictly after the last pick
-    const float ov = lane < n0 ? wb.v[lane] : -CUDART_INF_F; const int oi = lane < n0 ? wb.id[lane] : INT32_MAX;
-    __syncwarp();
-    float pv = CUDART_INF_F; int pi = -1, cnt = 0;
-    for (int r = 0; r < K; ++r) {
-        float bv = -CUDART_INF_F; int bi = INT32_MAX;
-        {
-            const bool after = ov < pv || (ov == pv && oi > pi);
-            if (after && ov > -CUDART_INF_F) { bv = ov; bi = oi; }
-        }
-#pragma unroll
-        for (int j = 0; j < kNV; ++j)
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const float v = x[j][i]; const int id = g.a0 + 4 * (lane + 32 * j) + i;
-                const bool after = v < pv || (v == pv && id > pi);
-                if (after && v > -CUDART_INF_F && better(v, id, bv, bi)) { bv = v; bi = id; }
-            }
-        warp_pick(bv, bi);
-        if (bi == INT32_MAX) break;
-        if (lane == 0) { wb.v[r] = bv; wb.id[r] = bi; }
-        pv = bv; pi = bi; ++cnt;
-    }
-    __syncwarp();
-    run.n = cnt;
+    const int n_new = wb.n;
+    if (n_new <= kCandCap - kMaxK) { run_merge(run, wb, n_new, K); return; }
+    // ---- 5. massive ties: exact selection straight from the registers
+    run_exact<4 * kNV>(run, K, [&](int e) { return x[e >> 2][e & 3]; },
+                       [&](int e) { return g.a0 + 4 * (lane + 32 * (e >> 2)) + (e & 3); });
 }
 
 // ---- which warp of the grid owns unit u, when N units are dealt to Wt warps in contiguous runs [g N / Wt, (g+1) N / Wt)
@@ -195,29 +176,57 @@ __device__ __forceinline__ RowPartials row_partials(const StepParams& p, int row
 }
 
 // ---- row merge (one full warp): partials of the row -> K log-probs.  Lane i < K ends with candidate i.
+// Lane l takes partial l of the row's list [text partials | timestamp partials]; header and entries are fetched
+// with independent 16-byte loads up front, so the usual row (<= 32 partials) costs ONE round trip to L2.
 struct RowOut { float lp; int tok; unsigned flags; };
 
-__device__ __forceinline__ RowOut merge_row(const StepParams& p, int row, unsigned rule_flags, const RowPartials& rpz, WarpBuf& wb) {
+__device__ __noinline__ RowOut merge_row(const StepParams& p, int row, unsigned rule_flags, const RowPartials& rpz, WarpBuf& wb) {
     const int lane = threadIdx.x & 31;
-    const int K = p.K;
+    const int K = p.K, KQ = (K + 3) >> 2;
     const Partial* __restrict__ parts = p.partials + (int64_t)row * p.upr;
-    // partition maxima and sums (text = 0, timestamps = 1)
-    float M[2], S[2];
+    const int cT = rpz.count[0], cnt = rpz.count[0] + rpz.count[1];
+    auto part_of = [&](int i) { return parts + (i < cT ? rpz.base[0] + i : rpz.base[1] + (i - cT)); };
+    auto load_entries = [&](const Partial* pp, float (&ev)[kMaxK], int (&ei)[kMaxK]) {
+#pragma unroll
+        for (int q = 0; q < kMaxK / 4; ++q)
+            if (q < KQ) {
+                const float4 a = __ldcg(reinterpret_cast<const float4*>(pp->v) + q);
+                const int4 b = __ldcg(reinterpret_cast<const int4*>(pp->id) + q);
+                ev[4 * q] = a.x; ev[4 * q + 1] = a.y; ev[4 * q + 2] = a.z; ev[4 * q + 3] = a.w;
+                ei[4 * q] = b.x; ei[4 * q + 1] = b.y; ei[4 * q + 2] = b.z; ei[4 * q + 3] = b.w;
+            }
+    };
+    // round 0 in registers
+    float4 h0 = make_float4(-CUDART_INF_F, 0.0f, 0.0f, 0.0f);
+    float ev0[kMaxK]; int ei0[kMaxK];
+#pragma unroll
+    for (int e = 0; e < kMaxK; ++e) { ev0[e] = -CUDART_INF_F; ei0[e] = INT32_MAX; }
+    if (lane < cnt) {
+        const Partial* pp = part_of(lane);
+        h0 = __ldcg(reinterpret_cast<const float4*>(pp));
+        load_entries(pp, ev0, ei0);
+    }
+    // ---- pass A: partition maxima and sums (text = 0, timestamps = 1)
+    float am[2] = {-CUDART_INF_F, -CUDART_INF_F}, as[2] = {0.0f, 0.0f};
     bool nan_seen = false;
+    for (int r = 0; 32 * r < cnt; ++r) {
+        const int i = lane + 32 * r;
+        if (i < cnt) {
+            const float4 h = r == 0 ? h0 : __ldcg(reinterpret_cast<const float4*>(part_of(i)));
+            const int q = i < cT ? 0 : 1;
+            if (h.y != h.y) nan_seen = true;
+            else if (h.x > am[q]) { as[q] = as[q] * exp_diff(am[q], h.x) + h.y; am[q] = h.x; }
+            else as[q] += h.y * exp_diff(h.x, am[q]);
+        }
+    }
+    float M[2], S[2];
 #pragma unroll
     for (int q = 0; q < 2; ++q) {
-        float m = -CUDART_INF_F;
-        for (int i = lane; i < rpz.count[q]; i += 32) m = fmaxf(m, __ldcg(&parts[rpz.base[q] + i].m));
-        m = warp_max(m);
-        float s = 0.0f;
-        for (int i = lane; i < rpz.count[q]; i += 32) {
-            const float pm = __ldcg(&parts[rpz.base[q] + i].m), ps = __ldcg(&parts[rpz.base[q] + i].s);
-            if (ps != ps) nan_seen = true;
-            else s += ps * exp_diff(pm, m);
-        }
+        M[q] = warp_max(am[q]);
+        float s = as[q] * exp_diff(am[q], M[q]);
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-        M[q] = m; S[q] = s;
+        S[q] = s;
     }
     nan_seen = __any_sync(0xffffffffu, nan_seen);
     RowOut r;
@@ -234,55 +243,62 @@ __device__ __forceinline__ RowOut merge_row(const StepParams& p, int row, unsign
     const float tot = Ts * exp_diff(Tm, Mx) + Ss * exp_diff(Sm, Mx);
     const float logtot = nan_seen ? CUDART_NAN_F : logf(tot);
     if (Mx == -CUDART_INF_F) r.flags |= 128u;   // everything masked: the reference yields NaN log-probs
-    // candidates: threshold on the partials' maxima (v[0]), gather, rank-sort
-    const int q_lo = ts_over_text ? 1 : 0;
-    float lmax = -CUDART_INF_F;
-    for (int q = q_lo; q < 2; ++q)
-        for (int i = lane; i < rpz.count[q]; i += 32) lmax = fmaxf(lmax, __ldcg(&parts[rpz.base[q] + i].v[0]));
-    const float tau = kth_threshold(lmax, K);
-    if (lane == 0) wb.n = 0;
-    __syncwarp();
-    for (int q = q_lo; q < 2; ++q)
-        for (int i = lane; i < rpz.count[q]; i += 32) {
-            const Partial* pp = parts + rpz.base[q] + i;
-            const int pn = min(__ldcg(&pp->n), K);
-            for (int e = 0; e < pn; ++e) {
-                const float v = __ldcg(&pp->v[e]);
-                if (!(v >= tau) || v == -CUDART_INF_F) break;      // sorted: nothing further can qualify
-                const int pos = atomicAdd(&wb.n, 1);
-                if (pos < kCandCap) { wb.v[pos] = v; wb.id[pos] = __ldcg(&pp->id[e]); }
+    // ---- pass B: candidates of the surviving partitions (each partial's list is sorted: entry 0 is its maximum)
+    Run cand;
+    run_reset(cand);
+    for (int rr = 0; 32 * rr < cnt; ++rr) {
+        const int i = lane + 32 * rr;
+        float ev[kMaxK]; int ei[kMaxK];
+#pragma unroll
+        for (int e = 0; e < kMaxK; ++e) { ev[e] = ev0[e]; ei[e] = ei0[e]; }
+        int pn = (int)__float_as_int(h0.z);
+        if (rr > 0) {
+#pragma unroll
+            for (int e = 0; e < kMaxK; ++e) { ev[e] = -CUDART_INF_F; ei[e] = INT32_MAX; }
+            pn = 0;
+            if (i < cnt) {
+                const Partial* pp = part_of(i);
+                pn = __ldcg(&pp->n);
+                load_entries(pp, ev, ei);
             }
         }
-    __syncwarp();
-    int n = wb.n;
-    if (n <= kCandCap) n = warp_compact(wb, n, K);
-    else {
-        // massive ties across many partials: K rounds of exact selection straight from the partials
-        float pv = CUDART_INF_F; int pi = -1; n = 0;
-        for (int rr = 0; rr < K; ++rr) {
-            float bv = -CUDART_INF_F; int bi = INT32_MAX;
-            for (int q = q_lo; q < 2; ++q)
-                for (int i = lane; i < rpz.count[q]; i += 32) {
-                    const Partial* pp = parts + rpz.base[q] + i;
-                    const int pn = min(__ldcg(&pp->n), K);
-                    for (int e = 0; e < pn; ++e) {
-                        const float v = __ldcg(&pp->v[e]); const int id = __ldcg(&pp->id[e]);
-                        const bool after = v < pv || (v == pv && id > pi);
-                        if (after && v > -CUDART_INF_F && better(v, id, bv, bi)) { bv = v; bi = id; }
-                    }
+        const bool alive = i < cnt && (i >= cT || !ts_over_text);
+        pn = alive ? min(pn, K) : 0;
+#pragma unroll
+        for (int e = 0; e < kMaxK; ++e)
+            if (e >= pn) ev[e] = -CUDART_INF_F;
+        const float lmax = ev[0];
+        if (!__any_sync(0xffffffffu, lmax > -CUDART_INF_F)) continue;
+        const float tau = fmaxf(kth_threshold(lmax, K), __shfl_sync(0xffffffffu, cand.rv, K - 1));
+        if (lane == 0) wb.n = 0;
+        __syncwarp();
+        if (lmax >= tau) {
+#pragma unroll
+            for (int e = 0; e < kMaxK; ++e)
+                if (ev[e] >= tau && ev[e] > -CUDART_INF_F) {
+                    const int pos = atomicAdd(&wb.n, 1);
+                    if (pos < kCandCap - kMaxK) { wb.v[pos] = ev[e]; wb.id[pos] = ei[e]; }
                 }
-            warp_pick(bv, bi);
-            if (bi == INT32_MAX) break;
-            if (lane == 0) { wb.v[rr] = bv; wb.id[rr] = bi; }
-            pv = bv; pi = bi; ++n;
         }
         __syncwarp();
+        const int n_new = wb.n;
+        if (n_new <= kCandCap - kMaxK) run_merge(cand, wb, n_new, K);
+        else run_exact<kMaxK>(cand, K, [&](int e) { return ev[e]; }, [&](int e) { return ei[e]; });
     }
-    const float x = lane < n ? wb.v[lane] : -CUDART_INF_F;
-    r.tok = lane < n ? wb.id[lane] : INT32_MAX;
-    r.lp = (x - Mx) - logtot;
-    __syncwarp();
+    r.tok = cand.ri;
+    r.lp = (cand.rv - Mx) - logtot;
     return r;
+}
+
+
+// `completed` of a step: every group adds 1 (+ 1 << 16 when it is "done") to one word; the last group to arrive
+// publishes whether all were done and re-arms the word for the next launch.
+__device__ __forceinline__ void publish_completed(const StepParams& p, int done) {
+    const int prev = atomicAdd(p.sync, 1 + (done << 16));
+    if ((prev & 0xffff) == p.n_groups - 1) {
+        *p.completed = ((prev >> 16) + done == p.n_groups) ? 1 : 0;
+        atomicExch(p.sync, 0);
+    }
 }
 
 // per-warp tables of the beam tail (alias the WarpBuf: the warp's run has been flushed when a tail starts)
@@ -298,7 +314,7 @@ static_assert(sizeof(TailScratch) <= kScratchBytes, "tail scratch does not fit t
 static_assert(sizeof(WarpBuf) <= kScratchBytes, "candidate buffer does not fit the per-warp slice");
 
 // ---- MODE_BEAM tail: BeamSearchTokenExtractor::update for one audio (beam_search.rs:49-146), ONE warp ----
-__device__ __forceinline__ void beam_tail(const StepParams& p, int audio, TailScratch& ts) {
+__device__ __noinline__ void beam_tail_general(const StepParams& p, int audio, TailScratch& ts) {
     const int k = p.beam, K = p.K, n_c = k * K;
     const int lane = threadIdx.x & 31;
     const int row0 = audio * k;
@@ -406,18 +422,7 @@ __device__ __forceinline__ void beam_tail(const StepParams& p, int audio, TailSc
         }
     }
     // 6. completed = all audios hold max_cand finished sequences (:141-146); last audio to arrive publishes
-    if (lane == 0) {
-        const int full = (have + n_store >= p.max_cand) ? 1 : 0;
-        if (full) atomicAdd(p.sync + 1, 1);
-        __threadfence();
-        const int arrived = atomicAdd(p.sync, 1);
-        if (arrived == p.n_groups - 1) {
-            __threadfence();
-            const int nfull = atomicExch(p.sync + 1, 0);
-            *p.completed = (nfull == p.n_groups) ? 1 : 0;
-            atomicExch(p.sync, 0);
-        }
-    }
+    if (lane == 0) publish_completed(p, (have + n_store >= p.max_cand) ? 1 : 0);
     __syncwarp();
 }
 
@@ -433,15 +438,7 @@ __device__ __forceinline__ void greedy_tail(const StepParams& p, int row, const 
     p.sum_out[row] = p.sum_in[row] + (last_eot ? 0.0f : r.lp);               // :39
     dst[p.cur_len] = next;
     if (r.flags & 128u) atomicAdd(&p.status->nan_rows, 1);
-    if (next == p.eot) atomicAdd(p.sync + 1, 1);
-    __threadfence();
-    const int arrived = atomicAdd(p.sync, 1);
-    if (arrived == p.n_groups - 1) {                                         // completed: every row's new last token is EOT
-        __threadfence();
-        const int n_eot = atomicExch(p.sync + 1, 0);
-        *p.completed = (n_eot == p.n_rows) ? 1 : 0;
-        atomicExch(p.sync, 0);
-    }
+    publish_completed(p, next == p.eot ? 1 : 0);        // completed: every row's new last token is EOT
 }
 
 // ---- MODE_FILTER tail: timestamp_tokens.rs:37-96 in place for one row, one warp.  The statistics were taken on
@@ -460,6 +457,132 @@ __device__ __forceinline__ void filter_tail(const StepParams& p, int row, const 
     if (lane == 0 && p.no_timestamps >= 0 && p.no_timestamps < V) rp[p.no_timestamps] = -CUDART_INF_F;
 }
 
+// ---- MODE_BEAM tail, k * (k + 1) <= 32 (beam <= 5): one candidate per lane, everything in registers; every global
+// read the tail needs is issued up front, so it costs one round trip to L2 before the outputs are written.
+struct FastTail {
+    long long tok_stage[256];                       // the audio's k token prefixes when k * cur_len <= 256
+    double sel_score[kMaxK], fin_sc[kMaxK];
+    int sel_src[kMaxK], sel_tok[kMaxK], fin_src[kMaxK];
+};
+static_assert(sizeof(FastTail) <= kScratchBytes, "fast tail scratch does not fit the per-warp slice");
+
+__device__ __noinline__ void beam_tail_fast(const StepParams& p, int audio, FastTail& fs) {
+    const int k = p.beam, K = p.K, n_c = k * K, L = p.cur_len;
+    const int lane = threadIdx.x & 31;
+    const int row0 = audio * k;
+    const bool valid = lane < n_c;
+    const int j = valid ? lane / K : 0, i = valid ? lane - j * K : 0;
+    // ---- phase 0: every load
+    const RowResult* rr = p.rowres + row0 + j;
+    const float lp = __ldcg(&rr->lp[i]);
+    int tok = __ldcg(&rr->tok[i]);
+    const unsigned fl = __ldcg(&rr->flags), same = __ldcg(&rr->same);
+    const float sum = p.sum_in[row0 + j];
+    int have = lane == 0 ? p.fin_n[audio] : 0;
+    const bool staged = k * L <= 256;
+    long long tv[8];
+    if (staged) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            const int idx = lane + 32 * q;
+            const int jj = idx / L, t = idx - jj * L;
+            tv[q] = idx < k * L ? p.tokens[(int64_t)(row0 + jj) * p.tok_stride + t] : 0;
+        }
+    }
+    // ---- candidates: score = f64(sum_logprobs[row]) + f64(logprob)   (beam_search.rs:70-71)
+    const double score = (double)sum + (double)lp;
+    const bool nan_seen = __any_sync(0xffffffffu, valid && (fl & 128u));
+    // a later beam with the same prefix proposing the same token overwrites this map entry (:74-77)
+    bool shadowed = false;
+    if (__any_sync(0xffffffffu, valid && same != 0u)) {
+        for (int j2 = 1; j2 < k; ++j2)
+            for (int i2 = 0; i2 < K; ++i2) {
+                const int t2 = __shfl_sync(0xffffffffu, tok, j2 * K + i2);
+                if (j2 > j && ((same >> j2) & 1u) && t2 == tok) shadowed = true;
+            }
+    }
+    const int sh = (!valid || shadowed || tok == INT32_MAX) ? 1 : 0;
+    // ---- rank by (score desc, source row asc, token asc) == (score desc, lane asc); shadowed entries go last
+    long long kb = __double_as_longlong(score);
+    kb = kb < 0 ? ~kb : (kb | (long long)0x8000000000000000ull);            // order-preserving: unsigned compare
+    const unsigned long long key = (unsigned long long)kb;
+    int rank = 0;
+    for (int d = 0; d < n_c; ++d) {
+        const unsigned long long kd = __shfl_sync(0xffffffffu, key, d);
+        const int shd = __shfl_sync(0xffffffffu, sh, d);
+        const bool before = shd != sh ? shd < sh : (kd != key ? kd > key : d < lane);
+        rank += before ? 1 : 0;
+    }
+    // ---- walk (beam_search.rs:87-104): EOT-terminated -> finished, others kept until k are saved.  An entry is
+    //      visited iff fewer than k live entries precede it in sorted order.
+    const bool ok = valid && !sh;
+    const bool live = ok && tok != p.eot, fin = ok && tok == p.eot;
+    const unsigned below = (1u << rank) - 1u;
+    const unsigned live_sorted = __reduce_or_sync(0xffffffffu, live ? (1u << rank) : 0u);
+    const int live_before = __popc(live_sorted & below);
+    const bool visited = live_before < k;
+    const unsigned fin_sorted = __reduce_or_sync(0xffffffffu, (fin && visited) ? (1u << rank) : 0u);
+    const int fidx = __popc(fin_sorted & below);
+    const int nf = min(__popc(fin_sorted), kMaxBeam), saved = min(__popc(live_sorted), k);
+    if (live && visited) { fs.sel_src[live_before] = j; fs.sel_tok[live_before] = tok; fs.sel_score[live_before] = score; }
+    if (fin && visited && fidx < kMaxBeam) { fs.fin_src[fidx] = j; fs.fin_sc[fidx] = score; }
+    if (staged) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q)
+            if (lane + 32 * q < k * L) fs.tok_stage[lane + 32 * q] = tv[q];
+    }
+    // fewer than k live candidates cannot happen with >= k+1 finite logits per row; keep the row count anyway
+    if (lane >= saved && lane < k) { fs.sel_src[lane] = 0; fs.sel_tok[lane] = p.eot; fs.sel_score[lane] = -CUDART_INF; }
+    __syncwarp();
+    // finished store: append in descending score until round(patience*k) entries (:124-138)
+    have = __shfl_sync(0xffffffffu, have, 0);
+    const int n_store = min(nf, max(0, p.max_cand - have));
+    if (lane == 0) {
+        p.fin_n[audio] = have + n_store;
+        if (p.dbg_fin_count) p.dbg_fin_count[audio] = nf;
+        if (nan_seen) atomicAdd(&p.status->nan_rows, 1);
+        publish_completed(p, (have + n_store >= p.max_cand) ? 1 : 0);   // (:141-146)
+    }
+    if (lane < k) {
+        if (p.dbg_fin_source) p.dbg_fin_source[audio * k + lane] = lane < nf ? row0 + fs.fin_src[lane] : -1;
+        if (p.dbg_fin_score) p.dbg_fin_score[audio * k + lane] = lane < nf ? fs.fin_sc[lane] : 0.0;
+        p.source_idx[row0 + lane] = row0 + fs.sel_src[lane];
+        p.sum_out[row0 + lane] = (float)fs.sel_score[lane];   // index_put_(.., score as f32) :91-95
+    }
+    // ---- outputs
+    const int L1 = L + 1;
+    for (int idx = lane; idx < k * L1; idx += 32) {
+        const int r = idx / L1, t = idx - r * L1;
+        const int src = fs.sel_src[r];
+        long long v = (long long)fs.sel_tok[r];
+        if (t < L) v = staged ? fs.tok_stage[src * L + t] : p.tokens[(int64_t)(row0 + src) * p.tok_stride + t];
+        p.next_tokens[(int64_t)(row0 + r) * p.next_stride + t] = v;
+    }
+    for (int idx = lane; idx < n_store * L1; idx += 32) {
+        const int r = idx / L1, t = idx - r * L1;
+        const int slot = have + r, src = fs.fin_src[r];
+        long long v = (long long)p.eot;
+        if (t < L) v = staged ? fs.tok_stage[src * L + t] : p.tokens[(int64_t)(row0 + src) * p.tok_stride + t];
+        p.fin_tokens[((int64_t)audio * p.max_cand + slot) * p.max_len + t] = v;
+        if (t == 0) {
+            p.fin_len[audio * p.max_cand + slot] = L1;
+            p.fin_score[audio * p.max_cand + slot] = fs.fin_sc[r];
+        }
+    }
+    __syncwarp();
+}
+
+#ifdef WRS_TRACE
+// investigation aid (tools/debug/dec_trace.py): per-warp event times in ns, [warp][8]
+__device__ unsigned long long g_trace[148 * kStepWarps * 8];
+__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define WRS_TR(slot) do { if (lane == 0) g_trace[gw * 8 + (slot)] = gtime(); } while (0)
+#define WRS_TR_ADD(slot, v) do { if (lane == 0) g_trace[gw * 8 + (slot)] += (v); } while (0)
+#else
+#define WRS_TR(slot) do {} while (0)
+#define WRS_TR_ADD(slot, v) do {} while (0)
+#endif
+
 template <int MODE>
 __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const StepParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -474,6 +597,10 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const Step
     const int64_t gw = (int64_t)blockIdx.x * kStepWarps + warp;
     if (gw >= Wt) return;
     const int64_t u_begin = gw * N / Wt, u_end = (gw + 1) * N / Wt;
+#ifdef WRS_TRACE
+    if (lane == 0) for (int q = 0; q < 8; ++q) g_trace[gw * 8 + q] = 0;
+#endif
+    WRS_TR(0);
 
     // rules of the first two rows this warp touches are fetched up front (a later row change costs a bubble)
     const int row_first = (int)(u_begin / p.upr);
@@ -488,6 +615,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const Step
     int rules_row = -1;
     RowRules rules;
     rules.t_lo = rules.t_hi = rules.s_lo = rules.s_hi = 0; rules.flags = 0;
+    int abase[2] = {0, 0};                               // first 16-byte aligned id slot of the row's two partitions
 
     auto rules_for = [&](int row) {
         if (row == rules_row) return;
@@ -495,45 +623,59 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const Step
         else if (row == row_first + 1) rules = row_rules_from(p.rc, tk_last[1], tk_pen[1], p.cur_len, p.sample_begin);
         else rules = row_rules(p.rc, p.tokens + (int64_t)row * p.tok_stride, p.cur_len, p.sample_begin);
         rules_row = row;
+        const float* rp = p.logits + (int64_t)row * p.row_stride;
+        abase[0] = -(int)((reinterpret_cast<uintptr_t>(rp) >> 2) & 3);
+        abase[1] = p.ts_split - (int)((reinterpret_cast<uintptr_t>(rp + p.ts_split) >> 2) & 3);
     };
-    auto geom_of = [&](int64_t u) {
+    // unit j of row `row`: ids [a0, a0 + 896) of its partition, clipped to the partition and to the row's rules
+    auto geom_of = [&](int row, int j) {
         Geom g;
-        g.row = (int)(u / p.upr);
-        const int j = (int)(u - (int64_t)g.row * p.upr);
-        rules_for(g.row);
-        int plo, phi;
-        if (j < p.n_text_units) { g.part = 0; plo = j * kUnit; phi = min(p.ts_split, plo + kUnit); g.lo = max(plo, rules.t_lo); g.hi = min(phi, rules.t_hi); }
-        else { g.part = 1; plo = p.ts_split + (j - p.n_text_units) * kUnit; phi = min(p.rc.n_vocab, plo + kUnit); g.lo = max(plo, rules.s_lo); g.hi = min(phi, rules.s_hi); }
-        const float* rp = p.logits + (int64_t)g.row * p.row_stride;
-        const int mis = (int)((reinterpret_cast<uintptr_t>(rp + g.lo) >> 2) & 3);
-        g.a0 = g.lo - mis;
+        g.row = row;
+        rules_for(row);
+        if (j < p.n_text_units) {
+            g.part = 0; g.a0 = abase[0] + j * kUnit;
+            g.lo = max(max(g.a0, 0), rules.t_lo); g.hi = min(min(g.a0 + kUnit, p.ts_split), rules.t_hi);
+        } else {
+            g.part = 1; g.a0 = abase[1] + (j - p.n_text_units) * kUnit;
+            g.lo = max(max(g.a0, p.ts_split), rules.s_lo); g.hi = min(min(g.a0 + kUnit, p.rc.n_vocab), rules.s_hi);
+        }
         return g;
     };
-    // loads of one unit: element base of slot j is a0 + 4 (lane + 32 j); everything outside [lo, hi) reads as -inf
+    // loads of one unit: slot j of a lane holds ids a0 + 4 (lane + 32 j) ..+3; everything outside [lo, hi) reads as -inf
     auto load_unit = [&](const Geom& g, float (&x)[kNV][4], uint32_t& bmw) {
         if (g.hi <= g.lo) { bmw = 0u; return; }
         const float* __restrict__ rp = p.logits + (int64_t)g.row * p.row_stride;
+        if (g.lo == g.a0 && g.hi == g.a0 + kUnit) {      // interior unit: seven aligned 16-byte loads, no predicates
+            const float4* __restrict__ src = reinterpret_cast<const float4*>(rp + g.a0) + lane;
 #pragma unroll
-        for (int j = 0; j < kNV; ++j) {
-            const int e = g.a0 + 4 * (lane + 32 * j);
-            if (e >= g.lo && e + 3 < g.hi) {
-                const float4 q = __ldcs(reinterpret_cast<const float4*>(rp + e));
+            for (int j = 0; j < kNV; ++j) {
+                const float4 q = __ldcs(src + 32 * j);
                 x[j][0] = q.x; x[j][1] = q.y; x[j][2] = q.z; x[j][3] = q.w;
-            } else {
+            }
+        } else {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) x[j][i] = (e + i >= g.lo && e + i < g.hi) ? __ldcs(rp + e + i) : -CUDART_INF_F;
+            for (int j = 0; j < kNV; ++j) {
+                const int e = g.a0 + 4 * (lane + 32 * j);
+                if (e >= g.lo && e + 3 < g.hi) {
+                    const float4 q = __ldcs(reinterpret_cast<const float4*>(rp + e));
+                    x[j][0] = q.x; x[j][1] = q.y; x[j][2] = q.z; x[j][3] = q.w;
+                } else {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) x[j][i] = (e + i >= g.lo && e + i < g.hi) ? __ldcs(rp + e + i) : -CUDART_INF_F;
+                }
             }
         }
         const int wbase = max(g.a0, 0) >> 5;
         bmw = __ldg(p.bm + min(wbase + lane, p.bm_words - 1));
     };
 
+    int row_n = row_first, j_n = (int)(u_begin - (int64_t)row_first * p.upr);   // (row, unit-in-row) of the prefetched unit
     float xn[kNV][4];
     uint32_t bm_n = 0u;
-    Geom gn = geom_of(u_begin);
+    Geom gn = geom_of(row_n, j_n);
     load_unit(gn, xn, bm_n);
     Run run;
-    run.m = -CUDART_INF_F; run.s = 0.0f; run.n = 0;
+    run_reset(run);
 
     for (int64_t u = u_begin; u < u_end; ++u) {
         const Geom g = gn;
@@ -544,55 +686,78 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const Step
             for (int i = 0; i < 4; ++i) x[j][i] = xn[j][i];
         const uint32_t bmw = bm_n;
         const bool has_next = u + 1 < u_end;
-        if (has_next) { gn = geom_of(u + 1); load_unit(gn, xn, bm_n); }
+        if (has_next) {
+            if (++j_n == p.upr) { j_n = 0; ++row_n; }
+            gn = geom_of(row_n, j_n);
+            load_unit(gn, xn, bm_n);
+        }
         if (g.hi > g.lo) reduce_unit(x, g, bmw, max(g.a0, 0) >> 5, p.K, wb, run);
+        if (u == u_begin) WRS_TR(1);
+        WRS_TR(2);
         if (has_next && gn.row == g.row && gn.part == g.part) continue;
 
         // ---- end of a (row, partition) run: leave the partial, arrive on the row
         const RowPartials rpz = row_partials(p, g.row, Wt, N);
         Partial* out = p.partials + (int64_t)g.row * p.upr + rpz.base[g.part] + (int)(gw - rpz.first_owner[g.part]);
-        if (lane < kMaxK) {
-            out->v[lane] = lane < run.n ? wb.v[lane] : -CUDART_INF_F;
-            out->id[lane] = lane < run.n ? wb.id[lane] : INT32_MAX;
-        }
+        if (lane < kMaxK) { out->v[lane] = run.rv; out->id[lane] = run.ri; }
         if (lane == 0) { out->m = run.m; out->s = run.s; out->n = run.n; }
-        run.m = -CUDART_INF_F; run.s = 0.0f; run.n = 0;
-        __threadfence();
+        run_reset(run);
         __syncwarp();
         int last = 0;
         if (lane == 0) {
+            __threadfence();                             // cumulative: publishes the whole warp's partial (ordered by the syncwarp)
             const int expected = rpz.count[0] + rpz.count[1];
             const int prev = atomicAdd(p.row_arrive + g.row, 1);
             last = (prev == expected - 1) ? 1 : 0;
-            if (last) p.row_arrive[g.row] = 0;           // self-reset for the next launch (stream-ordered)
+            if (last) { p.row_arrive[g.row] = 0; __threadfence(); }   // self-reset for the next launch (stream-ordered)
         }
         last = __shfl_sync(0xffffffffu, last, 0);
         if (!last) continue;
-        __threadfence();
 
         // ---- this warp completed the row: merge it
         const int row = g.row;
         RowRules rr_row;
         {
-            const int keep = rules_row;                  // rules of the prefetched unit must survive
+            const int keep = rules_row, ka0 = abase[0], ka1 = abase[1];   // state of the prefetched unit must survive
             const RowRules keep_rules = rules;
             rules_for(row);
             rr_row = rules;
-            rules = keep_rules; rules_row = keep;
+            rules = keep_rules; rules_row = keep; abase[0] = ka0; abase[1] = ka1;
         }
-        unsigned same = 0u;
-        if (MODE == MODE_BEAM) {
-            // which later beams of this audio hold an identical prefix (HashMap key = whole sequence, beam_search.rs:74-77)
-            const int j = row % p.beam, rbase = row - j;
-            const int64_t* mine = p.tokens + (int64_t)row * p.tok_stride;
-            for (int j2 = j + 1; j2 < p.beam; ++j2) {
-                const int64_t* other = p.tokens + (int64_t)(rbase + j2) * p.tok_stride;
-                bool diff = false;
-                for (int t = lane; t < p.cur_len; t += 32) diff |= (mine[t] != other[t]);
-                if (!__any_sync(0xffffffffu, diff)) same |= 1u << j2;
-            }
+#ifdef WRS_TRACE
+        const unsigned long long tm0 = gtime();
+#endif
+        // which later beams of this audio hold an identical prefix (HashMap key = whole sequence, beam_search.rs:74-77):
+        // the first 32 positions of up to 4 later beams are fetched before the merge so both latencies overlap
+        const int bj = MODE == MODE_BEAM ? row % p.beam : 0, rbase = row - bj;
+        const int64_t* mine = p.tokens + (int64_t)row * p.tok_stride;
+        int64_t pre_m = 0, pre_o[4] = {0, 0, 0, 0};
+        if (MODE == MODE_BEAM && lane < p.cur_len) {
+            pre_m = mine[lane];
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                if (bj + 1 + q < p.beam) pre_o[q] = p.tokens[(int64_t)(rbase + bj + 1 + q) * p.tok_stride + lane];
         }
         const RowOut r = merge_row(p, row, rr_row.flags, rpz, wb);
+        unsigned same = 0u;
+        if (MODE == MODE_BEAM) {
+            unsigned diff = 0u;
+#pragma unroll
+            for (int q = 0; q < 4; ++q)
+                if (pre_o[q] != pre_m) diff |= 1u << (bj + 1 + q);          // lanes >= cur_len hold 0 == 0
+            for (int j2 = bj + 5; j2 < p.beam; ++j2)
+                if (lane < p.cur_len && p.tokens[(int64_t)(rbase + j2) * p.tok_stride + lane] != pre_m) diff |= 1u << j2;
+            for (int t = lane + 32; t < p.cur_len; t += 32) {
+                const int64_t mt = mine[t];
+                for (int j2 = bj + 1; j2 < p.beam; ++j2)
+                    if (p.tokens[(int64_t)(rbase + j2) * p.tok_stride + t] != mt) diff |= 1u << j2;
+            }
+            diff = __reduce_or_sync(0xffffffffu, diff);
+            same = ~diff & ((1u << p.beam) - 1u) & ~((2u << bj) - 1u);
+        }
+#ifdef WRS_TRACE
+        WRS_TR_ADD(4, gtime() - tm0); WRS_TR_ADD(5, 1);
+#endif
         if (lane < p.K) {
             if (p.dbg_lp) p.dbg_lp[(int64_t)row * p.K + lane] = r.lp;
             if (p.dbg_tok) p.dbg_tok[(int64_t)row * p.K + lane] = r.tok;
@@ -607,22 +772,29 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const Step
             RowResult* res = p.rowres + row;
             if (lane < kMaxK) { res->lp[lane] = r.lp; res->tok[lane] = lane < p.K ? r.tok : INT32_MAX; }
             if (lane == 0) { res->flags = r.flags; res->same = same; }
-            __threadfence();
             __syncwarp();
             const int audio = row / p.beam;
             int last_a = 0;
             if (lane == 0) {
+                __threadfence();
                 const int prev = atomicAdd(p.audio_arrive + audio, 1);
                 last_a = (prev == p.beam - 1) ? 1 : 0;
-                if (last_a) p.audio_arrive[audio] = 0;
+                if (last_a) { p.audio_arrive[audio] = 0; __threadfence(); }
             }
             last_a = __shfl_sync(0xffffffffu, last_a, 0);
             if (last_a) {
-                __threadfence();
-                beam_tail(p, audio, *reinterpret_cast<TailScratch*>(scratch));
+#ifdef WRS_TRACE
+                const unsigned long long tt0 = gtime();
+#endif
+                if (p.beam * p.K <= 32) beam_tail_fast(p, audio, *reinterpret_cast<FastTail*>(scratch));
+                else beam_tail_general(p, audio, *reinterpret_cast<TailScratch*>(scratch));
+#ifdef WRS_TRACE
+                WRS_TR_ADD(6, gtime() - tt0); WRS_TR_ADD(7, 1);
+#endif
             }
         }
     }
+    WRS_TR(3);
 }
 
 // ---- sparse in-place fills: logits.index_fill_(1, idx, -inf)   suppress_tokens.rs:22, suppress_blanks.rs:41
@@ -714,13 +886,20 @@ void set_debug(StepParams& p, const wrs_step_debug* dbg) {
 
 extern "C" {
 
+#ifdef WRS_TRACE
+int wrs_debug_trace_read(unsigned long long* out_host, int n) {
+    return (int)cudaMemcpyFromSymbol(out_host, wrs::g_trace, sizeof(unsigned long long) * n);
+}
+#endif
+
 int wrs_decoder_create(wrs_ctx* ctx, const wrs_decode_cfg* cfg, const int32_t* suppress_ids, int32_t n_suppress,
                        int32_t max_rows, wrs_decoder** out) {
     if (!ctx || !cfg || !out) return fail(ctx, WRS_ERR_INVALID, "wrs_decoder_create: null argument");
     *out = nullptr;
     const wrs_decode_cfg& c = *cfg;
-    if (c.n_vocab < 8 || c.beam_size < 1 || c.beam_size > kMaxBeam || max_rows < c.beam_size || max_rows % c.beam_size != 0)
-        return fail(ctx, WRS_ERR_INVALID, "wrs_decoder_create: need n_vocab >= 8, 1 <= beam_size <= 15, max_rows a multiple of beam_size");
+    if (c.n_vocab < 8 || c.beam_size < 1 || c.beam_size > kMaxBeam || max_rows < c.beam_size || max_rows % c.beam_size != 0 ||
+        max_rows >= 32768)
+        return fail(ctx, WRS_ERR_INVALID, "wrs_decoder_create: need n_vocab >= 8, 1 <= beam_size <= 15, max_rows a multiple of beam_size below 32768");
     if (c.eot < 0 || c.eot >= c.n_vocab || (c.timestamps && (c.ts_begin <= c.eot || c.ts_begin > c.n_vocab ||
                                                               c.no_timestamps < 0 || c.no_timestamps >= c.n_vocab)))
         return fail(ctx, WRS_ERR_INVALID, "wrs_decoder_create: need 0 <= eot < ts_begin <= n_vocab and a valid no_timestamps id");
@@ -732,8 +911,9 @@ int wrs_decoder_create(wrs_ctx* ctx, const wrs_decode_cfg* cfg, const int32_t* s
     d->max_cand = std::max(1, (int)std::round(c.patience * (float)c.beam_size));   // f32::round, beam_search.rs:122
     // unit geometry: text ids [0, ts_split) and timestamp ids [ts_split, V) never share a unit
     d->ts_split = c.timestamps ? c.ts_begin : c.n_vocab;
-    d->n_text_units = (d->ts_split + kUnit - 1) / kUnit;
-    d->n_ts_units = (c.n_vocab - d->ts_split + kUnit - 1) / kUnit;
+    // units start on 16-byte boundaries of a row's memory: up to 3 slack ids in front of a partition
+    d->n_text_units = (d->ts_split + 3 + kUnit - 1) / kUnit;
+    d->n_ts_units = c.n_vocab > d->ts_split ? (c.n_vocab - d->ts_split + 3 + kUnit - 1) / kUnit : 0;
     d->upr = d->n_text_units + d->n_ts_units;
     d->bm_words = (c.n_vocab + 31) / 32 + 2;
     std::vector<uint32_t> base(d->bm_words, 0u), first, ts(d->bm_words, 0u);

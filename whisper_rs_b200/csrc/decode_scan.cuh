@@ -4,8 +4,9 @@
 // (index_fill_, slice fill_, log_softmax, logsumexp, max) and src/decode/extractor/beam_search.rs:37,62-65
 // (log_softmax, topk) with one read of the row: masks are predicates, never written back.
 //
-// A row is cut into UNITS of 892 token ids (57 text units + 2 timestamp units for V = 51865; a unit never
-// straddles ts_begin).  A warp owns a contiguous run of units: it keeps the unit being reduced and the next
+// A row is cut into UNITS of 896 elements that start on 16-byte boundaries of the row's memory (57 text units +
+// 2 timestamp units for V = 51865; a unit never straddles ts_begin, the first and last unit of a partition are
+// ragged).  A warp owns a contiguous run of units: it keeps the unit being reduced and the next
 // one (already in flight) in registers, 7 x 16-byte loads per lane each, and folds every unit into the run's
 // {max, sum exp(x - max), top-K}.  Top-K is threshold based: K rounds of redux.max over the lane maxima give
 // a value that at least K elements reach, so only the handful of elements at or above it are gathered
@@ -23,8 +24,7 @@ namespace wrs {
 constexpr int kStepThreads = 512;
 constexpr int kStepWarps = kStepThreads / 32;
 constexpr int kNV = 7;                                   // float4 slots per lane per unit
-constexpr int kUnitSpan = 32 * 4 * kNV;                  // 896 elements loaded per unit
-constexpr int kUnit = kUnitSpan - 4;                     // 892 ids per unit (3 = worst-case alignment slack)
+constexpr int kUnit = 32 * 4 * kNV;                      // 896 elements per unit, 16-byte aligned in memory
 constexpr int kMaxK = 16;                                // beam + 1 <= 16
 constexpr int kCandCap = 128;                            // gathered candidates per warp before the exact fallback
 constexpr float kLog2e = 1.4426950408889634f;
@@ -139,6 +139,69 @@ __device__ __forceinline__ void warp_pick(float& bv, int& bi) {
         const float v2 = __shfl_xor_sync(0xffffffffu, bv, o); const int i2 = __shfl_xor_sync(0xffffffffu, bi, o);
         if (better(v2, i2, bv, bi)) { bv = v2; bi = i2; }
     }
+}
+
+// The running statistics of the (row, partition) run a warp is reducing.  Lane r < n holds the run's r-th best
+// candidate (rv, ri) in (value desc, id asc) order; other lanes hold (-inf, INT32_MAX).
+struct Run { float m, s, rv; int ri, n; };
+
+__device__ __forceinline__ void run_reset(Run& run) {
+    run.m = -CUDART_INF_F; run.s = 0.0f; run.rv = -CUDART_INF_F; run.ri = INT32_MAX; run.n = 0;
+}
+
+// Merge the n_new gathered candidates wb[0, n_new) into the run's list, keeping the best K.
+__device__ __forceinline__ void run_merge(Run& run, WarpBuf& wb, int n_new, int K) {
+    const int lane = threadIdx.x & 31;
+    if (n_new + K <= 32) {
+        // one entry per lane: the old list on lanes [0, K), the new candidates on lanes [K, K + n_new)
+        float cv = run.rv; int ci = run.ri;
+        if (lane >= K) {
+            const int e = lane - K;
+            cv = e < n_new ? wb.v[e] : -CUDART_INF_F; ci = e < n_new ? wb.id[e] : INT32_MAX;
+        }
+        float nv = -CUDART_INF_F; int ni = INT32_MAX, cnt = 0;
+        for (int r = 0; r < K; ++r) {
+            const float m = warp_max(cv);
+            if (m == -CUDART_INF_F) break;
+            const int w = __reduce_min_sync(0xffffffffu, cv == m ? ci : INT32_MAX);
+            if (cv == m && ci == w) cv = -CUDART_INF_F;
+            if (lane == r) { nv = m; ni = w; }
+            ++cnt;
+        }
+        run.rv = nv; run.ri = ni; run.n = cnt;
+        __syncwarp();
+        return;
+    }
+    // many candidates: rank-sort in shared memory (the old list is appended behind the new candidates)
+    if (lane < run.n) { wb.v[n_new + lane] = run.rv; wb.id[n_new + lane] = run.ri; }
+    __syncwarp();
+    const int n = warp_compact(wb, n_new + run.n, K);
+    run.rv = lane < n ? wb.v[lane] : -CUDART_INF_F; run.ri = lane < n ? wb.id[lane] : INT32_MAX; run.n = n;
+    __syncwarp();
+}
+
+// Exact fallback for massive ties: K rounds of warp-wide selection over {run list} U {the lane's NE elements}, each
+// strictly after the previous pick.  `val(e)` / `idx(e)` give the lane's e-th element (-inf = absent).
+template <int NE, class Val, class Idx>
+__device__ __forceinline__ void run_exact(Run& run, int K, Val val, Idx idx) {
+    const int lane = threadIdx.x & 31;
+    const float ov = run.rv; const int oi = run.ri;
+    float pv = CUDART_INF_F, nv = -CUDART_INF_F; int pi = -1, ni = INT32_MAX, cnt = 0;
+    for (int r = 0; r < K; ++r) {
+        float bv = -CUDART_INF_F; int bi = INT32_MAX;
+        if ((ov < pv || (ov == pv && oi > pi)) && ov > -CUDART_INF_F) { bv = ov; bi = oi; }
+#pragma unroll
+        for (int e = 0; e < NE; ++e) {
+            const float v = val(e); const int id = idx(e);
+            const bool after = v < pv || (v == pv && id > pi);
+            if (after && v > -CUDART_INF_F && better(v, id, bv, bi)) { bv = v; bi = id; }
+        }
+        warp_pick(bv, bi);
+        if (bi == INT32_MAX) break;
+        if (lane == r) { nv = bv; ni = bi; }
+        pv = bv; pi = bi; ++cnt;
+    }
+    run.rv = nv; run.ri = ni; run.n = cnt;
 }
 
 }  // namespace wrs
