@@ -49,7 +49,9 @@ namespace wrs {
 enum { MODE_BEAM = 0, MODE_GREEDY = 1, MODE_FILTER = 2 };
 constexpr int kMaxBeam = 15;
 constexpr int kMaxCandAudio = kMaxBeam * kMaxK;          // 240
-constexpr int kScratchBytes = 4608;                      // per-warp shared scratch (WarpBuf, or the beam tail's tables)
+constexpr int kStageBytes = kUnit * 4;                    // per-warp landing zone of the unit in flight (cp.async)
+constexpr int kScratchBytes = 2688;                      // per-warp scratch behind it (WarpBuf, or the fast beam tail's tables)
+constexpr int kWarpSmem = kStageBytes + kScratchBytes;   // the general beam tail (beam > 5) takes the whole slice
 
 // what the row merge leaves for the audio-level tail
 struct __align__(16) RowResult {
@@ -109,52 +111,72 @@ __device__ __forceinline__ void reduce_unit(float (&x)[kNV][4], const Geom& g, u
             }
         }
     }
-    // ---- 2. lane max, warp max, sum of exp(x - warp max)
+    // ---- 2. lane max; exp-sum against the run's reference (no cross-lane traffic unless the reference moves)
     float tmax = -CUDART_INF_F;
 #pragma unroll
-    for (int j = 0; j < kNV; ++j)
-#pragma unroll
-        for (int i = 0; i < 4; ++i) tmax = fmaxf(tmax, x[j][i]);
-    const float wmax = warp_max(tmax);
-    const float ref = (wmax == -CUDART_INF_F) ? 0.0f : wmax;
-    const float nref = -ref * kLog2e;
-    float s0 = 0.0f, s1 = 0.0f;
-#pragma unroll
-    for (int j = 0; j < kNV; ++j) {
-        s0 += ex2(fmaf(x[j][0], kLog2e, nref)) + ex2(fmaf(x[j][1], kLog2e, nref));   // NaN inputs keep the sum NaN
-        s1 += ex2(fmaf(x[j][2], kLog2e, nref)) + ex2(fmaf(x[j][3], kLog2e, nref));
+    for (int j = 0; j < kNV; ++j) tmax = fmaxf(tmax, fmaxf(fmaxf(x[j][0], x[j][1]), fmaxf(x[j][2], x[j][3])));
+    run.lm = fmaxf(run.lm, tmax);
+    if (!run.ref_set || __any_sync(0xffffffffu, tmax > run.ref + 64.0f)) {
+        const float wm = warp_max(tmax);
+        if (wm > -CUDART_INF_F) {
+            if (run.ref_set) run.ls *= ex2((run.ref - wm) * kLog2e);
+            run.ref = wm; run.ref_set = true;
+        }
     }
-    float ssum = s0 + s1;
+    {
+        const float nref = -run.ref * kLog2e;
+        float s0 = 0.0f, s1 = 0.0f;
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) ssum += __shfl_xor_sync(0xffffffffu, ssum, o);
-    if (ssum != ssum) run.s = ssum;                      // keep NaN visible
-    else if (wmax > run.m) { run.s = run.s * exp_diff(run.m, wmax) + ssum; run.m = wmax; }
-    else if (wmax > -CUDART_INF_F) run.s += ssum * ex2((wmax - run.m) * kLog2e);
-    if (wmax == -CUDART_INF_F) return;                   // nothing finite in this unit
-    // ---- 3. threshold: at least K elements of the unit reach tau_u; nothing below the run's K-th best can matter
-    const float tau_u = kth_threshold(tmax, K);
-    const float tau_r = __shfl_sync(0xffffffffu, run.rv, K - 1);     // -inf while the run holds fewer than K
-    const float tau = fmaxf(tau_u, tau_r);
-    if (!__any_sync(0xffffffffu, tmax >= tau)) return;
+        for (int j = 0; j < kNV; ++j) {
+            s0 += ex2(fmaf(x[j][0], kLog2e, nref)) + ex2(fmaf(x[j][1], kLog2e, nref));   // NaN inputs keep the sum NaN
+            s1 += ex2(fmaf(x[j][2], kLog2e, nref)) + ex2(fmaf(x[j][3], kLog2e, nref));
+        }
+        run.ls += s0 + s1;
+    }
+    // ---- 3. top-K: gather everything that reaches tau, a value the run's K-th best is known to reach
+    if (run.tau == -CUDART_INF_F) run.tau = kth_threshold(tmax, K);      // at least K elements of this unit reach it
+    const float tau = run.tau;
+    const bool mine = tmax >= tau && tmax > -CUDART_INF_F;
+    if (!__any_sync(0xffffffffu, mine)) return;
+    const int np0 = run.np;
+    if (mine) {
+#pragma unroll
+        for (int j = 0; j < kNV; ++j) {
+            if (fmaxf(fmaxf(x[j][0], x[j][1]), fmaxf(x[j][2], x[j][3])) >= tau) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    if (x[j][i] >= tau && x[j][i] > -CUDART_INF_F) {
+                        const int pos = atomicAdd(&wb.n, 1);
+                        if (pos < kCandCap - kMaxK) { wb.v[pos] = x[j][i]; wb.id[pos] = g.a0 + 4 * (lane + 32 * j) + i; }
+                    }
+            }
+        }
+    }
+    __syncwarp();
+    const int n_tot = wb.n;
+    if (n_tot <= kCandCap / 2) { run.np = n_tot; return; }
+    if (n_tot <= kCandCap - kMaxK) run_merge(run, wb, n_tot, K);
+    else {
+        // massive ties: merge what was pending before this unit, then select exactly straight from the registers
+        run_merge(run, wb, np0, K);
+        run_exact<4 * kNV>(run, K, [&](int e) { return x[e >> 2][e & 3]; },
+                           [&](int e) { return g.a0 + 4 * (lane + 32 * (e >> 2)) + (e & 3); });
+    }
+    run.np = 0;
     if (lane == 0) wb.n = 0;
+    run.tau = fmaxf(run.tau, __shfl_sync(0xffffffffu, run.rv, K - 1));   // -inf while the list holds fewer than K
     __syncwarp();
-    // ---- 4. gather everything at or above the threshold
-    if (tmax >= tau) {
+}
+
+// End of a run: merge the pending candidates and turn the lane-local statistics into {max, sum exp(x - max)}.
+__device__ __forceinline__ void run_finish(Run& run, WarpBuf& wb, int K) {
+    if (run.np > 0) run_merge(run, wb, run.np, K);
+    run.np = 0;
+    run.m = warp_max(run.lm);
+    float s = run.ls;
 #pragma unroll
-        for (int j = 0; j < kNV; ++j)
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-                if (x[j][i] >= tau && x[j][i] > -CUDART_INF_F) {
-                    const int pos = atomicAdd(&wb.n, 1);
-                    if (pos < kCandCap - kMaxK) { wb.v[pos] = x[j][i]; wb.id[pos] = g.a0 + 4 * (lane + 32 * j) + i; }
-                }
-    }
-    __syncwarp();
-    const int n_new = wb.n;
-    if (n_new <= kCandCap - kMaxK) { run_merge(run, wb, n_new, K); return; }
-    // ---- 5. massive ties: exact selection straight from the registers
-    run_exact<4 * kNV>(run, K, [&](int e) { return x[e >> 2][e & 3]; },
-                       [&](int e) { return g.a0 + 4 * (lane + 32 * (e >> 2)) + (e & 3); });
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    run.s = (s != s) ? s : s * exp_diff(run.ref_set ? run.ref : -CUDART_INF_F, run.m);   // the reference is a seen maximum: ref <= m
 }
 
 // ---- which warp of the grid owns unit u, when N units are dealt to Wt warps in contiguous runs [g N / Wt, (g+1) N / Wt)
@@ -180,12 +202,20 @@ __device__ __forceinline__ RowPartials row_partials(const StepParams& p, int row
 // with independent 16-byte loads up front, so the usual row (<= 32 partials) costs ONE round trip to L2.
 struct RowOut { float lp; int tok; unsigned flags; };
 
-__device__ __noinline__ RowOut merge_row(const StepParams& p, int row, unsigned rule_flags, const RowPartials& rpz, WarpBuf& wb) {
+__device__ __noinline__ RowOut merge_row(const StepParams& p, int row, unsigned rule_flags, const RowPartials& rpz, int64_t Wt,
+                                         int64_t N, WarpBuf& wb) {
     const int lane = threadIdx.x & 31;
     const int K = p.K, KQ = (K + 3) >> 2;
     const Partial* __restrict__ parts = p.partials + (int64_t)row * p.upr;
     const int cT = rpz.count[0], cnt = rpz.count[0] + rpz.count[1];
-    auto part_of = [&](int i) { return parts + (i < cT ? rpz.base[0] + i : rpz.base[1] + (i - cT)); };
+    // partial i of the list [text partials | timestamp partials] sits in the slot of its run's first unit: the first
+    // unit of the owning warp's range, or the partition's first unit if the range starts before it
+    auto part_of = [&](int i) {
+        const int q = i < cT ? 0 : 1;
+        const int64_t g = rpz.first_owner[q] + (q ? i - cT : i);
+        const int64_t j = g * N / Wt - (int64_t)row * p.upr;
+        return parts + (int)max(j, (int64_t)rpz.base[q]);
+    };
     auto load_entries = [&](const Partial* pp, float (&ev)[kMaxK], int (&ei)[kMaxK]) {
 #pragma unroll
         for (int q = 0; q < kMaxK / 4; ++q)
@@ -310,7 +340,7 @@ struct TailScratch {
     double sel_score[kMaxBeam], fin_sc[kMaxBeam];
     int sel_src[kMaxBeam], sel_tok[kMaxBeam], fin_src[kMaxBeam];
 };
-static_assert(sizeof(TailScratch) <= kScratchBytes, "tail scratch does not fit the per-warp slice");
+static_assert(sizeof(TailScratch) <= kWarpSmem, "tail scratch does not fit the per-warp slice");
 static_assert(sizeof(WarpBuf) <= kScratchBytes, "candidate buffer does not fit the per-warp slice");
 
 // ---- MODE_BEAM tail: BeamSearchTokenExtractor::update for one audio (beam_search.rs:49-146), ONE warp ----
@@ -587,7 +617,9 @@ template <int MODE>
 __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const StepParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    unsigned char* scratch = smem_raw + warp * kScratchBytes;
+    unsigned char* slice = smem_raw + warp * kWarpSmem;
+    float4* stage = reinterpret_cast<float4*>(slice);
+    unsigned char* scratch = slice + kStageBytes;
     WarpBuf& wb = *reinterpret_cast<WarpBuf*>(scratch);
 
     // N units are dealt to the first Wt = min(warps of the grid, N) warps: every active warp owns >= 1 unit, so the
@@ -641,18 +673,35 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const Step
         }
         return g;
     };
-    // loads of one unit: slot j of a lane holds ids a0 + 4 (lane + 32 j) ..+3; everything outside [lo, hi) reads as -inf
-    auto load_unit = [&](const Geom& g, float (&x)[kNV][4], uint32_t& bmw) {
-        if (g.hi <= g.lo) { bmw = 0u; return; }
-        const float* __restrict__ rp = p.logits + (int64_t)g.row * p.row_stride;
-        if (g.lo == g.a0 && g.hi == g.a0 + kUnit) {      // interior unit: seven aligned 16-byte loads, no predicates
-            const float4* __restrict__ src = reinterpret_cast<const float4*>(rp + g.a0) + lane;
+    auto interior = [](const Geom& g) { return g.lo == g.a0 && g.hi == g.a0 + kUnit; };
+    // start the flight of a unit: an interior unit goes to the warp's stage with seven 16-byte cp.async per lane (every
+    // lane later reads back exactly what it copied); a ragged or clipped unit is loaded directly when its turn comes
+    auto prefetch = [&](const Geom& g, uint32_t& bmw) {
+        bmw = 0u;
+        if (g.hi <= g.lo) return;
+        if (interior(g)) {
+            const float* src = p.logits + (int64_t)g.row * p.row_stride + g.a0 + 4 * lane;
+            const unsigned dst = (unsigned)__cvta_generic_to_shared(stage + lane);
+#pragma unroll
+            for (int j = 0; j < kNV; ++j)
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst + 512u * j), "l"(src + 128 * j) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        const int wbase = max(g.a0, 0) >> 5;
+        bmw = __ldg(p.bm + min(wbase + lane, p.bm_words - 1));
+    };
+    // bring the current unit into registers; slot j of a lane holds ids a0 + 4 (lane + 32 j) ..+3, everything outside
+    // [lo, hi) reads as -inf
+    auto fetch = [&](const Geom& g, float (&x)[kNV][4]) {
+        if (interior(g)) {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
 #pragma unroll
             for (int j = 0; j < kNV; ++j) {
-                const float4 q = __ldcs(src + 32 * j);
+                const float4 q = stage[lane + 32 * j];
                 x[j][0] = q.x; x[j][1] = q.y; x[j][2] = q.z; x[j][3] = q.w;
             }
         } else {
+            const float* __restrict__ rp = p.logits + (int64_t)g.row * p.row_stride;
 #pragma unroll
             for (int j = 0; j < kNV; ++j) {
                 const int e = g.a0 + 4 * (lane + 32 * j);
@@ -665,50 +714,54 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const Step
                 }
             }
         }
-        const int wbase = max(g.a0, 0) >> 5;
-        bmw = __ldg(p.bm + min(wbase + lane, p.bm_words - 1));
     };
 
-    int row_n = row_first, j_n = (int)(u_begin - (int64_t)row_first * p.upr);   // (row, unit-in-row) of the prefetched unit
-    float xn[kNV][4];
+    int row_n = row_first, j_n = (int)(u_begin - (int64_t)row_first * p.upr);   // (row, unit-in-row) of the unit in flight
     uint32_t bm_n = 0u;
     Geom gn = geom_of(row_n, j_n);
-    load_unit(gn, xn, bm_n);
+    prefetch(gn, bm_n);
     Run run;
     run_reset(run);
+    int run_j0 = j_n, run_units = 0;                     // first unit-in-row and unit count of the current run
 
     for (int64_t u = u_begin; u < u_end; ++u) {
         const Geom g = gn;
-        float x[kNV][4];
-#pragma unroll
-        for (int j = 0; j < kNV; ++j)
-#pragma unroll
-            for (int i = 0; i < 4; ++i) x[j][i] = xn[j][i];
         const uint32_t bmw = bm_n;
         const bool has_next = u + 1 < u_end;
-        if (has_next) {
-            if (++j_n == p.upr) { j_n = 0; ++row_n; }
-            gn = geom_of(row_n, j_n);
-            load_unit(gn, xn, bm_n);
+        {
+            float x[kNV][4];
+            if (g.hi > g.lo) fetch(g, x);
+            __syncwarp();
+            if (has_next) {
+                if (++j_n == p.upr) { j_n = 0; ++row_n; }
+                gn = geom_of(row_n, j_n);
+                prefetch(gn, bm_n);
+            }
+            if (run_units == 0) {                        // a run starts with an empty pending list (merges and tails share wb)
+                if (lane == 0) wb.n = 0;
+                __syncwarp();
+            }
+            if (g.hi > g.lo) reduce_unit(x, g, bmw, max(g.a0, 0) >> 5, p.K, wb, run);
         }
-        if (g.hi > g.lo) reduce_unit(x, g, bmw, max(g.a0, 0) >> 5, p.K, wb, run);
+        ++run_units;
         if (u == u_begin) WRS_TR(1);
         WRS_TR(2);
         if (has_next && gn.row == g.row && gn.part == g.part) continue;
 
-        // ---- end of a (row, partition) run: leave the partial, arrive on the row
-        const RowPartials rpz = row_partials(p, g.row, Wt, N);
-        Partial* out = p.partials + (int64_t)g.row * p.upr + rpz.base[g.part] + (int)(gw - rpz.first_owner[g.part]);
+        // ---- end of a (row, partition) run: leave the partial in the slot of the run's first unit, arrive on the row
+        run_finish(run, wb, p.K);
+        Partial* out = p.partials + (int64_t)g.row * p.upr + run_j0;
         if (lane < kMaxK) { out->v[lane] = run.rv; out->id[lane] = run.ri; }
         if (lane == 0) { out->m = run.m; out->s = run.s; out->n = run.n; }
+        const int units_done = run_units;
         run_reset(run);
+        run_j0 = j_n; run_units = 0;
         __syncwarp();
         int last = 0;
         if (lane == 0) {
             __threadfence();                             // cumulative: publishes the whole warp's partial (ordered by the syncwarp)
-            const int expected = rpz.count[0] + rpz.count[1];
-            const int prev = atomicAdd(p.row_arrive + g.row, 1);
-            last = (prev == expected - 1) ? 1 : 0;
+            const int prev = atomicAdd(p.row_arrive + g.row, units_done);
+            last = (prev + units_done == p.upr) ? 1 : 0;  // every unit of the row has been folded into some partial
             if (last) { p.row_arrive[g.row] = 0; __threadfence(); }   // self-reset for the next launch (stream-ordered)
         }
         last = __shfl_sync(0xffffffffu, last, 0);
@@ -716,6 +769,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const Step
 
         // ---- this warp completed the row: merge it
         const int row = g.row;
+        const RowPartials rpz = row_partials(p, row, Wt, N);
         RowRules rr_row;
         {
             const int keep = rules_row, ka0 = abase[0], ka1 = abase[1];   // state of the prefetched unit must survive
@@ -738,7 +792,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const Step
             for (int q = 0; q < 4; ++q)
                 if (bj + 1 + q < p.beam) pre_o[q] = p.tokens[(int64_t)(rbase + bj + 1 + q) * p.tok_stride + lane];
         }
-        const RowOut r = merge_row(p, row, rr_row.flags, rpz, wb);
+        const RowOut r = merge_row(p, row, rr_row.flags, rpz, Wt, N, wb);
         unsigned same = 0u;
         if (MODE == MODE_BEAM) {
             unsigned diff = 0u;
@@ -787,7 +841,13 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const Step
                 const unsigned long long tt0 = gtime();
 #endif
                 if (p.beam * p.K <= 32) beam_tail_fast(p, audio, *reinterpret_cast<FastTail*>(scratch));
-                else beam_tail_general(p, audio, *reinterpret_cast<TailScratch*>(scratch));
+                else {
+                    asm volatile("cp.async.wait_group 0;" ::: "memory");     // the tables overlay the stage
+                    __syncwarp();
+                    beam_tail_general(p, audio, *reinterpret_cast<TailScratch*>(slice));
+                    __syncwarp();
+                    if (has_next) prefetch(gn, bm_n);
+                }
 #ifdef WRS_TRACE
                 WRS_TR_ADD(6, gtime() - tt0); WRS_TR_ADD(7, 1);
 #endif
@@ -862,7 +922,7 @@ StepParams step_params(wrs_decoder* dec, const float* logits, int64_t row_stride
 template <int MODE>
 int launch_step(wrs_decoder* dec, const StepParams& p, cudaStream_t stream) {
     wrs_ctx* ctx = dec->ctx;
-    const size_t smem = (size_t)kStepWarps * kScratchBytes;
+    const size_t smem = (size_t)kStepWarps * kWarpSmem;
     if (!dec->smem_attr_set) {
         WRS_CUDA(ctx, cudaFuncSetAttribute(decode_step_kernel<MODE_BEAM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         WRS_CUDA(ctx, cudaFuncSetAttribute(decode_step_kernel<MODE_GREEDY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

@@ -6,9 +6,9 @@
 //
 // A row is cut into UNITS of 896 elements that start on 16-byte boundaries of the row's memory (57 text units +
 // 2 timestamp units for V = 51865; a unit never straddles ts_begin, the first and last unit of a partition are
-// ragged).  A warp owns a contiguous run of units: it keeps the unit being reduced and the next
-// one (already in flight) in registers, 7 x 16-byte loads per lane each, and folds every unit into the run's
-// {max, sum exp(x - max), top-K}.  Top-K is threshold based: K rounds of redux.max over the lane maxima give
+// ragged).  A warp owns a contiguous run of units: the unit being reduced sits in registers (7 x 16 bytes per
+// lane) while the next one is in flight into the warp's shared-memory stage (cp.async); every unit is folded into
+// the run's {max, sum exp(x - ref), top-K}.  Top-K is threshold based: K rounds of redux.max over the lane maxima give
 // a value that at least K elements reach, so only the handful of elements at or above it are gathered
 // (shared memory, per warp) and rank-sorted.  No block-level barrier is used anywhere.
 //
@@ -21,8 +21,8 @@
 
 namespace wrs {
 
-constexpr int kStepThreads = 512;
-constexpr int kStepWarps = kStepThreads / 32;
+constexpr int kStepWarps = 16;                           // one 512-thread CTA per SM, up to 128 registers per thread
+constexpr int kStepThreads = kStepWarps * 32;
 constexpr int kNV = 7;                                   // float4 slots per lane per unit
 constexpr int kUnit = 32 * 4 * kNV;                      // 896 elements per unit, 16-byte aligned in memory
 constexpr int kMaxK = 16;                                // beam + 1 <= 16
@@ -141,12 +141,17 @@ __device__ __forceinline__ void warp_pick(float& bv, int& bi) {
     }
 }
 
-// The running statistics of the (row, partition) run a warp is reducing.  Lane r < n holds the run's r-th best
-// candidate (rv, ri) in (value desc, id asc) order; other lanes hold (-inf, INT32_MAX).
-struct Run { float m, s, rv; int ri, n; };
+// The running statistics of the (row, partition) run a warp is reducing.
+//   softmax: every lane sums exp(x - ref) for its own elements against a reference fixed by the run's first unit
+//            (re-based only if a later unit tops it by more than 64), so a unit costs no cross-lane traffic;
+//   top-K:   lane r < n holds the run's r-th best candidate (rv, ri) in (value desc, id asc) order, other lanes hold
+//            (-inf, INT32_MAX); wb[0, np) holds gathered candidates not merged yet; tau is a value the run's K-th best
+//            is known to reach (-inf while unknown).
+struct Run { float ref, ls, lm, tau, rv, m, s; int ri, n, np; bool ref_set; };
 
 __device__ __forceinline__ void run_reset(Run& run) {
-    run.m = -CUDART_INF_F; run.s = 0.0f; run.rv = -CUDART_INF_F; run.ri = INT32_MAX; run.n = 0;
+    run.ref = 0.0f; run.ls = 0.0f; run.lm = -CUDART_INF_F; run.tau = -CUDART_INF_F; run.ref_set = false;
+    run.m = -CUDART_INF_F; run.s = 0.0f; run.rv = -CUDART_INF_F; run.ri = INT32_MAX; run.n = 0; run.np = 0;
 }
 
 // Merge the n_new gathered candidates wb[0, n_new) into the run's list, keeping the best K.
