@@ -51,17 +51,22 @@ void mel_filter_slaney(float* out) {
 }
 
 bool build_mel_bank(const float* dense, MelBank* bank) {
-    int total = 0;
+    int total = 0, total4 = 0;
+    for (int i = 0; i < 2 * MelBank::kMaxPadded; ++i) bank->w2[i] = 0.0f;
     for (int m = 0; m < WRS_N_MELS; ++m) {
         int lo = -1, hi = -1;
         for (int k = 0; k < WRS_N_BINS; ++k)
             if (dense[m * WRS_N_BINS + k] != 0.0f) { if (lo < 0) lo = k; hi = k; }
         if (lo < 0) { lo = 0; hi = -1; }
-        const int n = hi - lo + 1;
-        if (total + n > MelBank::kMaxWeights) return false;
+        const int n = hi - lo + 1, n4 = (n + 3) & ~3;
+        if (total + n > MelBank::kMaxWeights || total4 + n4 > MelBank::kMaxPadded) return false;
         bank->lo[m] = lo; bank->n[m] = n; bank->off[m] = total;
-        for (int j = 0; j < n; ++j) bank->w[total + j] = dense[m * WRS_N_BINS + lo + j];
-        total += n;
+        bank->n4[m] = n4; bank->off4[m] = total4;
+        for (int j = 0; j < n; ++j) {
+            bank->w[total + j] = dense[m * WRS_N_BINS + lo + j];
+            bank->w2[2 * (total4 + j)] = bank->w2[2 * (total4 + j) + 1] = bank->w[total + j];
+        }
+        total += n; total4 += n4;
     }
     bank->total = total;
     return true;

@@ -1,18 +1,22 @@
 // K1: fused log-mel front-end for batches of audio segments (sm_100a).
 //
 // Replaces the ATen op sequence of reference src/audio.rs:230-259 (hann_window, stft, abs, pow, matmul,
-// clamp_min, log10, max, maximum, add, div) with one persistent kernel:
+// clamp_min, log10, max, maximum, add, div) with one persistent kernel.  A CTA (16 warps) takes slices of 64
+// frames; every lane works on TWO frames (f0 + lane, f0 + 32 + lane) held side by side in 64-bit register pairs,
+// so the whole FFT runs on Blackwell's packed FP32 instructions (FADD2 / FMUL2 / FFMA2: one issue slot, two frames):
 //
 //   PCM (HBM) --LDG.128--> smem, transposed [sample mod 160][frame row]     (conflict-free, lane = frame)
-//   stage A  warp t : 32 frames x real 25-point DFT + W400^{tq}       -> smem Y[t][q][lane]
-//   stage B  warp q : 32 frames x complex 16-point DFT, |X|^2         -> smem P[bin][lane]
-//   stage C  warp w : 32 frames x 5 mel rows (banded FP32 FMA), log10 -> smem tile[mel][frame]
-//   slice end       : block max -> atomicMax per segment; wait for the segment's other slices
-//                     (co-resident CTAs, bounded spin); floor (max-8), (x+4)/4, float4 stores.
+//   stage A  warp t : 64 frames x real 25-point DFT + W400^{tq}       -> smem Y[t][q][lane]   (float4: re2, im2)
+//   stage B  warp q : 64 frames x complex 16-point DFT, |X|^2         -> smem P[bin][lane]    (float2)
+//            warps 13..15 meanwhile stage the NEXT slice's PCM (the tile is free once stage A is done)
+//   stage C  warp w : 64 frames x 5 mel rows (banded FP32 FMA), log10 -> smem tile[mel][frame]
+//   slice end       : raw log-mel -> HBM, block max -> atomicMax per segment, arrival count per segment
+//   one slice later : the segment's max is known (all its slices have arrived): floor (max-8), (x+4)/4 applied in
+//                     place on the slice's own 20 KB (still in L2)
 //
-// Within a warp every lane works on a different frame and the same (t | q | mel): window values,
-// twiddles and filter weights are warp-uniform (constant bank / smem broadcast) and no lane ever reads
-// another lane's column of Y or P.
+// Within a warp every lane works on different frames and the same (t | q | mel): window values, twiddles and
+// filter weights are warp-uniform (constant bank / broadcast loads) and no lane ever reads another lane's
+// column of Y or P.
 #include <algorithm>
 #include <cmath>
 
@@ -23,15 +27,16 @@ namespace wrs {
 
 constexpr int kThreads = 512;
 constexpr int kWarps = kThreads / 32;
-constexpr int kNFP = 37;            // padded row count of the transposed PCM tile (== 5 mod 8 -> conflict-free stores)
-constexpr int kRows = 35;           // frame rows f0-2 .. f0+32 needed by 32 frames
-constexpr int kStageTasks = 45;     // 9 row blocks x 5 column blocks of (4 rows x 8 float4)
-constexpr int kStagePerWarp = 3;    // ceil(45 / 16)
+constexpr int kTW = 64;              // frames per slice (two per lane)
+constexpr int kRows = kTW + 3;       // 160-sample rows f0-2 .. f0+64 needed by 64 frames
+constexpr int kNFP = 69;             // padded row count of the transposed PCM tile (== 5 mod 8 -> conflict-free stores)
+constexpr int kRowBlocks = (kRows + 3) / 4;          // staging tasks: 17 row blocks x 5 column blocks of (4 rows x 8 float4)
 constexpr float kLog10Of2 = 0.30102999566398120f;
 
-__constant__ float c_win[WRS_N_FFT];        // periodic Hann, src/audio.rs:233
-__constant__ int c_aoff[WRS_N_FFT];         // sample n of a frame -> offset in the transposed PCM tile
-__constant__ cf c_tw[16 * 13];              // W400^{tq}
+struct TabEntry { int aoff; float win; };            // sample n of a frame: offset in the transposed tile, Hann weight
+struct TwEntry { float2 wr, wi, nwi; };              // W400^{tq} as broadcast pairs {c,c} {s,s} {-s,-s}
+__constant__ TabEntry c_tab[WRS_N_FFT];              // periodic Hann, src/audio.rs:233
+__constant__ TwEntry c_tw[16 * 13];
 
 struct LogmelParams {
     const float* pcm;
@@ -50,15 +55,17 @@ struct LogmelParams {
     DevStatus* status;
 };
 
-template <int NG>
+constexpr int kPRows = WRS_N_BINS + 5;               // 201 bins + rows the zero-padded band tails may touch
+
 struct LogmelSmem {
-    static constexpr int TW = NG * 32;
-    float pcmT[WRS_HOP_LENGTH * kNFP];
-    cf Y[16 * 13 * 32];
-    float P[(WRS_N_BINS + 1) * 32];
-    float tile[WRS_N_MELS * TW];
-    MelBank bank;
+    float pcmT[WRS_HOP_LENGTH * kNFP];               // 44 160 B
+    float4 Y[16 * 13 * 32];                          // 106 496 B
+    float2 P[kPRows * 32];                           // 52 736 B
+    float tile[WRS_N_MELS * kTW];                    // 20 480 B
+    float4 w4[MelBank::kMaxPadded / 2];              // 6 144 B: filter weights as broadcast pairs, two per float4 {w0,w0,w1,w1}
+    int lo[WRS_N_MELS], n4[WRS_N_MELS], off4[WRS_N_MELS];
     int red_max;
+    int fin_ready;                                   // the oldest pending slice's segment is complete: seg_floor is valid
     float seg_floor;
 };
 
@@ -81,160 +88,296 @@ __device__ __forceinline__ float4 load_stage4(const float* __restrict__ seg, int
                        load_reflect(seg, i0 + 3, n));
 }
 
-template <int NG, bool FUSED>
+// Staging of the 67 x 160 PCM samples of a slice into the transposed tile: 85 tasks of (4 rows x 32 columns), task
+// k of a warp is w + nw k; a lane moves one float4 per task.  Loads and stores are separate so that the loads can be
+// issued long before the tile is free / the data is needed.
+template <int NT>
+__device__ __forceinline__ void stage_load(const LogmelParams& p, int seg, int fs, int w, int nw, int lane, float4 (&v)[NT]) {
+    const float* __restrict__ segp = p.pcm + (int64_t)seg * p.seg_stride;
+    const int rr = lane >> 3, jj = lane & 7;
+    // no reflection, no ragged end, 16-byte aligned: plain vector loads
+    const bool interior = p.vec_in != 0 && fs >= 2 && (int64_t)WRS_HOP_LENGTH * (fs - 2 + kRows) <= (int64_t)p.n_samples;
+    if (interior) {
+#pragma unroll
+        for (int k = 0; k < NT; ++k) {
+            const int task = w + nw * k;
+            const int rb = task / 5, cb = task - rb * 5;
+            const int r = rb * 4 + rr;
+            if (task < kRowBlocks * 5 && r < kRows)
+                v[k] = __ldg(reinterpret_cast<const float4*>(segp + WRS_HOP_LENGTH * (fs - 2 + r) + 4 * jj + 32 * cb));
+        }
+    } else {
+#pragma unroll 1
+        for (int k = 0; k < NT; ++k) {
+            const int task = w + nw * k;
+            const int rb = task / 5, cb = task - rb * 5;
+            const int r = rb * 4 + rr;
+            float4 t = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            if (task < kRowBlocks * 5 && r < kRows)
+                t = load_stage4(segp, WRS_HOP_LENGTH * (fs - 2 + r) + 4 * jj + 32 * cb, p.n_samples, p.vec_in != 0);
+#pragma unroll
+            for (int kk = 0; kk < NT; ++kk)
+                if (kk == k) v[kk] = t;
+        }
+    }
+}
+template <int NT>
+__device__ __forceinline__ void stage_store(LogmelSmem& sm, int w, int nw, int lane, const float4 (&v)[NT]) {
+    const int rr = lane >> 3, jj = lane & 7;
+#pragma unroll
+    for (int k = 0; k < NT; ++k) {
+        const int task = w + nw * k;
+        const int rb = task / 5, cb = task - rb * 5;
+        const int r = rb * 4 + rr;
+        if (task < kRowBlocks * 5 && r < kRows) {
+            float* d = sm.pcmT + (4 * jj + 32 * cb) * kNFP + r;
+            d[0] = v[k].x; d[kNFP] = v[k].y; d[2 * kNFP] = v[k].z; d[3 * kNFP] = v[k].w;
+        }
+    }
+}
+constexpr int kStagePerWarp = (kRowBlocks * 5 + kWarps - 1) / kWarps;   // 6
+
+__device__ __forceinline__ void fence_acq_rel() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
+
+// Blocking floor + scale of one slice in place: out = (max(raw, segmax - 8) + 4) / 4 (src/audio.rs:256-258).  Only the
+// drain at the end of the kernel (and a full pending queue) comes here; the steady state hides it inside the slice loop.
+__device__ __forceinline__ void finalize_slice_blocking(LogmelSmem& sm, const LogmelParams& p, int seg, int fs, int tid) {
+    const int nf = min(kTW, p.n_frames - fs);
+    if (tid == 0) {
+        // every slice of the segment is owned by a CTA that is running or has finished (persistent grid no larger than
+        // what is co-resident; waits only ever point at lower slice indices), so this wait ends; the bound is a safety net
+        volatile int* cnt = p.seg_cnt + seg;
+        int spins = 0;
+        while (*cnt < p.slices_per_seg) {
+            __nanosleep(64);
+            if (++spins > (1 << 22)) { atomicExch(&p.status->timeout, 1); break; }
+        }
+        fence_acq_rel();
+        sm.seg_floor = key_float(*(volatile int*)(p.seg_max + seg)) - 8.0f;
+    }
+    __syncthreads();
+    const float fl = sm.seg_floor;
+    float* __restrict__ outp = p.out + ((int64_t)seg * WRS_N_MELS) * p.n_frames + fs;
+    for (int idx = tid; idx < WRS_N_MELS * nf; idx += kThreads) {
+        const int m = idx / nf, c = idx - m * nf;
+        float* q = outp + (int64_t)m * p.n_frames + c;
+        *q = (fmaxf(__ldcg(q), fl) + 4.0f) * 0.25f;
+    }
+    __syncthreads();
+}
+
+constexpr int kTilePerThread = (WRS_N_MELS * (kTW / 4) + kThreads - 1) / kThreads;   // float4 of a [80][64] tile per thread: 3
+
+template <bool FUSED>
 __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    LogmelSmem<NG>& sm = *reinterpret_cast<LogmelSmem<NG>*>(smem_raw);
-    constexpr int TW = LogmelSmem<NG>::TW;
+    LogmelSmem& sm = *reinterpret_cast<LogmelSmem*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-    // filterbank -> smem (once per CTA)
-    {
-        const int* src = reinterpret_cast<const int*>(p.bank);
-        int* dst = reinterpret_cast<int*>(&sm.bank);
-        for (int i = tid; i < (int)(sizeof(MelBank) / 4); i += kThreads) dst[i] = src[i];
+    // filterbank -> smem (once per CTA); the rows of P behind bin 200 stay zero (zero-padded band tails read them)
+    for (int i = tid; i < WRS_N_MELS; i += kThreads) { sm.lo[i] = p.bank->lo[i]; sm.n4[i] = p.bank->n4[i]; sm.off4[i] = p.bank->off4[i]; }
+    for (int i = tid; i < MelBank::kMaxPadded / 2; i += kThreads) sm.w4[i] = reinterpret_cast<const float4*>(p.bank->w2)[i];
+    for (int i = tid; i < (kPRows - WRS_N_BINS) * 32; i += kThreads) sm.P[WRS_N_BINS * 32 + i] = make_float2(0.0f, 0.0f);
+
+    // slices are dealt round-robin; (seg, fs) of the current slice advance without divisions
+    const int step_seg = (int)gridDim.x / p.slices_per_seg, step_sl = (int)gridDim.x % p.slices_per_seg;
+    int seg = (int)blockIdx.x / p.slices_per_seg, sl = (int)blockIdx.x % p.slices_per_seg;
+    // slices whose floor/scale is still to be applied, oldest first (fs < 0: empty)
+    int pend_seg[3] = {0, 0, 0}, pend_fs[3] = {-1, -1, -1};
+    if ((int)blockIdx.x < p.total_slices) {
+        float4 v[kStagePerWarp];
+        stage_load(p, seg, sl * kTW, warp, kWarps, lane, v);
+        stage_store(sm, warp, kWarps, lane, v);
     }
-    // staging geometry of this lane: 4 rows x 8 float4 per warp task
-    const int st_rr = lane >> 3, st_jj = lane & 7;
+    __syncthreads();
 
     for (int slice = blockIdx.x; slice < p.total_slices; slice += gridDim.x) {
-        const int seg = slice / p.slices_per_seg;
-        const int fs = (slice - seg * p.slices_per_seg) * TW;   // first frame of the slice
-        const int nf = min(TW, p.n_frames - fs);
-        const int ngroups = (nf + 31) >> 5;
-        const float* __restrict__ segp = p.pcm + (int64_t)seg * p.seg_stride;
-        float lmax = -INFINITY;
+        const int fs = sl * kTW;                         // first frame of the slice
+        const int nf = min(kTW, p.n_frames - fs);
+        int nseg = seg + step_seg, nsl = sl + step_sl;   // the slice after this one
+        if (nsl >= p.slices_per_seg) { nsl -= p.slices_per_seg; ++nseg; }
+        const bool has_next = slice + (int)gridDim.x < p.total_slices;
         if (tid == 0) sm.red_max = float_key(-INFINITY);
 
-        float4 pre[kStagePerWarp];
-        auto stage_load = [&](int f0) {
+        // ---- stage A: warp = t.  Frames lane and lane + 32 side by side.
+        {
+            const int t = warp;
+            f32x2 v[25];
 #pragma unroll
-            for (int k = 0; k < kStagePerWarp; ++k) {
-                const int task = warp + k * kWarps;
-                const int r = (task / 5) * 4 + st_rr, j = (task % 5) * 8 + st_jj;
-                if (task < kStageTasks && r < kRows)
-                    pre[k] = load_stage4(segp, WRS_HOP_LENGTH * (f0 - 2 + r) + 4 * j, p.n_samples, p.vec_in != 0);
+            for (int m = 0; m < 25; ++m) {
+                const TabEntry e = c_tab[16 * m + t];
+                const float* src = sm.pcmT + e.aoff + lane;
+                v[m] = pack2(src[0] * e.win, src[32] * e.win);
             }
-        };
-        auto stage_store = [&]() {
-#pragma unroll
-            for (int k = 0; k < kStagePerWarp; ++k) {
-                const int task = warp + k * kWarps;
-                const int r = (task / 5) * 4 + st_rr, j = (task % 5) * 8 + st_jj;
-                if (task < kStageTasks && r < kRows) {
-                    float* d = sm.pcmT + (4 * j) * kNFP + r;
-                    d[0] = pre[k].x; d[kNFP] = pre[k].y; d[2 * kNFP] = pre[k].z; d[3 * kNFP] = pre[k].w;
-                }
-            }
-        };
-
-        stage_load(fs);
-        stage_store();
-        __syncthreads();
-
-        for (int g = 0; g < ngroups; ++g) {
-            const int f0 = fs + 32 * g;
-            const bool more = (g + 1 < ngroups);
-            if (more) stage_load(f0 + 32);
-
-            // ---- stage A: warp = t
+            cx<f32x2> y[13];
+            rdft25(v, y);
+            float4* dst = sm.Y + (t * 13) * 32 + lane;
             {
-                const int t = warp;
-                float v[25];
-#pragma unroll
-                for (int m = 0; m < 25; ++m) {
-                    const int n = 16 * m + t;
-                    v[m] = sm.pcmT[c_aoff[n] + lane] * c_win[n];
-                }
-                cf y[13];
-                rdft25(v, y);
-                cf* dst = sm.Y + (t * 13) * 32 + lane;
-                dst[0] = y[0];
-#pragma unroll
-                for (int q = 1; q < 13; ++q) dst[q * 32] = cmul(y[q], c_tw[t * 13 + q]);
+                float a, b, c, d;
+                unpack2(y[0].re, a, b); unpack2(y[0].im, c, d);
+                dst[0] = make_float4(a, b, c, d);
             }
-            __syncthreads();
-            if (more) stage_store();
-
-            // ---- stage B: warp = q
-            if (warp < 13) {
-                const int q = warp;
-                cf z[16];
 #pragma unroll
-                for (int t = 0; t < 16; ++t) z[t] = sm.Y[(t * 13 + q) * 32 + lane];
-                cdft16(z);
-#pragma unroll
-                for (int s = 0; s < 16; ++s) {
-                    if (q != 0 || s < 9) sm.P[stageb_bin(q, s) * 32 + lane] = z[s].re * z[s].re + z[s].im * z[s].im;
-                }
-            }
-            __syncthreads();
-
-            // ---- stage C: banded mel projection (src/audio.rs:252), clamp + log10 (:254)
-            {
-                const bool valid = (f0 + lane) < p.n_frames;
-#pragma unroll
-                for (int i = 0; i < WRS_N_MELS / kWarps; ++i) {
-                    const int m = i * kWarps + warp;
-                    const int lo = sm.bank.lo[m], n = sm.bank.n[m];
-                    const float* w = sm.bank.w + sm.bank.off[m];
-                    const float* pp = sm.P + lo * 32 + lane;
-                    float acc = 0.0f;
-                    for (int j = 0; j < n; ++j) acc = fmaf(w[j], pp[j * 32], acc);
-                    const float val = __log2f(fmaxf(acc, 1e-10f)) * kLog10Of2;
-                    sm.tile[m * TW + g * 32 + lane] = val;
-                    if (valid) lmax = fmaxf(lmax, val);
-                }
+            for (int q = 1; q < 13; ++q) {
+                const TwEntry w = c_tw[t * 13 + q];
+                const f32x2 wr = pack2(w.wr.x, w.wr.y), wi = pack2(w.wi.x, w.wi.y), nwi = pack2(w.nwi.x, w.nwi.y);
+                const f32x2 re = fma_(y[q].im, nwi, mul_(y[q].re, wr));
+                const f32x2 im = fma_(y[q].re, wi, mul_(y[q].im, wr));
+                float a, b, c, d;
+                unpack2(re, a, b); unpack2(im, c, d);
+                dst[q * 32] = make_float4(a, b, c, d);
             }
         }
+        __syncthreads();
 
+        // ---- stage B: warp = q < 13.  Meanwhile one lane of warp 15 asks whether the oldest pending slice's segment
+        //      has completed (all its slices have posted their maxima) and, if so, fetches the segment's floor.
+        if (warp < 13) {
+            const int q = warp;
+            cx<f32x2> z[16];
+#pragma unroll
+            for (int t = 0; t < 16; ++t) {
+                const float4 a = sm.Y[(t * 13 + q) * 32 + lane];
+                z[t].re = pack2(a.x, a.y); z[t].im = pack2(a.z, a.w);
+            }
+            cdft16(z);
+#pragma unroll
+            for (int s = 0; s < 16; ++s) {
+                if (q != 0 || s < 9) {
+                    float a, b;
+                    unpack2(power(z[s]), a, b);
+                    sm.P[stageb_bin(q, s) * 32 + lane] = make_float2(a, b);
+                }
+            }
+        } else if (FUSED && warp == 15 && lane == 0) {
+            int ready = 0;
+            if (pend_fs[0] >= 0 && *(volatile int*)(p.seg_cnt + pend_seg[0]) >= p.slices_per_seg) {
+                fence_acq_rel();
+                sm.seg_floor = key_float(*(volatile int*)(p.seg_max + pend_seg[0])) - 8.0f;
+                ready = 1;
+            }
+            sm.fin_ready = ready;
+        }
+        __syncthreads();
+
+        // ---- stage C: banded mel projection (src/audio.rs:252), clamp + log10 (:254).  Its arithmetic hides two
+        //      streams of global traffic issued up front: the next slice's PCM (into the tile stage A has left) and the
+        //      raw log-mel of the pending slice whose floor has just become known.
+        const bool fin = FUSED && sm.fin_ready != 0;
+        const int fseg = pend_seg[0], ffs = pend_fs[0];
+        const int fnf4 = fin ? (min(kTW, p.n_frames - ffs) >> 2) : 0;
+        float* __restrict__ foutp = p.out + ((int64_t)fseg * WRS_N_MELS) * p.n_frames + ffs;
+        const bool fvec = p.vec_out != 0;                // n_frames % 4 == 0 and 16-byte aligned rows
+        float4 nxt[kStagePerWarp], raw[kTilePerThread];
+        if (has_next) stage_load(p, nseg, nsl * kTW, warp, kWarps, lane, nxt);
+        if (fin && fvec) {
+#pragma unroll
+            for (int k = 0; k < kTilePerThread; ++k) {
+                const int idx = tid + k * kThreads;
+                if (idx < WRS_N_MELS * (kTW / 4) && (idx & 15) < fnf4)
+                    raw[k] = __ldcg(reinterpret_cast<const float4*>(foutp + (int64_t)(idx >> 4) * p.n_frames + 4 * (idx & 15)));
+            }
+        }
+        float lmax = -INFINITY;
+        {
+            const bool ok0 = lane < nf, ok1 = lane + 32 < nf;
+#pragma unroll 1
+            for (int i = 0; i < WRS_N_MELS / kWarps; ++i) {
+                const int m = i * kWarps + warp;
+                const int n4 = sm.n4[m];
+                const float4* w = sm.w4 + (sm.off4[m] >> 1);
+                const float2* pp = sm.P + sm.lo[m] * 32 + lane;
+                f32x2 acc0, acc1;
+                zero_(acc0); zero_(acc1);
+                for (int j = 0; j < n4; j += 4) {
+                    const float4 wa = w[j >> 1], wb = w[(j >> 1) + 1];
+                    const float2 p0 = pp[j * 32], p1 = pp[j * 32 + 32], p2 = pp[j * 32 + 64], p3 = pp[j * 32 + 96];
+                    acc0 = fma_(pack2(p0.x, p0.y), pack2(wa.x, wa.y), acc0);
+                    acc1 = fma_(pack2(p1.x, p1.y), pack2(wa.z, wa.w), acc1);
+                    acc0 = fma_(pack2(p2.x, p2.y), pack2(wb.x, wb.y), acc0);
+                    acc1 = fma_(pack2(p3.x, p3.y), pack2(wb.z, wb.w), acc1);
+                }
+                float a0, a1;
+                unpack2(add_(acc0, acc1), a0, a1);
+                const float v0 = __log2f(fmaxf(a0, 1e-10f)) * kLog10Of2, v1 = __log2f(fmaxf(a1, 1e-10f)) * kLog10Of2;
+                sm.tile[m * kTW + lane] = v0; sm.tile[m * kTW + 32 + lane] = v1;
+                if (ok0) lmax = fmaxf(lmax, v0);
+                if (ok1) lmax = fmaxf(lmax, v1);
+            }
+        }
+        if (has_next) stage_store(sm, warp, kWarps, lane, nxt);
+        if (fin) {                                       // out = (max(raw, segmax - 8) + 4) / 4   (src/audio.rs:256-258)
+            const float fl = sm.seg_floor;
+            if (fvec) {
+#pragma unroll
+                for (int k = 0; k < kTilePerThread; ++k) {
+                    const int idx = tid + k * kThreads;
+                    if (idx < WRS_N_MELS * (kTW / 4) && (idx & 15) < fnf4) {
+                        float4 v = raw[k];
+                        v.x = (fmaxf(v.x, fl) + 4.0f) * 0.25f; v.y = (fmaxf(v.y, fl) + 4.0f) * 0.25f;
+                        v.z = (fmaxf(v.z, fl) + 4.0f) * 0.25f; v.w = (fmaxf(v.w, fl) + 4.0f) * 0.25f;
+                        *reinterpret_cast<float4*>(foutp + (int64_t)(idx >> 4) * p.n_frames + 4 * (idx & 15)) = v;
+                    }
+                }
+            } else {
+                const int fnf = min(kTW, p.n_frames - ffs);
+                for (int idx = tid; idx < WRS_N_MELS * fnf; idx += kThreads) {
+                    const int m = idx / fnf, c = idx - m * fnf;
+                    float* q = foutp + (int64_t)m * p.n_frames + c;
+                    *q = (fmaxf(__ldcg(q), fl) + 4.0f) * 0.25f;
+                }
+            }
+            pend_seg[0] = pend_seg[1]; pend_fs[0] = pend_fs[1];
+            pend_seg[1] = pend_seg[2]; pend_fs[1] = pend_fs[2];
+            pend_fs[2] = -1;
+        }
         // ---- per-slice max -> per-segment max (src/audio.rs:256 `log_spec.max()`)
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) lmax = fmaxf(lmax, __shfl_xor_sync(0xffffffffu, lmax, o));
         if (lane == 0) atomicMax(&sm.red_max, float_key(lmax));
         __syncthreads();
-        if (tid == 0) {
-            atomicMax(p.seg_max + seg, sm.red_max);
-            if (FUSED) {
-                __threadfence();
-                atomicAdd(p.seg_cnt + seg, 1);
-                // every slice of a segment is owned by a co-resident CTA (cooperative launch, slices_per_seg <=
-                // gridDim.x, slices taken in index order) so this wait always ends; the bound is a safety net.
-                volatile int* cnt = p.seg_cnt + seg;
-                int spins = 0;
-                while (*cnt < p.slices_per_seg) {
-                    __nanosleep(64);
-                    if (++spins > (1 << 22)) { atomicExch(&p.status->timeout, 1); break; }
-                }
-                __threadfence();
-                sm.seg_floor = key_float(*(volatile int*)(p.seg_max + seg)) - 8.0f;
-            }
-        }
-        __syncthreads();
 
-        // ---- floor, scale (src/audio.rs:256-258) and coalesced store of the [80][nf] tile
-        const float floor_v = FUSED ? sm.seg_floor : -INFINITY;
+        // ---- raw log10(mel) of the [80][nf] tile -> HBM, coalesced
         float* __restrict__ outp = p.out + ((int64_t)seg * WRS_N_MELS) * p.n_frames + fs;
-        if (p.vec_out && (nf & 3) == 0) {
+        if (p.vec_out) {
             const int nf4 = nf >> 2;
-            for (int idx = tid; idx < WRS_N_MELS * nf4; idx += kThreads) {
-                const int m = idx / nf4, c4 = idx - m * nf4;
-                float4 v = *reinterpret_cast<const float4*>(sm.tile + m * TW + 4 * c4);
-                if (FUSED) {
-                    v.x = (fmaxf(v.x, floor_v) + 4.0f) * 0.25f; v.y = (fmaxf(v.y, floor_v) + 4.0f) * 0.25f;
-                    v.z = (fmaxf(v.z, floor_v) + 4.0f) * 0.25f; v.w = (fmaxf(v.w, floor_v) + 4.0f) * 0.25f;
-                }
-                *reinterpret_cast<float4*>(outp + (int64_t)m * p.n_frames + 4 * c4) = v;
+#pragma unroll
+            for (int k = 0; k < kTilePerThread; ++k) {
+                const int idx = tid + k * kThreads;
+                if (idx < WRS_N_MELS * (kTW / 4) && (idx & 15) < nf4)
+                    *reinterpret_cast<float4*>(outp + (int64_t)(idx >> 4) * p.n_frames + 4 * (idx & 15)) =
+                        *reinterpret_cast<const float4*>(sm.tile + 4 * idx);
             }
         } else {
             for (int idx = tid; idx < WRS_N_MELS * nf; idx += kThreads) {
                 const int m = idx / nf, c = idx - m * nf;
-                float v = sm.tile[m * TW + c];
-                if (FUSED) v = (fmaxf(v, floor_v) + 4.0f) * 0.25f;
-                outp[(int64_t)m * p.n_frames + c] = v;
+                outp[(int64_t)m * p.n_frames + c] = sm.tile[m * kTW + c];
             }
         }
-        __syncthreads();
+        if (tid == 0) atomicMax(p.seg_max + seg, sm.red_max);
+        if (FUSED) {
+            fence_acq_rel();
+            __syncthreads();
+            if (tid == 0) atomicAdd(p.seg_cnt + seg, 1);
+            if (pend_fs[2] >= 0) {                       // queue full (a straggling segment): wait for the oldest
+                finalize_slice_blocking(sm, p, pend_seg[0], pend_fs[0], tid);
+                pend_seg[0] = pend_seg[1]; pend_fs[0] = pend_fs[1];
+                pend_seg[1] = pend_seg[2]; pend_fs[1] = pend_fs[2];
+                pend_fs[2] = -1;
+            }
+            const int slot = pend_fs[0] < 0 ? 0 : (pend_fs[1] < 0 ? 1 : 2);
+            if (slot == 0) { pend_seg[0] = seg; pend_fs[0] = fs; }
+            else if (slot == 1) { pend_seg[1] = seg; pend_fs[1] = fs; }
+            else { pend_seg[2] = seg; pend_fs[2] = fs; }
+        } else {
+            __syncthreads();
+        }
+        seg = nseg; sl = nsl;
+    }
+    if (FUSED) {
+#pragma unroll
+        for (int k = 0; k < 3; ++k)
+            if (pend_fs[k] >= 0) finalize_slice_blocking(sm, p, pend_seg[k], pend_fs[k], tid);
     }
 }
 
@@ -273,27 +416,24 @@ static bool g_tables_ready[64] = {false};
 static int init_tables(wrs_ctx* ctx) {
     if (ctx->device < 64 && g_tables_ready[ctx->device]) return WRS_OK;
     const double PI = 3.14159265358979323846;
-    float win[WRS_N_FFT];
-    int aoff[WRS_N_FFT];
-    cf tw[16 * 13];
+    static TabEntry tab[WRS_N_FFT];
+    static TwEntry tw[16 * 13];
     for (int n = 0; n < WRS_N_FFT; ++n) {
-        win[n] = (float)(0.5 - 0.5 * std::cos(2.0 * PI * n / WRS_N_FFT));
         const int u = n + 120;   // frame f, sample n  ->  row f-2+u/160 of the tile, column u%160
-        aoff[n] = (u % WRS_HOP_LENGTH) * kNFP + (u / WRS_HOP_LENGTH);
+        tab[n].aoff = (u % WRS_HOP_LENGTH) * kNFP + (u / WRS_HOP_LENGTH);
+        tab[n].win = (float)(0.5 - 0.5 * std::cos(2.0 * PI * n / WRS_N_FFT));
     }
     for (int t = 0; t < 16; ++t)
         for (int q = 0; q < 13; ++q) {
             const double a = -2.0 * PI * (double)(t * q) / 400.0;
-            tw[t * 13 + q] = cf{(float)std::cos(a), (float)std::sin(a)};
+            const float c = (float)std::cos(a), s = (float)std::sin(a);
+            tw[t * 13 + q] = TwEntry{make_float2(c, c), make_float2(s, s), make_float2(-s, -s)};
         }
-    WRS_CUDA(ctx, cudaMemcpyToSymbol(c_win, win, sizeof(win)));
-    WRS_CUDA(ctx, cudaMemcpyToSymbol(c_aoff, aoff, sizeof(aoff)));
+    WRS_CUDA(ctx, cudaMemcpyToSymbol(c_tab, tab, sizeof(tab)));
     WRS_CUDA(ctx, cudaMemcpyToSymbol(c_tw, tw, sizeof(tw)));
     if (ctx->device < 64) g_tables_ready[ctx->device] = true;
     return WRS_OK;
 }
-
-constexpr int kNG = 4;   // 128-frame slices
 
 }  // namespace wrs
 
@@ -309,7 +449,7 @@ int wrs_logmel_set_filter(wrs_ctx* ctx, const float* filter_host) {
     }
     wrs::MelBank bank;
     if (!wrs::build_mel_bank(filter_host, &bank))
-        return wrs::fail(ctx, WRS_ERR_UNSUPPORTED, "wrs_logmel_set_filter: filterbank is not banded (more than 1024 in-band weights)");
+        return wrs::fail(ctx, WRS_ERR_UNSUPPORTED, "wrs_logmel_set_filter: filterbank is not banded (more than 768 in-band weights after padding every band to a multiple of four)");
     WRS_CUDA(ctx, cudaSetDevice(ctx->device));
     WRS_CUDA(ctx, cudaMemcpy(ctx->d_bank, &bank, sizeof(bank), cudaMemcpyHostToDevice));
     return WRS_OK;
@@ -330,7 +470,7 @@ int wrs_logmel_batch(wrs_ctx* ctx, const float* pcm, int64_t n_segments, int64_t
     int rc = init_tables(ctx);
     if (rc != WRS_OK) return rc;
 
-    constexpr int TW = kNG * 32;
+    constexpr int TW = kTW;
     LogmelParams p;
     p.pcm = pcm; p.out = out; p.seg_stride = seg_stride;
     p.n_segments = (int)n_segments; p.n_samples = (int)n_samples; p.n_frames = (int)(n_samples / WRS_HOP_LENGTH);
@@ -357,26 +497,27 @@ int wrs_logmel_batch(wrs_ctx* ctx, const float* pcm, int64_t n_segments, int64_t
     WRS_CUDA(ctx, cudaMemsetAsync(p.seg_max, 0x80, sizeof(int) * n_segments, stream));
     WRS_CUDA(ctx, cudaMemsetAsync(p.seg_cnt, 0, sizeof(int) * n_segments, stream));
 
-    const size_t smem = sizeof(LogmelSmem<kNG>);
+    const size_t smem = sizeof(LogmelSmem);
     if (ctx->logmel_max_ctas_per_sm == 0) {
-        WRS_CUDA(ctx, cudaFuncSetAttribute(logmel_kernel<kNG, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        WRS_CUDA(ctx, cudaFuncSetAttribute(logmel_kernel<kNG, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        WRS_CUDA(ctx, cudaFuncSetAttribute(logmel_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        WRS_CUDA(ctx, cudaFuncSetAttribute(logmel_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         int occ = 0;
-        WRS_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, logmel_kernel<kNG, true>, kThreads, smem));
+        WRS_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, logmel_kernel<true>, kThreads, smem));
         if (occ < 1) return fail(ctx, WRS_ERR_CUDA, "logmel kernel does not fit on an SM");
         ctx->logmel_max_ctas_per_sm = occ;
     }
     const int resident = ctx->sm_count * ctx->logmel_max_ctas_per_sm;
     const int grid = (int)std::min<int64_t>(total, resident);
-    bool fused = p.slices_per_seg <= grid;
-    if (ctx->opt_logmel_fused == 0) fused = false;
+    // fused: the floor/scale of a slice is applied one slice later by the CTA that produced it, once the segment's
+    // other slices (all owned by co-resident CTAs: cooperative launch) have posted their maxima
+    const bool fused = ctx->opt_logmel_fused != 0;
     ctx->stat_last_logmel_mode = fused ? 1 : 0;
     ctx->stat_last_logmel_grid = grid;
     if (fused) {
         void* args[] = {(void*)&p};
-        WRS_CUDA(ctx, cudaLaunchCooperativeKernel((void*)logmel_kernel<kNG, true>, dim3(grid), dim3(kThreads), args, smem, stream));
+        WRS_CUDA(ctx, cudaLaunchCooperativeKernel((void*)logmel_kernel<true>, dim3(grid), dim3(kThreads), args, smem, stream));
     } else {
-        logmel_kernel<kNG, false><<<grid, kThreads, smem, stream>>>(p);
+        logmel_kernel<false><<<grid, kThreads, smem, stream>>>(p);
         WRS_CUDA(ctx, cudaGetLastError());
         const int64_t per_seg = (int64_t)WRS_N_MELS * p.n_frames, tot = per_seg * n_segments;
         const int vec = ((reinterpret_cast<uintptr_t>(out) & 15) == 0 && (per_seg & 3) == 0) ? 1 : 0;

@@ -16,7 +16,13 @@ struct MelBank {
     int lo[WRS_N_MELS];
     int n[WRS_N_MELS];
     int off[WRS_N_MELS];
+    static constexpr int kMaxPadded = 768;
     float w[kMaxWeights];
+    // the same bands padded with zero weights to multiples of four, every weight twice {w, w}: the broadcast operand of a
+    // packed two-frame FMA.  Row m: n4[m] weights from off4[m] (both multiples of 4).
+    int n4[WRS_N_MELS];
+    int off4[WRS_N_MELS];
+    float w2[2 * kMaxPadded];
     int total;
 };
 
