@@ -168,8 +168,19 @@ __device__ __forceinline__ void finalize_slice_blocking(LogmelSmem& sm, const Lo
 
 constexpr int kTilePerThread = (WRS_N_MELS * (kTW / 4) + kThreads - 1) / kThreads;   // float4 of a [80][64] tile per thread: 3
 
+#ifdef WRS_TRACE
+// investigation aid (tools/debug/logmel_trace.py): per-CTA cycles spent in each phase of the slice loop
+__device__ unsigned long long g_lm_trace[148 * 8];
+#define LM_T(k) do { if (tid == 0) { const long long now_ = clock64(); acc_[k] += now_ - t_; t_ = now_; } } while (0)
+#else
+#define LM_T(k) do {} while (0)
+#endif
+
 template <bool FUSED>
 __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams p) {
+#ifdef WRS_TRACE
+    long long acc_[8] = {0, 0, 0, 0, 0, 0, 0, 0}, t_ = clock64();
+#endif
     extern __shared__ __align__(16) unsigned char smem_raw[];
     LogmelSmem& sm = *reinterpret_cast<LogmelSmem*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -184,6 +195,7 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
     int seg = (int)blockIdx.x / p.slices_per_seg, sl = (int)blockIdx.x % p.slices_per_seg;
     // slices whose floor/scale is still to be applied, oldest first (fs < 0: empty)
     int pend_seg[3] = {0, 0, 0}, pend_fs[3] = {-1, -1, -1};
+    int post_seg = -1;                                   // segment of the slice whose "posted" count is still owed
     if ((int)blockIdx.x < p.total_slices) {
         float4 v[kStagePerWarp];
         stage_load(p, seg, sl * kTW, warp, kWarps, lane, v);
@@ -201,7 +213,10 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
 
         // ---- stage A: warp = t.  Frames lane and lane + 32 side by side.
         {
-            const int t = warp;
+            // opaque copy: keeps the compiler from hoisting the 38 twiddle / window constants of this warp out of the
+            // slice loop, where they would sit in registers (and spill) through stages B and C
+            int t = warp;
+            asm volatile("" : "+r"(t));
             f32x2 v[25];
 #pragma unroll
             for (int m = 0; m < 25; ++m) {
@@ -229,6 +244,7 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
             }
         }
         __syncthreads();
+        LM_T(0);
 
         // ---- stage B: warp = q < 13.  Meanwhile one lane of warp 15 asks whether the oldest pending slice's segment
         //      has completed (all its slices have posted their maxima) and, if so, fetches the segment's floor.
@@ -250,6 +266,9 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
                 }
             }
         } else if (FUSED && warp == 15 && lane == 0) {
+            // the previous slice's raw rows and maximum were issued before the barrier above: one fence by this lane
+            // orders all of them before the count that tells the other CTAs this slice has posted
+            if (post_seg >= 0) { fence_acq_rel(); atomicAdd(p.seg_cnt + post_seg, 1); }
             int ready = 0;
             if (pend_fs[0] >= 0 && *(volatile int*)(p.seg_cnt + pend_seg[0]) >= p.slices_per_seg) {
                 fence_acq_rel();
@@ -259,6 +278,7 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
             sm.fin_ready = ready;
         }
         __syncthreads();
+        LM_T(1);
 
         // ---- stage C: banded mel projection (src/audio.rs:252), clamp + log10 (:254).  Its arithmetic hides two
         //      streams of global traffic issued up front: the next slice's PCM (into the tile stage A has left) and the
@@ -278,6 +298,7 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
                     raw[k] = __ldcg(reinterpret_cast<const float4*>(foutp + (int64_t)(idx >> 4) * p.n_frames + 4 * (idx & 15)));
             }
         }
+        LM_T(7);
         float lmax = -INFINITY;
         {
             const bool ok0 = lane < nf, ok1 = lane + 32 < nf;
@@ -305,7 +326,9 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
                 if (ok1) lmax = fmaxf(lmax, v1);
             }
         }
+        LM_T(2);
         if (has_next) stage_store(sm, warp, kWarps, lane, nxt);
+        LM_T(3);
         if (fin) {                                       // out = (max(raw, segmax - 8) + 4) / 4   (src/audio.rs:256-258)
             const float fl = sm.seg_floor;
             if (fvec) {
@@ -335,7 +358,9 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) lmax = fmaxf(lmax, __shfl_xor_sync(0xffffffffu, lmax, o));
         if (lane == 0) atomicMax(&sm.red_max, float_key(lmax));
+        LM_T(4);
         __syncthreads();
+        LM_T(5);
 
         // ---- raw log10(mel) of the [80][nf] tile -> HBM, coalesced
         float* __restrict__ outp = p.out + ((int64_t)seg * WRS_N_MELS) * p.n_frames + fs;
@@ -356,10 +381,11 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
         }
         if (tid == 0) atomicMax(p.seg_max + seg, sm.red_max);
         if (FUSED) {
-            fence_acq_rel();
-            __syncthreads();
-            if (tid == 0) atomicAdd(p.seg_cnt + seg, 1);
-            if (pend_fs[2] >= 0) {                       // queue full (a straggling segment): wait for the oldest
+            post_seg = seg;                              // counted by warp 15 during the next stage B
+            if (pend_fs[2] >= 0) {                       // queue full (a straggling segment): wait for the oldest --
+                __syncthreads();                         // after this slice has been counted, so that two CTAs
+                if (tid == 0) { fence_acq_rel(); atomicAdd(p.seg_cnt + seg, 1); }   // can never wait on each other
+                post_seg = -1;
                 finalize_slice_blocking(sm, p, pend_seg[0], pend_fs[0], tid);
                 pend_seg[0] = pend_seg[1]; pend_fs[0] = pend_fs[1];
                 pend_seg[1] = pend_seg[2]; pend_fs[1] = pend_fs[2];
@@ -369,12 +395,16 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
             if (slot == 0) { pend_seg[0] = seg; pend_fs[0] = fs; }
             else if (slot == 1) { pend_seg[1] = seg; pend_fs[1] = fs; }
             else { pend_seg[2] = seg; pend_fs[2] = fs; }
-        } else {
-            __syncthreads();
         }
+        LM_T(6);
         seg = nseg; sl = nsl;
     }
+#ifdef WRS_TRACE
+    if (tid == 0) for (int k = 0; k < 8; ++k) g_lm_trace[blockIdx.x * 8 + k] = acc_[k];
+#endif
     if (FUSED) {
+        __syncthreads();
+        if (tid == 0 && post_seg >= 0) { fence_acq_rel(); atomicAdd(p.seg_cnt + post_seg, 1); }
 #pragma unroll
         for (int k = 0; k < 3; ++k)
             if (pend_fs[k] >= 0) finalize_slice_blocking(sm, p, pend_seg[k], pend_fs[k], tid);
@@ -438,6 +468,12 @@ static int init_tables(wrs_ctx* ctx) {
 }  // namespace wrs
 
 extern "C" {
+
+#ifdef WRS_TRACE
+int wrs_debug_logmel_trace_read(unsigned long long* out_host, int n) {
+    return (int)cudaMemcpyFromSymbol(out_host, wrs::g_lm_trace, sizeof(unsigned long long) * n);
+}
+#endif
 
 int wrs_logmel_set_filter(wrs_ctx* ctx, const float* filter_host) {
     if (!ctx) return wrs::fail(nullptr, WRS_ERR_INVALID, "wrs_logmel_set_filter: null ctx");
