@@ -4,17 +4,19 @@ ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)
 sys.path.insert(0, ROOT)
 import numpy as np, torch
 from whisper_rs_b200 import _lib, audio, synth
+if len(sys.argv) > 1:
+    _lib.context(0).set_option("logmel_fused", int(sys.argv[1]))
 pcm = torch.from_numpy(synth.audio_batch(16, seed=1)).repeat(4, 1).contiguous().cuda()
 for _ in range(3):
     audio.log_mel_spectrogram_batch(pcm)
 torch.cuda.synchronize()
-buf = np.zeros(148 * 8, dtype=np.uint64)
+buf = np.zeros(148 * 12, dtype=np.uint64)
 h = _lib.lib()
 h.wrs_debug_logmel_trace_read.argtypes = [C.c_void_p, C.c_int]
-print("rc", h.wrs_debug_logmel_trace_read(buf.ctypes.data_as(C.c_void_p), 148 * 8))
-t = buf.reshape(148, 8).astype(np.float64)
+print("rc", h.wrs_debug_logmel_trace_read(buf.ctypes.data_as(C.c_void_p), 148 * 12))
+t = buf.reshape(148, 12).astype(np.float64)
 slices = 3008 / 148.0
-names = ["stage A", "stage B (+poll)", "C: mel (warp 0)", "C: stage_store (warp 0)", "C: finalize + max (warp 0)", "C: barrier wait (warp 0)", "raw store + post", "C: issue loads (warp 0)"]
+names = ["stage A", "stage B (+copy issue, poll)", "C: raw loads / edge staging (warp 0)", "C: mel (warp 0)", "C: finalize + max (warp 0)", "C: barrier wait (warp 0)", "raw store + queue", "wait for PCM tile", "C: edge staging total", "edge slices (count)"]
 for k, n in enumerate(names):
     print(f"{n:34s} mean {t[:, k].mean() / slices:9.0f} cycles/slice   (min CTA {t[:, k].min() / slices:.0f}, max {t[:, k].max() / slices:.0f})")
-print("sum per slice", t[:, :8].sum(1).mean() / slices)
+print("sum per slice", t[:, :9].sum(1).mean() / slices)

@@ -52,7 +52,7 @@ void mel_filter_slaney(float* out) {
 
 bool build_mel_bank(const float* dense, MelBank* bank) {
     int total = 0, total4 = 0;
-    for (int i = 0; i < 2 * MelBank::kMaxPadded; ++i) bank->w2[i] = 0.0f;
+    for (int i = 0; i < MelBank::kMaxPadded; ++i) bank->wp[i] = 0.0f;
     for (int m = 0; m < WRS_N_MELS; ++m) {
         int lo = -1, hi = -1;
         for (int k = 0; k < WRS_N_BINS; ++k)
@@ -64,7 +64,7 @@ bool build_mel_bank(const float* dense, MelBank* bank) {
         bank->n4[m] = n4; bank->off4[m] = total4;
         for (int j = 0; j < n; ++j) {
             bank->w[total + j] = dense[m * WRS_N_BINS + lo + j];
-            bank->w2[2 * (total4 + j)] = bank->w2[2 * (total4 + j) + 1] = bank->w[total + j];
+            bank->wp[total4 + j] = bank->w[total + j];
         }
         total += n; total4 += n4;
     }

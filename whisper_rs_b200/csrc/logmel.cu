@@ -2,21 +2,20 @@
 //
 // Replaces the ATen op sequence of reference src/audio.rs:230-259 (hann_window, stft, abs, pow, matmul,
 // clamp_min, log10, max, maximum, add, div) with one persistent kernel.  A CTA (16 warps) takes slices of 64
-// frames; every lane works on TWO frames (f0 + lane, f0 + 32 + lane) held side by side in 64-bit register pairs,
-// so the whole FFT runs on Blackwell's packed FP32 instructions (FADD2 / FMUL2 / FFMA2: one issue slot, two frames):
+// frames; every lane works on TWO frames held side by side in 64-bit register pairs, so the whole FFT runs on
+// Blackwell's packed FP32 instructions (FADD2 / FMUL2 / FFMA2: one issue slot, two frames):
 //
-//   PCM (HBM) --LDG.128--> smem, transposed [sample mod 160][frame row]     (conflict-free, lane = frame)
-//   stage A  warp t : 64 frames x real 25-point DFT + W400^{tq}       -> smem Y[t][q][lane]   (float4: re2, im2)
-//   stage B  warp q : 64 frames x complex 16-point DFT, |X|^2         -> smem P[bin][lane]    (float2)
-//            warps 13..15 meanwhile stage the NEXT slice's PCM (the tile is free once stage A is done)
-//   stage C  warp w : 64 frames x 5 mel rows (banded FP32 FMA), log10 -> smem tile[mel][frame]
-//   slice end       : raw log-mel -> HBM, block max -> atomicMax per segment, arrival count per segment
-//   one slice later : the segment's max is known (all its slices have arrived): floor (max-8), (x+4)/4 applied in
-//                     place on the slice's own 20 KB (still in L2)
-//
-// Within a warp every lane works on different frames and the same (t | q | mel): window values, twiddles and
-// filter weights are warp-uniform (constant bank / broadcast loads) and no lane ever reads another lane's
-// column of Y or P.
+//   PCM (HBM) --bulk async copy--> smem tile, row-major [67 rows of 160 samples], pitch 164     (no registers, one
+//            mbarrier; issued by an idle warp as soon as stage A has released the tile, lands behind stages B and C)
+//   stage A  warp (g, tq), lane (f8, tl): frames 8g+f8 and 8g+f8+32, t = 4tq+tl:
+//            real 25-point DFT over the taps 16m+t, times W400^{tq}   -> smem Y[t][q][frame pair]  (float4: re2, im2)
+//            (8 frames x 4 consecutive taps per load = 32 distinct banks at pitch 164)
+//   stage B  warp q, lane = frame pair: complex 16-point DFT, |X|^2   -> smem P[bin][frame pair]   (float2)
+//            warp 14 issues the next slice's PCM copy; warp 15 posts the previous slice and polls the pending one
+//   stage C  warp w, lane = frame pair: 5 mel rows (banded FP32 FMA), log10 -> smem tile[mel][frame]
+//   slice end       : raw log-mel -> HBM, block max -> atomicMax per segment
+//   one slice later : the slice is counted as posted; once all slices of a segment have posted, its max is final
+//                     and floor (max-8), (x+4)/4 are applied in place on the slice's own 20 KB (still in L2)
 #include <algorithm>
 #include <cmath>
 
@@ -29,14 +28,12 @@ constexpr int kThreads = 512;
 constexpr int kWarps = kThreads / 32;
 constexpr int kTW = 64;              // frames per slice (two per lane)
 constexpr int kRows = kTW + 3;       // 160-sample rows f0-2 .. f0+64 needed by 64 frames
-constexpr int kNFP = 69;             // padded row count of the transposed PCM tile (== 5 mod 8 -> conflict-free stores)
-constexpr int kRowBlocks = (kRows + 3) / 4;          // staging tasks: 17 row blocks x 5 column blocks of (4 rows x 8 float4)
+constexpr int kPitch = WRS_HOP_LENGTH + 4;   // words per tile row: 16-byte aligned rows, frame stride == 4 banks
 constexpr float kLog10Of2 = 0.30102999566398120f;
 
-struct TabEntry { int aoff; float win; };            // sample n of a frame: offset in the transposed tile, Hann weight
-struct TwEntry { float2 wr, wi, nwi; };              // W400^{tq} as broadcast pairs {c,c} {s,s} {-s,-s}
-__constant__ TabEntry c_tab[WRS_N_FFT];              // periodic Hann, src/audio.rs:233
-__constant__ TwEntry c_tw[16 * 13];
+struct TabEntry { int off; float win; };             // tap n of frame 0: word offset in the tile, periodic Hann weight
+__constant__ TabEntry c_tab[WRS_N_FFT];              // src/audio.rs:233
+__constant__ float2 c_tw[16 * 13];                   // W400^{tq} = (cos, sin)(-2 pi t q / 400)
 
 struct LogmelParams {
     const float* pcm;
@@ -55,19 +52,23 @@ struct LogmelParams {
     DevStatus* status;
 };
 
-constexpr int kPRows = WRS_N_BINS + 5;               // 201 bins + rows the zero-padded band tails may touch
+constexpr int kPRows = WRS_N_BINS + 3;               // 201 bins + rows the zero-padded band tails may touch
 
 struct LogmelSmem {
-    float pcmT[WRS_HOP_LENGTH * kNFP];               // 44 160 B
+    float pcm[kRows * kPitch];                       // 43 952 B
     float4 Y[16 * 13 * 32];                          // 106 496 B
-    float2 P[kPRows * 32];                           // 52 736 B
+    float2 P[kPRows * 32];                           // 52 224 B
     float tile[WRS_N_MELS * kTW];                    // 20 480 B
-    float4 w4[MelBank::kMaxPadded / 2];              // 6 144 B: filter weights as broadcast pairs, two per float4 {w0,w0,w1,w1}
+    float w[MelBank::kMaxPadded];                    // 3 072 B: in-band filter weights, bands zero-padded to multiples of 4
+    TabEntry tab[WRS_N_FFT];                         // 3 200 B
+    float2 tw[16 * 13];                              // 1 664 B
     int lo[WRS_N_MELS], n4[WRS_N_MELS], off4[WRS_N_MELS];
+    unsigned long long pcm_bar;                      // mbarrier: bytes of the PCM tile in flight
     int red_max;
     int fin_ready;                                   // the oldest pending slice's segment is complete: seg_floor is valid
     float seg_floor;
 };
+static_assert(sizeof(LogmelSmem) <= 227 * 1024, "log-mel working set exceeds the 227 KB a CTA can own");
 
 __device__ __forceinline__ int float_key(float f) {
     const int b = __float_as_int(f);
@@ -82,61 +83,66 @@ __device__ __forceinline__ float load_reflect(const float* __restrict__ seg, int
     return (i >= 0 && i < n) ? __ldg(seg + i) : 0.0f;
 }
 
-__device__ __forceinline__ float4 load_stage4(const float* __restrict__ seg, int i0, int n, bool vec) {
-    if (vec && i0 >= 0 && i0 + 3 < n) return __ldg(reinterpret_cast<const float4*>(seg + i0));
-    return make_float4(load_reflect(seg, i0, n), load_reflect(seg, i0 + 1, n), load_reflect(seg, i0 + 2, n),
-                       load_reflect(seg, i0 + 3, n));
+// ---- async-proxy plumbing of the PCM tile (cp.async.bulk + mbarrier complete_tx)
+__device__ __forceinline__ unsigned smem_addr(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 }
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_addr(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_addr(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_addr(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-// Staging of the 67 x 160 PCM samples of a slice into the transposed tile: 85 tasks of (4 rows x 32 columns), task
-// k of a warp is w + nw k; a lane moves one float4 per task.  Loads and stores are separate so that the loads can be
-// issued long before the tile is free / the data is needed.
-template <int NT>
-__device__ __forceinline__ void stage_load(const LogmelParams& p, int seg, int fs, int w, int nw, int lane, float4 (&v)[NT]) {
+// The tile of slice (seg, fs) is rows fs-2 .. fs+64 of the segment cut into 160-sample rows.  Away from the segment's
+// ends (no reflection, nothing ragged) and with 16-byte aligned PCM it is one contiguous range of the input.
+__device__ __forceinline__ bool slice_is_interior(const LogmelParams& p, int fs) {
+    return p.vec_in != 0 && fs >= 2 && (int64_t)WRS_HOP_LENGTH * (fs - 2 + kRows) <= (int64_t)p.n_samples;
+}
+// 67 row copies of 640 B, completion counted in bytes on the tile's mbarrier.  Two warps share the issue (part 0 also
+// makes the phase's single arrival and announces the byte count; a copy that completes before that only drives the
+// pending byte count negative for a moment).
+__device__ __forceinline__ void stage_bulk(LogmelSmem& sm, const LogmelParams& p, int seg, int fs, int lane, int part) {
+    const float* __restrict__ src = p.pcm + (int64_t)seg * p.seg_stride + (int64_t)WRS_HOP_LENGTH * (fs - 2);
+    constexpr int kHalf = (kRows + 1) / 2;
+    fence_proxy_async();                             // the tile was last touched by ordinary loads/stores
+    if (part == 0 && lane == 0) mbar_expect_tx(&sm.pcm_bar, kRows * WRS_HOP_LENGTH * (unsigned)sizeof(float));
+    const int r0 = part * kHalf, r1 = min(kRows, r0 + kHalf);
+    for (int r = r0 + lane; r < r1; r += 32)
+        bulk_g2s(sm.pcm + r * kPitch, src + r * WRS_HOP_LENGTH, WRS_HOP_LENGTH * (unsigned)sizeof(float), &sm.pcm_bar);
+}
+// the segment's first and last slices (reflection, ragged end) and unaligned input: element-wise, whole CTA
+__device__ __forceinline__ void stage_general(LogmelSmem& sm, const LogmelParams& p, int seg, int fs, int tid) {
     const float* __restrict__ segp = p.pcm + (int64_t)seg * p.seg_stride;
-    const int rr = lane >> 3, jj = lane & 7;
-    // no reflection, no ragged end, 16-byte aligned: plain vector loads
-    const bool interior = p.vec_in != 0 && fs >= 2 && (int64_t)WRS_HOP_LENGTH * (fs - 2 + kRows) <= (int64_t)p.n_samples;
-    if (interior) {
-#pragma unroll
-        for (int k = 0; k < NT; ++k) {
-            const int task = w + nw * k;
-            const int rb = task / 5, cb = task - rb * 5;
-            const int r = rb * 4 + rr;
-            if (task < kRowBlocks * 5 && r < kRows)
-                v[k] = __ldg(reinterpret_cast<const float4*>(segp + WRS_HOP_LENGTH * (fs - 2 + r) + 4 * jj + 32 * cb));
-        }
-    } else {
-#pragma unroll 1
-        for (int k = 0; k < NT; ++k) {
-            const int task = w + nw * k;
-            const int rb = task / 5, cb = task - rb * 5;
-            const int r = rb * 4 + rr;
-            float4 t = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-            if (task < kRowBlocks * 5 && r < kRows)
-                t = load_stage4(segp, WRS_HOP_LENGTH * (fs - 2 + r) + 4 * jj + 32 * cb, p.n_samples, p.vec_in != 0);
-#pragma unroll
-            for (int kk = 0; kk < NT; ++kk)
-                if (kk == k) v[kk] = t;
-        }
+    const int base = WRS_HOP_LENGTH * (fs - 2);
+#pragma unroll 4
+    for (int idx = tid; idx < kRows * WRS_HOP_LENGTH; idx += kThreads) {
+        const int r = idx / WRS_HOP_LENGTH, c = idx - r * WRS_HOP_LENGTH;
+        sm.pcm[r * kPitch + c] = load_reflect(segp, base + idx, p.n_samples);
     }
 }
-template <int NT>
-__device__ __forceinline__ void stage_store(LogmelSmem& sm, int w, int nw, int lane, const float4 (&v)[NT]) {
-    const int rr = lane >> 3, jj = lane & 7;
-#pragma unroll
-    for (int k = 0; k < NT; ++k) {
-        const int task = w + nw * k;
-        const int rb = task / 5, cb = task - rb * 5;
-        const int r = rb * 4 + rr;
-        if (task < kRowBlocks * 5 && r < kRows) {
-            float* d = sm.pcmT + (4 * jj + 32 * cb) * kNFP + r;
-            d[0] = v[k].x; d[kNFP] = v[k].y; d[2 * kNFP] = v[k].z; d[3 * kNFP] = v[k].w;
-        }
-    }
-}
-constexpr int kStagePerWarp = (kRowBlocks * 5 + kWarps - 1) / kWarps;   // 6
 
+__device__ __forceinline__ int ld_acquire(const int* p) {
+    int v;
+    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
 __device__ __forceinline__ void fence_acq_rel() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 
 // Blocking floor + scale of one slice in place: out = (max(raw, segmax - 8) + 4) / 4 (src/audio.rs:256-258).  Only the
@@ -166,11 +172,13 @@ __device__ __forceinline__ void finalize_slice_blocking(LogmelSmem& sm, const Lo
     __syncthreads();
 }
 
+
+constexpr int kPend = 4;              // slices a CTA may have waiting for their segment's maximum
 constexpr int kTilePerThread = (WRS_N_MELS * (kTW / 4) + kThreads - 1) / kThreads;   // float4 of a [80][64] tile per thread: 3
 
 #ifdef WRS_TRACE
 // investigation aid (tools/debug/logmel_trace.py): per-CTA cycles spent in each phase of the slice loop
-__device__ unsigned long long g_lm_trace[148 * 8];
+__device__ unsigned long long g_lm_trace[148 * 12];
 #define LM_T(k) do { if (tid == 0) { const long long now_ = clock64(); acc_[k] += now_ - t_; t_ = now_; } } while (0)
 #else
 #define LM_T(k) do {} while (0)
@@ -179,27 +187,35 @@ __device__ unsigned long long g_lm_trace[148 * 8];
 template <bool FUSED>
 __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams p) {
 #ifdef WRS_TRACE
-    long long acc_[8] = {0, 0, 0, 0, 0, 0, 0, 0}, t_ = clock64();
+    long long acc_[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, t_ = clock64();
 #endif
     extern __shared__ __align__(16) unsigned char smem_raw[];
     LogmelSmem& sm = *reinterpret_cast<LogmelSmem*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-    // filterbank -> smem (once per CTA); the rows of P behind bin 200 stay zero (zero-padded band tails read them)
+    // tables -> smem (once per CTA); the rows of P behind bin 200 stay zero (zero-padded band tails read them)
     for (int i = tid; i < WRS_N_MELS; i += kThreads) { sm.lo[i] = p.bank->lo[i]; sm.n4[i] = p.bank->n4[i]; sm.off4[i] = p.bank->off4[i]; }
-    for (int i = tid; i < MelBank::kMaxPadded / 2; i += kThreads) sm.w4[i] = reinterpret_cast<const float4*>(p.bank->w2)[i];
+    for (int i = tid; i < MelBank::kMaxPadded; i += kThreads) sm.w[i] = p.bank->wp[i];
+    for (int i = tid; i < WRS_N_FFT; i += kThreads) sm.tab[i] = c_tab[i];
+    for (int i = tid; i < 16 * 13; i += kThreads) sm.tw[i] = c_tw[i];
     for (int i = tid; i < (kPRows - WRS_N_BINS) * 32; i += kThreads) sm.P[WRS_N_BINS * 32 + i] = make_float2(0.0f, 0.0f);
+    if (tid == 0) mbar_init(&sm.pcm_bar, 1);
+    __syncthreads();
 
     // slices are dealt round-robin; (seg, fs) of the current slice advance without divisions
     const int step_seg = (int)gridDim.x / p.slices_per_seg, step_sl = (int)gridDim.x % p.slices_per_seg;
     int seg = (int)blockIdx.x / p.slices_per_seg, sl = (int)blockIdx.x % p.slices_per_seg;
     // slices whose floor/scale is still to be applied, oldest first (fs < 0: empty)
-    int pend_seg[3] = {0, 0, 0}, pend_fs[3] = {-1, -1, -1};
+    int pend_seg[kPend], pend_fs[kPend];
+#pragma unroll
+    for (int k = 0; k < kPend; ++k) { pend_seg[k] = 0; pend_fs[k] = -1; }
     int post_seg = -1;                                   // segment of the slice whose "posted" count is still owed
+    unsigned pcm_parity = 0;                             // phase of pcm_bar the next bulk-copied tile completes
+    bool cur_bulk = false;                               // the current slice's tile arrives through pcm_bar
     if ((int)blockIdx.x < p.total_slices) {
-        float4 v[kStagePerWarp];
-        stage_load(p, seg, sl * kTW, warp, kWarps, lane, v);
-        stage_store(sm, warp, kWarps, lane, v);
+        cur_bulk = slice_is_interior(p, sl * kTW);
+        if (cur_bulk) { if (warp == 13 || warp == 14) stage_bulk(sm, p, seg, sl * kTW, lane, warp - 13); }
+        else stage_general(sm, p, seg, sl * kTW, tid);
     }
     __syncthreads();
 
@@ -209,24 +225,32 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
         int nseg = seg + step_seg, nsl = sl + step_sl;   // the slice after this one
         if (nsl >= p.slices_per_seg) { nsl -= p.slices_per_seg; ++nseg; }
         const bool has_next = slice + (int)gridDim.x < p.total_slices;
+        const bool next_bulk = has_next && slice_is_interior(p, nsl * kTW);
         if (tid == 0) sm.red_max = float_key(-INFINITY);
+        // has the oldest pending slice's segment completed?  The answer is asked for here and looked at in stage B, so
+        // that the round trip to L2 is off every warp's critical path.
+        int polled = 0;
+        if (FUSED && warp == 15 && lane == 0 && pend_fs[0] >= 0) polled = ld_acquire(p.seg_cnt + pend_seg[0]);
+        if (cur_bulk) { mbar_wait(&sm.pcm_bar, pcm_parity); pcm_parity ^= 1u; }
+        LM_T(7);
 
-        // ---- stage A: warp = t.  Frames lane and lane + 32 side by side.
+        // ---- stage A: 4 frame groups x 4 tap quads.  Lane (f8, tl): frames 8g+f8 and 8g+f8+32, taps 16m + 4tq + tl.
         {
-            // opaque copy: keeps the compiler from hoisting the 38 twiddle / window constants of this warp out of the
-            // slice loop, where they would sit in registers (and spill) through stages B and C
-            int t = warp;
-            asm volatile("" : "+r"(t));
+            // opaque copy: keeps the compiler from hoisting this thread's 25 tap offsets / window values / twiddles out
+            // of the slice loop, where they would sit in registers (and spill) through stages B and C
+            int wv = warp;
+            asm volatile("" : "+r"(wv));
+            const int g = wv & 3, t = (wv >> 2) * 4 + (lane >> 3), fp = 8 * g + (lane & 7);
+            const float* src = sm.pcm + fp * kPitch;
             f32x2 v[25];
 #pragma unroll
             for (int m = 0; m < 25; ++m) {
-                const TabEntry e = c_tab[16 * m + t];
-                const float* src = sm.pcmT + e.aoff + lane;
-                v[m] = pack2(src[0] * e.win, src[32] * e.win);
+                const TabEntry e = sm.tab[16 * m + t];
+                v[m] = mul_(pack2(src[e.off], src[e.off + 32 * kPitch]), pack2(e.win, e.win));
             }
             cx<f32x2> y[13];
             rdft25(v, y);
-            float4* dst = sm.Y + (t * 13) * 32 + lane;
+            float4* dst = sm.Y + (t * 13) * 32 + fp;
             {
                 float a, b, c, d;
                 unpack2(y[0].re, a, b); unpack2(y[0].im, c, d);
@@ -234,8 +258,8 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
             }
 #pragma unroll
             for (int q = 1; q < 13; ++q) {
-                const TwEntry w = c_tw[t * 13 + q];
-                const f32x2 wr = pack2(w.wr.x, w.wr.y), wi = pack2(w.wi.x, w.wi.y), nwi = pack2(w.nwi.x, w.nwi.y);
+                const float2 w = sm.tw[t * 13 + q];
+                const f32x2 wr = pack2(w.x, w.x), wi = pack2(w.y, w.y), nwi = pack2(-w.y, -w.y);
                 const f32x2 re = fma_(y[q].im, nwi, mul_(y[q].re, wr));
                 const f32x2 im = fma_(y[q].re, wi, mul_(y[q].im, wr));
                 float a, b, c, d;
@@ -246,8 +270,9 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
         __syncthreads();
         LM_T(0);
 
-        // ---- stage B: warp = q < 13.  Meanwhile one lane of warp 15 asks whether the oldest pending slice's segment
-        //      has completed (all its slices have posted their maxima) and, if so, fetches the segment's floor.
+        // ---- stage B: warp = q < 13, lane = frame pair (lane, lane + 32).  The tile is free now: warp 14 starts the
+        //      next slice's copy.  One lane of warp 15 counts the previous slice as posted and asks whether the oldest
+        //      pending slice's segment has completed (all its slices have posted their maxima).
         if (warp < 13) {
             const int q = warp;
             cx<f32x2> z[16];
@@ -265,13 +290,14 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
                     sm.P[stageb_bin(q, s) * 32 + lane] = make_float2(a, b);
                 }
             }
+        } else if (warp < 15) {
+            if (next_bulk) stage_bulk(sm, p, nseg, nsl * kTW, lane, warp - 13);
         } else if (FUSED && warp == 15 && lane == 0) {
             // the previous slice's raw rows and maximum were issued before the barrier above: one fence by this lane
             // orders all of them before the count that tells the other CTAs this slice has posted
             if (post_seg >= 0) { fence_acq_rel(); atomicAdd(p.seg_cnt + post_seg, 1); }
             int ready = 0;
-            if (pend_fs[0] >= 0 && *(volatile int*)(p.seg_cnt + pend_seg[0]) >= p.slices_per_seg) {
-                fence_acq_rel();
+            if (pend_fs[0] >= 0 && polled >= p.slices_per_seg) {
                 sm.seg_floor = key_float(*(volatile int*)(p.seg_max + pend_seg[0])) - 8.0f;
                 ready = 1;
             }
@@ -280,16 +306,14 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
         __syncthreads();
         LM_T(1);
 
-        // ---- stage C: banded mel projection (src/audio.rs:252), clamp + log10 (:254).  Its arithmetic hides two
-        //      streams of global traffic issued up front: the next slice's PCM (into the tile stage A has left) and the
-        //      raw log-mel of the pending slice whose floor has just become known.
+        // ---- stage C: banded mel projection (src/audio.rs:252), clamp + log10 (:254).  Its arithmetic hides the
+        //      raw log-mel of the pending slice whose floor has just become known (read back from L2 up front).
         const bool fin = FUSED && sm.fin_ready != 0;
         const int fseg = pend_seg[0], ffs = pend_fs[0];
         const int fnf4 = fin ? (min(kTW, p.n_frames - ffs) >> 2) : 0;
         float* __restrict__ foutp = p.out + ((int64_t)fseg * WRS_N_MELS) * p.n_frames + ffs;
         const bool fvec = p.vec_out != 0;                // n_frames % 4 == 0 and 16-byte aligned rows
-        float4 nxt[kStagePerWarp], raw[kTilePerThread];
-        if (has_next) stage_load(p, nseg, nsl * kTW, warp, kWarps, lane, nxt);
+        float4 raw[kTilePerThread];
         if (fin && fvec) {
 #pragma unroll
             for (int k = 0; k < kTilePerThread; ++k) {
@@ -298,7 +322,14 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
                     raw[k] = __ldcg(reinterpret_cast<const float4*>(foutp + (int64_t)(idx >> 4) * p.n_frames + 4 * (idx & 15)));
             }
         }
-        LM_T(7);
+        LM_T(2);
+        if (has_next && !next_bulk) {
+            stage_general(sm, p, nseg, nsl * kTW, tid);
+            LM_T(8);
+#ifdef WRS_TRACE
+            if (tid == 0) acc_[9] += 1;
+#endif
+        }
         float lmax = -INFINITY;
         {
             const bool ok0 = lane < nf, ok1 = lane + 32 < nf;
@@ -306,17 +337,17 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
             for (int i = 0; i < WRS_N_MELS / kWarps; ++i) {
                 const int m = i * kWarps + warp;
                 const int n4 = sm.n4[m];
-                const float4* w = sm.w4 + (sm.off4[m] >> 1);
+                const float4* w = reinterpret_cast<const float4*>(sm.w + sm.off4[m]);
                 const float2* pp = sm.P + sm.lo[m] * 32 + lane;
                 f32x2 acc0, acc1;
                 zero_(acc0); zero_(acc1);
                 for (int j = 0; j < n4; j += 4) {
-                    const float4 wa = w[j >> 1], wb = w[(j >> 1) + 1];
+                    const float4 wa = w[j >> 2];
                     const float2 p0 = pp[j * 32], p1 = pp[j * 32 + 32], p2 = pp[j * 32 + 64], p3 = pp[j * 32 + 96];
-                    acc0 = fma_(pack2(p0.x, p0.y), pack2(wa.x, wa.y), acc0);
-                    acc1 = fma_(pack2(p1.x, p1.y), pack2(wa.z, wa.w), acc1);
-                    acc0 = fma_(pack2(p2.x, p2.y), pack2(wb.x, wb.y), acc0);
-                    acc1 = fma_(pack2(p3.x, p3.y), pack2(wb.z, wb.w), acc1);
+                    acc0 = fma_(pack2(p0.x, p0.y), pack2(wa.x, wa.x), acc0);
+                    acc1 = fma_(pack2(p1.x, p1.y), pack2(wa.y, wa.y), acc1);
+                    acc0 = fma_(pack2(p2.x, p2.y), pack2(wa.z, wa.z), acc0);
+                    acc1 = fma_(pack2(p3.x, p3.y), pack2(wa.w, wa.w), acc1);
                 }
                 float a0, a1;
                 unpack2(add_(acc0, acc1), a0, a1);
@@ -326,8 +357,6 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
                 if (ok1) lmax = fmaxf(lmax, v1);
             }
         }
-        LM_T(2);
-        if (has_next) stage_store(sm, warp, kWarps, lane, nxt);
         LM_T(3);
         if (fin) {                                       // out = (max(raw, segmax - 8) + 4) / 4   (src/audio.rs:256-258)
             const float fl = sm.seg_floor;
@@ -350,9 +379,9 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
                     *q = (fmaxf(__ldcg(q), fl) + 4.0f) * 0.25f;
                 }
             }
-            pend_seg[0] = pend_seg[1]; pend_fs[0] = pend_fs[1];
-            pend_seg[1] = pend_seg[2]; pend_fs[1] = pend_fs[2];
-            pend_fs[2] = -1;
+#pragma unroll
+            for (int k = 0; k + 1 < kPend; ++k) { pend_seg[k] = pend_seg[k + 1]; pend_fs[k] = pend_fs[k + 1]; }
+            pend_fs[kPend - 1] = -1;
         }
         // ---- per-slice max -> per-segment max (src/audio.rs:256 `log_spec.max()`)
 #pragma unroll
@@ -362,7 +391,8 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
         __syncthreads();
         LM_T(5);
 
-        // ---- raw log10(mel) of the [80][nf] tile -> HBM, coalesced
+        // ---- raw log10(mel) of the [80][nf] tile -> HBM, coalesced.  No barrier follows: the next stage A touches
+        //      neither the tile nor red_max, and two barriers pass before stage C writes them again.
         float* __restrict__ outp = p.out + ((int64_t)seg * WRS_N_MELS) * p.n_frames + fs;
         if (p.vec_out) {
             const int nf4 = nf >> 2;
@@ -382,31 +412,31 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
         if (tid == 0) atomicMax(p.seg_max + seg, sm.red_max);
         if (FUSED) {
             post_seg = seg;                              // counted by warp 15 during the next stage B
-            if (pend_fs[2] >= 0) {                       // queue full (a straggling segment): wait for the oldest --
+            if (pend_fs[kPend - 1] >= 0) {               // queue full (a straggling segment): wait for the oldest --
                 __syncthreads();                         // after this slice has been counted, so that two CTAs
                 if (tid == 0) { fence_acq_rel(); atomicAdd(p.seg_cnt + seg, 1); }   // can never wait on each other
                 post_seg = -1;
                 finalize_slice_blocking(sm, p, pend_seg[0], pend_fs[0], tid);
-                pend_seg[0] = pend_seg[1]; pend_fs[0] = pend_fs[1];
-                pend_seg[1] = pend_seg[2]; pend_fs[1] = pend_fs[2];
-                pend_fs[2] = -1;
+#pragma unroll
+                for (int k = 0; k + 1 < kPend; ++k) { pend_seg[k] = pend_seg[k + 1]; pend_fs[k] = pend_fs[k + 1]; }
+                pend_fs[kPend - 1] = -1;
             }
-            const int slot = pend_fs[0] < 0 ? 0 : (pend_fs[1] < 0 ? 1 : 2);
-            if (slot == 0) { pend_seg[0] = seg; pend_fs[0] = fs; }
-            else if (slot == 1) { pend_seg[1] = seg; pend_fs[1] = fs; }
-            else { pend_seg[2] = seg; pend_fs[2] = fs; }
+            bool placed = false;
+#pragma unroll
+            for (int k = 0; k < kPend; ++k)
+                if (!placed && pend_fs[k] < 0) { pend_seg[k] = seg; pend_fs[k] = fs; placed = true; }
         }
         LM_T(6);
-        seg = nseg; sl = nsl;
+        seg = nseg; sl = nsl; cur_bulk = next_bulk;
     }
 #ifdef WRS_TRACE
-    if (tid == 0) for (int k = 0; k < 8; ++k) g_lm_trace[blockIdx.x * 8 + k] = acc_[k];
+    if (tid == 0) for (int k = 0; k < 12; ++k) g_lm_trace[blockIdx.x * 12 + k] = acc_[k];
 #endif
     if (FUSED) {
         __syncthreads();
         if (tid == 0 && post_seg >= 0) { fence_acq_rel(); atomicAdd(p.seg_cnt + post_seg, 1); }
 #pragma unroll
-        for (int k = 0; k < 3; ++k)
+        for (int k = 0; k < kPend; ++k)
             if (pend_fs[k] >= 0) finalize_slice_blocking(sm, p, pend_seg[k], pend_fs[k], tid);
     }
 }
@@ -447,17 +477,16 @@ static int init_tables(wrs_ctx* ctx) {
     if (ctx->device < 64 && g_tables_ready[ctx->device]) return WRS_OK;
     const double PI = 3.14159265358979323846;
     static TabEntry tab[WRS_N_FFT];
-    static TwEntry tw[16 * 13];
+    static float2 tw[16 * 13];
     for (int n = 0; n < WRS_N_FFT; ++n) {
-        const int u = n + 120;   // frame f, sample n  ->  row f-2+u/160 of the tile, column u%160
-        tab[n].aoff = (u % WRS_HOP_LENGTH) * kNFP + (u / WRS_HOP_LENGTH);
+        const int u = n + 120;   // frame f, tap n  ->  row f + u/160 of the tile (row 0 = frame row fs-2), column u%160
+        tab[n].off = (u / WRS_HOP_LENGTH) * kPitch + (u % WRS_HOP_LENGTH);
         tab[n].win = (float)(0.5 - 0.5 * std::cos(2.0 * PI * n / WRS_N_FFT));
     }
     for (int t = 0; t < 16; ++t)
         for (int q = 0; q < 13; ++q) {
             const double a = -2.0 * PI * (double)(t * q) / 400.0;
-            const float c = (float)std::cos(a), s = (float)std::sin(a);
-            tw[t * 13 + q] = TwEntry{make_float2(c, c), make_float2(s, s), make_float2(-s, -s)};
+            tw[t * 13 + q] = make_float2((float)std::cos(a), (float)std::sin(a));
         }
     WRS_CUDA(ctx, cudaMemcpyToSymbol(c_tab, tab, sizeof(tab)));
     WRS_CUDA(ctx, cudaMemcpyToSymbol(c_tw, tw, sizeof(tw)));

@@ -18,11 +18,11 @@ struct MelBank {
     int off[WRS_N_MELS];
     static constexpr int kMaxPadded = 768;
     float w[kMaxWeights];
-    // the same bands padded with zero weights to multiples of four, every weight twice {w, w}: the broadcast operand of a
-    // packed two-frame FMA.  Row m: n4[m] weights from off4[m] (both multiples of 4).
+    // the same bands padded with zero weights to multiples of four (the mel loop takes four bins per step, a weight is
+    // the scalar operand of a packed two-frame FMA).  Row m: n4[m] weights from off4[m] (both multiples of 4).
     int n4[WRS_N_MELS];
     int off4[WRS_N_MELS];
-    float w2[2 * kMaxPadded];
+    float wp[kMaxPadded];
     int total;
 };
 
