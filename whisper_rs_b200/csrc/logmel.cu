@@ -58,7 +58,6 @@ struct LogmelSmem {
     float pcm[kRows * kPitch];                       // 43 952 B
     float4 Y[16 * 13 * 32];                          // 106 496 B
     float2 P[kPRows * 32];                           // 52 224 B
-    float tile[WRS_N_MELS * kTW];                    // 20 480 B
     float w[MelBank::kMaxPadded];                    // 3 072 B: in-band filter weights, bands zero-padded to multiples of 4
     TabEntry tab[WRS_N_FFT];                         // 3 200 B
     float2 tw[16 * 13];                              // 1 664 B
@@ -145,6 +144,43 @@ __device__ __forceinline__ int ld_acquire(const int* p) {
 }
 __device__ __forceinline__ void fence_acq_rel() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
 
+// out = (max(raw, segmax - 8) + 4) / 4 (src/audio.rs:256-258) in place on one [80][nf] slice, by NT threads (t = 0..NT-1).
+// Aligned rows: all of a thread's 16-byte loads go out before the first store.
+template <int NT>
+__device__ __forceinline__ void floor_scale_slice(float* __restrict__ outp, int64_t n_frames, int nf, float fl, int t, bool vec) {
+    if (vec) {
+        constexpr int kPer = (WRS_N_MELS * (kTW / 4) + NT - 1) / NT, kBatch = kPer < 7 ? kPer : 7;
+        const int nf4 = nf >> 2;
+#pragma unroll 1
+        for (int k0 = 0; k0 < kPer; k0 += kBatch) {
+            float4 v[kBatch];
+#pragma unroll
+            for (int k = 0; k < kBatch; ++k) {
+                const int idx = t + (k0 + k) * NT;
+                if (idx < WRS_N_MELS * (kTW / 4) && (idx & 15) < nf4)
+                    v[k] = __ldcg(reinterpret_cast<const float4*>(outp + (int64_t)(idx >> 4) * n_frames + 4 * (idx & 15)));
+            }
+#pragma unroll
+            for (int k = 0; k < kBatch; ++k) {
+                const int idx = t + (k0 + k) * NT;
+                if (idx < WRS_N_MELS * (kTW / 4) && (idx & 15) < nf4) {
+                    float4 x = v[k];
+                    x.x = (fmaxf(x.x, fl) + 4.0f) * 0.25f; x.y = (fmaxf(x.y, fl) + 4.0f) * 0.25f;
+                    x.z = (fmaxf(x.z, fl) + 4.0f) * 0.25f; x.w = (fmaxf(x.w, fl) + 4.0f) * 0.25f;
+                    *reinterpret_cast<float4*>(outp + (int64_t)(idx >> 4) * n_frames + 4 * (idx & 15)) = x;
+                }
+            }
+        }
+    } else {
+        const int d = max(nf, 1);
+        for (int idx = t; idx < WRS_N_MELS * nf; idx += NT) {
+            const int m = idx / d, c = idx - m * d;
+            float* q = outp + (int64_t)m * n_frames + c;
+            *q = (fmaxf(__ldcg(q), fl) + 4.0f) * 0.25f;
+        }
+    }
+}
+
 // Blocking floor + scale of one slice in place: out = (max(raw, segmax - 8) + 4) / 4 (src/audio.rs:256-258).  Only the
 // drain at the end of the kernel (and a full pending queue) comes here; the steady state hides it inside the slice loop.
 __device__ __forceinline__ void finalize_slice_blocking(LogmelSmem& sm, const LogmelParams& p, int seg, int fs, int tid) {
@@ -162,19 +198,12 @@ __device__ __forceinline__ void finalize_slice_blocking(LogmelSmem& sm, const Lo
         sm.seg_floor = key_float(*(volatile int*)(p.seg_max + seg)) - 8.0f;
     }
     __syncthreads();
-    const float fl = sm.seg_floor;
-    float* __restrict__ outp = p.out + ((int64_t)seg * WRS_N_MELS) * p.n_frames + fs;
-    for (int idx = tid; idx < WRS_N_MELS * nf; idx += kThreads) {
-        const int m = idx / nf, c = idx - m * nf;
-        float* q = outp + (int64_t)m * p.n_frames + c;
-        *q = (fmaxf(__ldcg(q), fl) + 4.0f) * 0.25f;
-    }
+    floor_scale_slice<kThreads>(p.out + ((int64_t)seg * WRS_N_MELS) * p.n_frames + fs, p.n_frames, nf, sm.seg_floor, tid, p.vec_out != 0);
     __syncthreads();
 }
 
 
 constexpr int kPend = 4;              // slices a CTA may have waiting for their segment's maximum
-constexpr int kTilePerThread = (WRS_N_MELS * (kTW / 4) + kThreads - 1) / kThreads;   // float4 of a [80][64] tile per thread: 3
 
 #ifdef WRS_TRACE
 // investigation aid (tools/debug/logmel_trace.py): per-CTA cycles spent in each phase of the slice loop
@@ -212,6 +241,7 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
     int post_seg = -1;                                   // segment of the slice whose "posted" count is still owed
     unsigned pcm_parity = 0;                             // phase of pcm_bar the next bulk-copied tile completes
     bool cur_bulk = false;                               // the current slice's tile arrives through pcm_bar
+    const bool ovec = p.vec_out != 0;                    // output rows 16-byte aligned, n_frames % 4 == 0: rows move as bulk copies
     if ((int)blockIdx.x < p.total_slices) {
         cur_bulk = slice_is_interior(p, sl * kTW);
         if (cur_bulk) { if (warp == 13 || warp == 14) stage_bulk(sm, p, seg, sl * kTW, lane, warp - 13); }
@@ -231,6 +261,7 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
         // that the round trip to L2 is off every warp's critical path.
         int polled = 0;
         if (FUSED && warp == 15 && lane == 0 && pend_fs[0] >= 0) polled = ld_acquire(p.seg_cnt + pend_seg[0]);
+        LM_T(10);
         if (cur_bulk) { mbar_wait(&sm.pcm_bar, pcm_parity); pcm_parity ^= 1u; }
         LM_T(7);
 
@@ -290,33 +321,38 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
                     sm.P[stageb_bin(q, s) * 32 + lane] = make_float2(a, b);
                 }
             }
-        } else if (warp < 15) {
-            if (next_bulk) stage_bulk(sm, p, nseg, nsl * kTW, lane, warp - 13);
-        } else if (FUSED && warp == 15 && lane == 0) {
-            // the previous slice's raw rows and maximum were issued before the barrier above: one fence by this lane
-            // orders all of them before the count that tells the other CTAs this slice has posted
-            if (post_seg >= 0) { fence_acq_rel(); atomicAdd(p.seg_cnt + post_seg, 1); }
-            int ready = 0;
-            if (pend_fs[0] >= 0 && polled >= p.slices_per_seg) {
-                sm.seg_floor = key_float(*(volatile int*)(p.seg_max + pend_seg[0])) - 8.0f;
-                ready = 1;
+        } else {
+            // the three warps without a bin: 13 and 14 start the next slice's copy (the tile is free now); one lane of
+            // 15 counts the previous slice as posted and looks at the poll
+            if (warp < 15) {
+                if (next_bulk) stage_bulk(sm, p, nseg, nsl * kTW, lane, warp - 13);
+            } else if (FUSED && lane == 0) {
+                // the previous slice's raw rows and maximum were issued before the barrier above: one fence by this
+                // lane orders all of them before the count that tells the other CTAs this slice has posted
+                if (post_seg >= 0) { fence_acq_rel(); atomicAdd(p.seg_cnt + post_seg, 1); }
+                int ready = 0;
+                if (pend_fs[0] >= 0 && polled >= p.slices_per_seg) {
+                    sm.seg_floor = key_float(*(volatile int*)(p.seg_max + pend_seg[0])) - 8.0f;
+                    ready = 1;
+                }
+                sm.fin_ready = ready;
             }
-            sm.fin_ready = ready;
         }
         __syncthreads();
         LM_T(1);
 
-        // ---- stage C: banded mel projection (src/audio.rs:252), clamp + log10 (:254).  Its arithmetic hides the
-        //      raw log-mel of the pending slice whose floor has just become known (read back from L2 up front).
+        // ---- stage C: banded mel projection (src/audio.rs:252), clamp + log10 (:254), raw rows -> HBM
         const bool fin = FUSED && sm.fin_ready != 0;
         const int fseg = pend_seg[0], ffs = pend_fs[0];
-        const int fnf4 = fin ? (min(kTW, p.n_frames - ffs) >> 2) : 0;
+        const int fnf = fin ? min(kTW, p.n_frames - ffs) : 0;
         float* __restrict__ foutp = p.out + ((int64_t)fseg * WRS_N_MELS) * p.n_frames + ffs;
-        const bool fvec = p.vec_out != 0;                // n_frames % 4 == 0 and 16-byte aligned rows
-        float4 raw[kTilePerThread];
-        if (fin && fvec) {
+        // the pending slice whose floor has just become known: its raw rows come back from L2 behind the mel arithmetic
+        constexpr int kPer = (WRS_N_MELS * (kTW / 4) + kThreads - 1) / kThreads;   // float4 of a [80][64] slice per thread: 3
+        const int fnf4 = fnf >> 2;
+        float4 raw[kPer];
+        if (fin && ovec) {
 #pragma unroll
-            for (int k = 0; k < kTilePerThread; ++k) {
+            for (int k = 0; k < kPer; ++k) {
                 const int idx = tid + k * kThreads;
                 if (idx < WRS_N_MELS * (kTW / 4) && (idx & 15) < fnf4)
                     raw[k] = __ldcg(reinterpret_cast<const float4*>(foutp + (int64_t)(idx >> 4) * p.n_frames + 4 * (idx & 15)));
@@ -331,6 +367,7 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
 #endif
         }
         float lmax = -INFINITY;
+        float* __restrict__ outp = p.out + ((int64_t)seg * WRS_N_MELS) * p.n_frames + fs;
         {
             const bool ok0 = lane < nf, ok1 = lane + 32 < nf;
 #pragma unroll 1
@@ -352,17 +389,18 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
                 float a0, a1;
                 unpack2(add_(acc0, acc1), a0, a1);
                 const float v0 = __log2f(fmaxf(a0, 1e-10f)) * kLog10Of2, v1 = __log2f(fmaxf(a1, 1e-10f)) * kLog10Of2;
-                sm.tile[m * kTW + lane] = v0; sm.tile[m * kTW + 32 + lane] = v1;
-                if (ok0) lmax = fmaxf(lmax, v0);
-                if (ok1) lmax = fmaxf(lmax, v1);
+                // raw row -> HBM straight from the registers, 128 contiguous bytes per store (src/audio.rs:254)
+                float* __restrict__ orow = outp + (int64_t)m * p.n_frames + lane;
+                if (ok0) { orow[0] = v0; lmax = fmaxf(lmax, v0); }
+                if (ok1) { orow[32] = v1; lmax = fmaxf(lmax, v1); }
             }
         }
         LM_T(3);
-        if (fin) {                                       // out = (max(raw, segmax - 8) + 4) / 4   (src/audio.rs:256-258)
-            const float fl = sm.seg_floor;
-            if (fvec) {
+        if (fin) {
+            const float fl = sm.seg_floor;               // out = (max(raw, segmax - 8) + 4) / 4   (src/audio.rs:256-258)
+            if (ovec) {
 #pragma unroll
-                for (int k = 0; k < kTilePerThread; ++k) {
+                for (int k = 0; k < kPer; ++k) {
                     const int idx = tid + k * kThreads;
                     if (idx < WRS_N_MELS * (kTW / 4) && (idx & 15) < fnf4) {
                         float4 v = raw[k];
@@ -372,12 +410,7 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
                     }
                 }
             } else {
-                const int fnf = min(kTW, p.n_frames - ffs);
-                for (int idx = tid; idx < WRS_N_MELS * fnf; idx += kThreads) {
-                    const int m = idx / fnf, c = idx - m * fnf;
-                    float* q = foutp + (int64_t)m * p.n_frames + c;
-                    *q = (fmaxf(__ldcg(q), fl) + 4.0f) * 0.25f;
-                }
+                floor_scale_slice<kThreads>(foutp, p.n_frames, fnf, fl, tid, false);   // unaligned output
             }
 #pragma unroll
             for (int k = 0; k + 1 < kPend; ++k) { pend_seg[k] = pend_seg[k + 1]; pend_fs[k] = pend_fs[k + 1]; }
@@ -391,24 +424,7 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
         __syncthreads();
         LM_T(5);
 
-        // ---- raw log10(mel) of the [80][nf] tile -> HBM, coalesced.  No barrier follows: the next stage A touches
-        //      neither the tile nor red_max, and two barriers pass before stage C writes them again.
-        float* __restrict__ outp = p.out + ((int64_t)seg * WRS_N_MELS) * p.n_frames + fs;
-        if (p.vec_out) {
-            const int nf4 = nf >> 2;
-#pragma unroll
-            for (int k = 0; k < kTilePerThread; ++k) {
-                const int idx = tid + k * kThreads;
-                if (idx < WRS_N_MELS * (kTW / 4) && (idx & 15) < nf4)
-                    *reinterpret_cast<float4*>(outp + (int64_t)(idx >> 4) * p.n_frames + 4 * (idx & 15)) =
-                        *reinterpret_cast<const float4*>(sm.tile + 4 * idx);
-            }
-        } else {
-            for (int idx = tid; idx < WRS_N_MELS * nf; idx += kThreads) {
-                const int m = idx / nf, c = idx - m * nf;
-                outp[(int64_t)m * p.n_frames + c] = sm.tile[m * kTW + c];
-            }
-        }
+        // No barrier follows: the next stage A touches nothing stage C reads, and red_max is only reset by thread 0.
         if (tid == 0) atomicMax(p.seg_max + seg, sm.red_max);
         if (FUSED) {
             post_seg = seg;                              // counted by warp 15 during the next stage B
