@@ -109,31 +109,38 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
 }
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-// The tile of slice (seg, fs) is rows fs-2 .. fs+64 of the segment cut into 160-sample rows.  Away from the segment's
-// ends (no reflection, nothing ragged) and with 16-byte aligned PCM it is one contiguous range of the input.
-__device__ __forceinline__ bool slice_is_interior(const LogmelParams& p, int fs) {
-    return p.vec_in != 0 && fs >= 2 && (int64_t)WRS_HOP_LENGTH * (fs - 2 + kRows) <= (int64_t)p.n_samples;
+// The tile of slice (seg, fs) is rows fs-2 .. fs+64 of the segment cut into 160-sample rows.  Rows that lie entirely
+// inside the segment are one contiguous range of the input and move as bulk copies (16-byte aligned PCM); the rows
+// in front of the segment (reflection, first slice) and at or behind its end (last slice) are filled element-wise.
+struct TilePlan { int r_lo, r_hi; };                 // plain rows [r_lo, r_hi)
+__device__ __forceinline__ TilePlan tile_plan(const LogmelParams& p, int fs) {
+    TilePlan t;
+    t.r_lo = max(0, 2 - fs);
+    t.r_hi = p.vec_in != 0 ? max(t.r_lo, min(kRows, p.n_samples / WRS_HOP_LENGTH - fs + 2)) : t.r_lo;
+    return t;
 }
-// 67 row copies of 640 B, completion counted in bytes on the tile's mbarrier.  Two warps share the issue (part 0 also
-// makes the phase's single arrival and announces the byte count; a copy that completes before that only drives the
-// pending byte count negative for a moment).
-__device__ __forceinline__ void stage_bulk(LogmelSmem& sm, const LogmelParams& p, int seg, int fs, int lane, int part) {
+// Row copies of 640 B, completion counted in bytes on the tile's mbarrier.  Two warps share the issue (part 0 also makes
+// the phase's single arrival and announces the byte count; a copy that completes before that only drives the pending
+// byte count negative for a moment).
+__device__ __forceinline__ void stage_bulk(LogmelSmem& sm, const LogmelParams& p, int seg, int fs, TilePlan t, int lane, int part) {
     const float* __restrict__ src = p.pcm + (int64_t)seg * p.seg_stride + (int64_t)WRS_HOP_LENGTH * (fs - 2);
-    constexpr int kHalf = (kRows + 1) / 2;
+    const int nb = t.r_hi - t.r_lo, half = (nb + 1) >> 1;
     fence_proxy_async();                             // the tile was last touched by ordinary loads/stores
-    if (part == 0 && lane == 0) mbar_expect_tx(&sm.pcm_bar, kRows * WRS_HOP_LENGTH * (unsigned)sizeof(float));
-    const int r0 = part * kHalf, r1 = min(kRows, r0 + kHalf);
+    if (part == 0 && lane == 0) mbar_expect_tx(&sm.pcm_bar, (unsigned)(nb * WRS_HOP_LENGTH * sizeof(float)));
+    const int r0 = t.r_lo + part * half, r1 = min(t.r_hi, r0 + half);
     for (int r = r0 + lane; r < r1; r += 32)
         bulk_g2s(sm.pcm + r * kPitch, src + r * WRS_HOP_LENGTH, WRS_HOP_LENGTH * (unsigned)sizeof(float), &sm.pcm_bar);
 }
-// the segment's first and last slices (reflection, ragged end) and unaligned input: element-wise, whole CTA
-__device__ __forceinline__ void stage_general(LogmelSmem& sm, const LogmelParams& p, int seg, int fs, int tid) {
+// the rows outside [r_lo, r_hi): element-wise with reflection at both ends (src/audio.rs:236 center = true), whole CTA
+__device__ __forceinline__ void stage_general(LogmelSmem& sm, const LogmelParams& p, int seg, int fs, TilePlan t, int tid) {
     const float* __restrict__ segp = p.pcm + (int64_t)seg * p.seg_stride;
     const int base = WRS_HOP_LENGTH * (fs - 2);
+    const int n1 = t.r_lo * WRS_HOP_LENGTH, total = n1 + (kRows - t.r_hi) * WRS_HOP_LENGTH;
 #pragma unroll 4
-    for (int idx = tid; idx < kRows * WRS_HOP_LENGTH; idx += kThreads) {
-        const int r = idx / WRS_HOP_LENGTH, c = idx - r * WRS_HOP_LENGTH;
-        sm.pcm[r * kPitch + c] = load_reflect(segp, base + idx, p.n_samples);
+    for (int idx = tid; idx < total; idx += kThreads) {
+        const int e = idx < n1 ? idx : idx - n1 + t.r_hi * WRS_HOP_LENGTH;
+        const int r = e / WRS_HOP_LENGTH, c = e - r * WRS_HOP_LENGTH;
+        sm.pcm[r * kPitch + c] = load_reflect(segp, base + e, p.n_samples);
     }
 }
 
@@ -243,9 +250,10 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
     bool cur_bulk = false;                               // the current slice's tile arrives through pcm_bar
     const bool ovec = p.vec_out != 0;                    // output rows 16-byte aligned, n_frames % 4 == 0: rows move as bulk copies
     if ((int)blockIdx.x < p.total_slices) {
-        cur_bulk = slice_is_interior(p, sl * kTW);
-        if (cur_bulk) { if (warp == 13 || warp == 14) stage_bulk(sm, p, seg, sl * kTW, lane, warp - 13); }
-        else stage_general(sm, p, seg, sl * kTW, tid);
+        const TilePlan t = tile_plan(p, sl * kTW);
+        cur_bulk = t.r_hi > t.r_lo;
+        if (cur_bulk && (warp == 13 || warp == 14)) stage_bulk(sm, p, seg, sl * kTW, t, lane, warp - 13);
+        stage_general(sm, p, seg, sl * kTW, t, tid);
     }
     __syncthreads();
 
@@ -255,7 +263,9 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
         int nseg = seg + step_seg, nsl = sl + step_sl;   // the slice after this one
         if (nsl >= p.slices_per_seg) { nsl -= p.slices_per_seg; ++nseg; }
         const bool has_next = slice + (int)gridDim.x < p.total_slices;
-        const bool next_bulk = has_next && slice_is_interior(p, nsl * kTW);
+        const TilePlan nplan = tile_plan(p, nsl * kTW);
+        const bool next_bulk = has_next && nplan.r_hi > nplan.r_lo;
+        const bool next_edge = has_next && nplan.r_hi - nplan.r_lo < kRows;
         if (tid == 0) sm.red_max = float_key(-INFINITY);
         // has the oldest pending slice's segment completed?  The answer is asked for here and looked at in stage B, so
         // that the round trip to L2 is off every warp's critical path.
@@ -325,7 +335,7 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
             // the three warps without a bin: 13 and 14 start the next slice's copy (the tile is free now); one lane of
             // 15 counts the previous slice as posted and looks at the poll
             if (warp < 15) {
-                if (next_bulk) stage_bulk(sm, p, nseg, nsl * kTW, lane, warp - 13);
+                if (next_bulk) stage_bulk(sm, p, nseg, nsl * kTW, nplan, lane, warp - 13);
             } else if (FUSED && lane == 0) {
                 // the previous slice's raw rows and maximum were issued before the barrier above: one fence by this
                 // lane orders all of them before the count that tells the other CTAs this slice has posted
@@ -359,8 +369,8 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
             }
         }
         LM_T(2);
-        if (has_next && !next_bulk) {
-            stage_general(sm, p, nseg, nsl * kTW, tid);
+        if (next_edge) {
+            stage_general(sm, p, nseg, nsl * kTW, nplan, tid);
             LM_T(8);
 #ifdef WRS_TRACE
             if (tid == 0) acc_[9] += 1;
