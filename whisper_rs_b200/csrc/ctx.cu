@@ -121,6 +121,12 @@ void wrs_ctx_destroy(wrs_ctx* ctx) {
     cudaFree(ctx->d_stage_in);
     cudaFree(ctx->d_stage_out);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+    if (ctx->h2d_stream) cudaStreamDestroy(ctx->h2d_stream);
+    if (ctx->d2h_stream) cudaStreamDestroy(ctx->d2h_stream);
+    for (int i = 0; i < wrs_ctx::kHostChunks; ++i) {
+        if (ctx->ev_in[i]) cudaEventDestroy(ctx->ev_in[i]);
+        if (ctx->ev_done[i]) cudaEventDestroy(ctx->ev_done[i]);
+    }
     delete ctx;
 }
 

@@ -640,11 +640,38 @@ int wrs_logmel_batch_host(wrs_ctx* ctx, const float* pcm_host, int64_t n_segment
         WRS_CUDA(ctx, cudaMalloc(&ctx->d_stage_out, out_bytes));
         ctx->stage_out_bytes = out_bytes;
     }
+    // Three streams: chunk c is copied in while chunk c-1 is computed and chunk c-2 is copied out, so that a large
+    // batch costs max(copy-in, copy-out) over PCIe (full duplex) instead of their sum; pinned host buffers make the
+    // copies truly asynchronous.  Chunks are whole segments.
+    if (!ctx->h2d_stream) {
+        WRS_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->h2d_stream, cudaStreamNonBlocking));
+        WRS_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->d2h_stream, cudaStreamNonBlocking));
+        for (int i = 0; i < wrs_ctx::kHostChunks; ++i) {
+            WRS_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_in[i], cudaEventDisableTiming));
+            WRS_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_done[i], cudaEventDisableTiming));
+        }
+    }
+    const int64_t per_chunk = std::max<int64_t>(4, (n_segments + wrs_ctx::kHostChunks - 1) / wrs_ctx::kHostChunks);
+    const int64_t out_per_seg = (int64_t)WRS_N_MELS * n_frames;
     cudaStream_t s = ctx->own_stream;
-    WRS_CUDA(ctx, cudaMemcpyAsync(ctx->d_stage_in, pcm_host, in_bytes, cudaMemcpyHostToDevice, s));
-    int rc = wrs_logmel_batch(ctx, ctx->d_stage_in, n_segments, n_samples, seg_stride, ctx->d_stage_out, s);
-    if (rc != WRS_OK) return rc;
-    WRS_CUDA(ctx, cudaMemcpyAsync(out_host, ctx->d_stage_out, out_bytes, cudaMemcpyDeviceToHost, s));
+    int c = 0;
+    for (int64_t s0 = 0; s0 < n_segments; s0 += per_chunk, ++c) {
+        const int64_t ns = std::min(per_chunk, n_segments - s0);
+        const size_t bytes_in = sizeof(float) * ((ns - 1) * seg_stride + n_samples);
+        WRS_CUDA(ctx, cudaMemcpyAsync(ctx->d_stage_in + s0 * seg_stride, pcm_host + s0 * seg_stride, bytes_in,
+                                      cudaMemcpyHostToDevice, ctx->h2d_stream));
+        WRS_CUDA(ctx, cudaEventRecord(ctx->ev_in[c], ctx->h2d_stream));
+        WRS_CUDA(ctx, cudaStreamWaitEvent(s, ctx->ev_in[c], 0));
+        int rc = wrs_logmel_batch(ctx, ctx->d_stage_in + s0 * seg_stride, ns, n_samples, seg_stride,
+                                  ctx->d_stage_out + s0 * out_per_seg, s);
+        if (rc != WRS_OK) { cudaDeviceSynchronize(); return rc; }
+        WRS_CUDA(ctx, cudaEventRecord(ctx->ev_done[c], s));
+        WRS_CUDA(ctx, cudaStreamWaitEvent(ctx->d2h_stream, ctx->ev_done[c], 0));
+        WRS_CUDA(ctx, cudaMemcpyAsync(out_host + s0 * out_per_seg, ctx->d_stage_out + s0 * out_per_seg,
+                                      sizeof(float) * ns * out_per_seg, cudaMemcpyDeviceToHost, ctx->d2h_stream));
+    }
+    WRS_CUDA(ctx, cudaStreamSynchronize(ctx->d2h_stream));
+    WRS_CUDA(ctx, cudaStreamSynchronize(ctx->h2d_stream));
     WRS_CUDA(ctx, cudaStreamSynchronize(s));
     return WRS_OK;
 }

@@ -51,6 +51,10 @@ struct wrs_ctx {
     float* d_stage_in = nullptr; size_t stage_in_bytes = 0;
     float* d_stage_out = nullptr; size_t stage_out_bytes = 0;
     cudaStream_t own_stream = nullptr;
+    // *_host pipeline: copy-in and copy-out streams beside own_stream, one event pair per chunk in flight
+    cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
+    static constexpr int kHostChunks = 64;
+    cudaEvent_t ev_in[kHostChunks] = {}, ev_done[kHostChunks] = {};
 };
 
 namespace wrs {
