@@ -1,4 +1,5 @@
 // Context, error plumbing and host-side helpers of libwrs_b200.so.
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 
@@ -58,7 +59,7 @@ bool build_mel_bank(const float* dense, MelBank* bank) {
         for (int k = 0; k < WRS_N_BINS; ++k)
             if (dense[m * WRS_N_BINS + k] != 0.0f) { if (lo < 0) lo = k; hi = k; }
         if (lo < 0) { lo = 0; hi = -1; }
-        const int n = hi - lo + 1, n4 = (n + 3) & ~3;
+        const int n = hi - lo + 1, n4 = std::max(4, (n + 3) & ~3);   // an empty row keeps four zero weights (K1 always takes a first step)
         if (total + n > MelBank::kMaxWeights || total4 + n4 > MelBank::kMaxPadded) return false;
         bank->lo[m] = lo; bank->n[m] = n; bank->off[m] = total;
         bank->n4[m] = n4; bank->off4[m] = total4;

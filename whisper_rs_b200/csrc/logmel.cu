@@ -380,22 +380,36 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
         float* __restrict__ outp = p.out + ((int64_t)seg * WRS_N_MELS) * p.n_frames + fs;
         {
             const bool ok0 = lane < nf, ok1 = lane + 32 < nf;
+            // software pipeline over the warp's 5 rows: a row's band description and its first four bins are fetched
+            // while the previous row is still in its log / store tail (most bands are 1..8 bins wide, so a row is
+            // mostly latency otherwise)
+            int n4 = sm.n4[warp];
+            const float4* w = reinterpret_cast<const float4*>(sm.w + sm.off4[warp]);
+            const float2* pp = sm.P + sm.lo[warp] * 32 + lane;
+            float4 wa = w[0];
+            float2 p0 = pp[0], p1 = pp[32], p2 = pp[64], p3 = pp[96];
 #pragma unroll 1
             for (int i = 0; i < WRS_N_MELS / kWarps; ++i) {
                 const int m = i * kWarps + warp;
-                const int n4 = sm.n4[m];
-                const float4* w = reinterpret_cast<const float4*>(sm.w + sm.off4[m]);
-                const float2* pp = sm.P + sm.lo[m] * 32 + lane;
-                f32x2 acc0, acc1;
-                zero_(acc0); zero_(acc1);
-                for (int j = 0; j < n4; j += 4) {
-                    const float4 wa = w[j >> 2];
-                    const float2 p0 = pp[j * 32], p1 = pp[j * 32 + 32], p2 = pp[j * 32 + 64], p3 = pp[j * 32 + 96];
-                    acc0 = fma_(pack2(p0.x, p0.y), pack2(wa.x, wa.x), acc0);
-                    acc1 = fma_(pack2(p1.x, p1.y), pack2(wa.y, wa.y), acc1);
-                    acc0 = fma_(pack2(p2.x, p2.y), pack2(wa.z, wa.z), acc0);
-                    acc1 = fma_(pack2(p3.x, p3.y), pack2(wa.w, wa.w), acc1);
+                const int mn = min(m + kWarps, WRS_N_MELS - 1);      // next row (the last iteration re-reads its own)
+                const int n4n = sm.n4[mn];
+                const float4* wn = reinterpret_cast<const float4*>(sm.w + sm.off4[mn]);
+                const float2* ppn = sm.P + sm.lo[mn] * 32 + lane;
+                f32x2 acc0 = mul_(pack2(p0.x, p0.y), pack2(wa.x, wa.x));
+                f32x2 acc1 = mul_(pack2(p1.x, p1.y), pack2(wa.y, wa.y));
+                acc0 = fma_(pack2(p2.x, p2.y), pack2(wa.z, wa.z), acc0);
+                acc1 = fma_(pack2(p3.x, p3.y), pack2(wa.w, wa.w), acc1);
+                for (int j = 4; j < n4; j += 4) {
+                    const float4 wb = w[j >> 2];
+                    const float2 q0 = pp[j * 32], q1 = pp[j * 32 + 32], q2 = pp[j * 32 + 64], q3 = pp[j * 32 + 96];
+                    acc0 = fma_(pack2(q0.x, q0.y), pack2(wb.x, wb.x), acc0);
+                    acc1 = fma_(pack2(q1.x, q1.y), pack2(wb.y, wb.y), acc1);
+                    acc0 = fma_(pack2(q2.x, q2.y), pack2(wb.z, wb.z), acc0);
+                    acc1 = fma_(pack2(q3.x, q3.y), pack2(wb.w, wb.w), acc1);
                 }
+                wa = wn[0];
+                p0 = ppn[0]; p1 = ppn[32]; p2 = ppn[64]; p3 = ppn[96];
+                n4 = n4n; w = wn; pp = ppn;
                 float a0, a1;
                 unpack2(add_(acc0, acc1), a0, a1);
                 const float v0 = __log2f(fmaxf(a0, 1e-10f)) * kLog10Of2, v1 = __log2f(fmaxf(a1, 1e-10f)) * kLog10Of2;
