@@ -30,6 +30,7 @@ constexpr int kTW = 64;              // frames per slice (two per lane)
 constexpr int kRows = kTW + 3;       // 160-sample rows f0-2 .. f0+64 needed by 64 frames
 constexpr int kPitch = WRS_HOP_LENGTH + 4;   // words per tile row: 16-byte aligned rows, frame stride == 4 banks
 constexpr float kLog10Of2 = 0.30102999566398120f;
+constexpr int kSlotEmpty = (int)0x80808080;         // memset pattern; as a key it decodes to -3.4e38, never a log10 value
 
 struct TabEntry { int off; float win; };             // tap n of frame 0: word offset in the tile, periodic Hann weight
 __constant__ TabEntry c_tab[WRS_N_FFT];              // src/audio.rs:233
@@ -47,8 +48,8 @@ struct LogmelParams {
     int vec_in;
     int vec_out;
     const MelBank* bank;
-    int* seg_max;   // [n_segments] order-preserving int key of the per-segment max of log10(mel)
-    int* seg_cnt;   // [n_segments] slices that have posted
+    int* seg_max;   // two-launch mode: [n_segments] order-preserving int key of the per-segment max of log10(mel)
+    int* slice_max; // fused mode: [n_segments][slices_per_seg] the same key per slice, kSlotEmpty until the slice has posted
     DevStatus* status;
 };
 
@@ -64,6 +65,9 @@ struct LogmelSmem {
     int lo[WRS_N_MELS], n4[WRS_N_MELS], off4[WRS_N_MELS];
     unsigned long long pcm_bar;                      // mbarrier: bytes of the PCM tile in flight
     int red_max;
+#ifdef WRS_TRACE
+    long long t_arrive[4];                           // barrier-B arrival times of warps 5, 13, 15 (investigation aid)
+#endif
     int fin_ready;                                   // the oldest pending slice's segment is complete: seg_floor is valid
     float seg_floor;
 };
@@ -144,12 +148,29 @@ __device__ __forceinline__ void stage_general(LogmelSmem& sm, const LogmelParams
     }
 }
 
-__device__ __forceinline__ int ld_acquire(const int* p) {
+// Per-slice maxima are single words written once (relaxed, gpu scope) and read by other CTAs the same way: a word is
+// either still kSlotEmpty or final, so no ordering between different words is ever needed -- no fences, no counters.
+__device__ __forceinline__ int ld_relaxed(const int* p) {
     int v;
-    asm volatile("ld.acquire.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    asm volatile("ld.relaxed.gpu.global.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
     return v;
 }
-__device__ __forceinline__ void fence_acq_rel() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
+__device__ __forceinline__ void st_relaxed(int* p, int v) { asm volatile("st.relaxed.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
+
+// One warp: have all slices of `seg` posted?  Folds the slots this lane owns beyond the two it may already hold
+// (a = slot lane, b = slot lane + 32, fetched earlier); returns the segment's max key on every lane, `complete` likewise.
+__device__ __forceinline__ int fold_slots(const LogmelParams& p, int seg, int a, int b, int lane, bool& complete) {
+    const int* slots = p.slice_max + (int64_t)seg * p.slices_per_seg;
+    bool miss = (lane < p.slices_per_seg && a == kSlotEmpty) || (lane + 32 < p.slices_per_seg && b == kSlotEmpty);
+    int mx = max(lane < p.slices_per_seg ? a : INT32_MIN, lane + 32 < p.slices_per_seg ? b : INT32_MIN);
+    for (int i = lane + 64; i < p.slices_per_seg; i += 32) {
+        const int v = ld_relaxed(slots + i);
+        miss = miss || v == kSlotEmpty;
+        mx = max(mx, v);
+    }
+    complete = !__any_sync(0xffffffffu, miss);
+    return __reduce_max_sync(0xffffffffu, mx);
+}
 
 // out = (max(raw, segmax - 8) + 4) / 4 (src/audio.rs:256-258) in place on one [80][nf] slice, by NT threads (t = 0..NT-1).
 // Aligned rows: all of a thread's 16-byte loads go out before the first store.
@@ -192,17 +213,21 @@ __device__ __forceinline__ void floor_scale_slice(float* __restrict__ outp, int6
 // drain at the end of the kernel (and a full pending queue) comes here; the steady state hides it inside the slice loop.
 __device__ __forceinline__ void finalize_slice_blocking(LogmelSmem& sm, const LogmelParams& p, int seg, int fs, int tid) {
     const int nf = min(kTW, p.n_frames - fs);
-    if (tid == 0) {
+    if (tid < 32) {
         // every slice of the segment is owned by a CTA that is running or has finished (persistent grid no larger than
-        // what is co-resident; waits only ever point at lower slice indices), so this wait ends; the bound is a safety net
-        volatile int* cnt = p.seg_cnt + seg;
-        int spins = 0;
-        while (*cnt < p.slices_per_seg) {
+        // what is co-resident; a CTA posts its slice before it ever waits), so this wait ends; the bound is a safety net
+        const int* slots = p.slice_max + (int64_t)seg * p.slices_per_seg;
+        int spins = 0, key;
+        for (;;) {
+            const int a = tid < p.slices_per_seg ? ld_relaxed(slots + tid) : 0;
+            const int b = tid + 32 < p.slices_per_seg ? ld_relaxed(slots + tid + 32) : 0;
+            bool complete;
+            key = fold_slots(p, seg, a, b, tid, complete);
+            if (complete) break;
             __nanosleep(64);
-            if (++spins > (1 << 22)) { atomicExch(&p.status->timeout, 1); break; }
+            if (++spins > (1 << 22)) { if (tid == 0) atomicExch(&p.status->timeout, 1); break; }
         }
-        fence_acq_rel();
-        sm.seg_floor = key_float(*(volatile int*)(p.seg_max + seg)) - 8.0f;
+        if (tid == 0) sm.seg_floor = key_float(key) - 8.0f;
     }
     __syncthreads();
     floor_scale_slice<kThreads>(p.out + ((int64_t)seg * WRS_N_MELS) * p.n_frames + fs, p.n_frames, nf, sm.seg_floor, tid, p.vec_out != 0);
@@ -245,7 +270,6 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
     int pend_seg[kPend], pend_fs[kPend];
 #pragma unroll
     for (int k = 0; k < kPend; ++k) { pend_seg[k] = 0; pend_fs[k] = -1; }
-    int post_seg = -1;                                   // segment of the slice whose "posted" count is still owed
     unsigned pcm_parity = 0;                             // phase of pcm_bar the next bulk-copied tile completes
     bool cur_bulk = false;                               // the current slice's tile arrives through pcm_bar
     const bool ovec = p.vec_out != 0;                    // output rows 16-byte aligned, n_frames % 4 == 0: rows move as bulk copies
@@ -269,8 +293,12 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
         if (tid == 0) sm.red_max = float_key(-INFINITY);
         // has the oldest pending slice's segment completed?  The answer is asked for here and looked at in stage B, so
         // that the round trip to L2 is off every warp's critical path.
-        int polled = 0;
-        if (FUSED && warp == 15 && lane == 0 && pend_fs[0] >= 0) polled = ld_acquire(p.seg_cnt + pend_seg[0]);
+        int poll_a = 0, poll_b = 0;
+        if (FUSED && warp == 15 && pend_fs[0] >= 0) {
+            const int* slots = p.slice_max + (int64_t)pend_seg[0] * p.slices_per_seg;
+            if (lane < p.slices_per_seg) poll_a = ld_relaxed(slots + lane);
+            if (lane + 32 < p.slices_per_seg) poll_b = ld_relaxed(slots + lane + 32);
+        }
         LM_T(10);
         if (cur_bulk) { mbar_wait(&sm.pcm_bar, pcm_parity); pcm_parity ^= 1u; }
         LM_T(7);
@@ -332,24 +360,29 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
                 }
             }
         } else {
-            // the three warps without a bin: 13 and 14 start the next slice's copy (the tile is free now); one lane of
-            // 15 counts the previous slice as posted and looks at the poll
+            // the three warps without a bin: 13 and 14 start the next slice's copy (the tile is free now); 15 folds the
+            // per-slice maxima it asked for at the top of the slice: is the oldest pending slice's segment complete?
             if (warp < 15) {
                 if (next_bulk) stage_bulk(sm, p, nseg, nsl * kTW, nplan, lane, warp - 13);
-            } else if (FUSED && lane == 0) {
-                // the previous slice's raw rows and maximum were issued before the barrier above: one fence by this
-                // lane orders all of them before the count that tells the other CTAs this slice has posted
-                if (post_seg >= 0) { fence_acq_rel(); atomicAdd(p.seg_cnt + post_seg, 1); }
-                int ready = 0;
-                if (pend_fs[0] >= 0 && polled >= p.slices_per_seg) {
-                    sm.seg_floor = key_float(*(volatile int*)(p.seg_max + pend_seg[0])) - 8.0f;
-                    ready = 1;
+            } else if (FUSED) {
+                bool ready = false;
+                int key = 0;
+                if (pend_fs[0] >= 0) key = fold_slots(p, pend_seg[0], poll_a, poll_b, lane, ready);
+                if (lane == 0) {
+                    if (ready) sm.seg_floor = key_float(key) - 8.0f;
+                    sm.fin_ready = ready ? 1 : 0;
                 }
-                sm.fin_ready = ready;
             }
         }
+#ifdef WRS_TRACE
+        if (lane == 0 && (warp == 5 || warp == 13 || warp == 15)) sm.t_arrive[warp == 5 ? 0 : (warp == 13 ? 1 : 2)] = clock64();
+        const long long tB0_ = t_;
+#endif
         __syncthreads();
         LM_T(1);
+#ifdef WRS_TRACE
+        if (tid == 0) { acc_[9] += sm.t_arrive[0] - tB0_; acc_[11] += sm.t_arrive[1] - tB0_; acc_[8] += sm.t_arrive[2] - tB0_; }
+#endif
 
         // ---- stage C: banded mel projection (src/audio.rs:252), clamp + log10 (:254), raw rows -> HBM
         const bool fin = FUSED && sm.fin_ready != 0;
@@ -371,10 +404,7 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
         LM_T(2);
         if (next_edge) {
             stage_general(sm, p, nseg, nsl * kTW, nplan, tid);
-            LM_T(8);
-#ifdef WRS_TRACE
-            if (tid == 0) acc_[9] += 1;
-#endif
+
         }
         float lmax = -INFINITY;
         float* __restrict__ outp = p.out + ((int64_t)seg * WRS_N_MELS) * p.n_frames + fs;
@@ -449,13 +479,14 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
         LM_T(5);
 
         // No barrier follows: the next stage A touches nothing stage C reads, and red_max is only reset by thread 0.
-        if (tid == 0) atomicMax(p.seg_max + seg, sm.red_max);
+        // the slice has posted once its maximum is out (its raw rows are only ever re-read by this CTA)
+        if (tid == 0) {
+            if (FUSED) st_relaxed(p.slice_max + (int64_t)seg * p.slices_per_seg + sl, sm.red_max);
+            else atomicMax(p.seg_max + seg, sm.red_max);
+        }
         if (FUSED) {
-            post_seg = seg;                              // counted by warp 15 during the next stage B
-            if (pend_fs[kPend - 1] >= 0) {               // queue full (a straggling segment): wait for the oldest --
-                __syncthreads();                         // after this slice has been counted, so that two CTAs
-                if (tid == 0) { fence_acq_rel(); atomicAdd(p.seg_cnt + seg, 1); }   // can never wait on each other
-                post_seg = -1;
+            if (pend_fs[kPend - 1] >= 0) {               // queue full (a straggling segment): wait for the oldest
+                __syncthreads();
                 finalize_slice_blocking(sm, p, pend_seg[0], pend_fs[0], tid);
 #pragma unroll
                 for (int k = 0; k + 1 < kPend; ++k) { pend_seg[k] = pend_seg[k + 1]; pend_fs[k] = pend_fs[k + 1]; }
@@ -474,7 +505,6 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
 #endif
     if (FUSED) {
         __syncthreads();
-        if (tid == 0 && post_seg >= 0) { fence_acq_rel(); atomicAdd(p.seg_cnt + post_seg, 1); }
 #pragma unroll
         for (int k = 0; k < kPend; ++k)
             if (pend_fs[k] >= 0) finalize_slice_blocking(sm, p, pend_seg[k], pend_fs[k], tid);
@@ -588,19 +618,20 @@ int wrs_logmel_batch(wrs_ctx* ctx, const float* pcm, int64_t n_segments, int64_t
     p.bank = ctx->d_bank;
     p.status = ctx->d_status;
 
-    if (n_segments > ctx->seg_cap) {
+    const bool fused = ctx->opt_logmel_fused != 0;
+    const int64_t need = fused ? total : n_segments;     // fused: one word per slice; two launches: one per segment
+    if (need > ctx->seg_cap) {
         WRS_CUDA(ctx, cudaStreamSynchronize(stream));
         cudaFree(ctx->d_seg_state);
         ctx->d_seg_state = nullptr;
-        const int64_t cap = std::max<int64_t>(n_segments, 256);
-        WRS_CUDA(ctx, cudaMalloc(&ctx->d_seg_state, sizeof(int) * 2 * cap));
+        const int64_t cap = std::max<int64_t>(need, 4096);
+        WRS_CUDA(ctx, cudaMalloc(&ctx->d_seg_state, sizeof(int) * cap));
         ctx->seg_cap = cap;
     }
     p.seg_max = ctx->d_seg_state;
-    p.seg_cnt = ctx->d_seg_state + ctx->seg_cap;
-    // 0x80808080 decodes to about -3.4e38: "minus infinity" for the max; counters start at 0
-    WRS_CUDA(ctx, cudaMemsetAsync(p.seg_max, 0x80, sizeof(int) * n_segments, stream));
-    WRS_CUDA(ctx, cudaMemsetAsync(p.seg_cnt, 0, sizeof(int) * n_segments, stream));
+    p.slice_max = ctx->d_seg_state;
+    // 0x80808080: kSlotEmpty for the per-slice words, and (decoding to about -3.4e38) "minus infinity" for atomicMax
+    WRS_CUDA(ctx, cudaMemsetAsync(ctx->d_seg_state, 0x80, sizeof(int) * need, stream));
 
     const size_t smem = sizeof(LogmelSmem);
     if (ctx->logmel_max_ctas_per_sm == 0) {
@@ -615,7 +646,6 @@ int wrs_logmel_batch(wrs_ctx* ctx, const float* pcm, int64_t n_segments, int64_t
     const int grid = (int)std::min<int64_t>(total, resident);
     // fused: the floor/scale of a slice is applied one slice later by the CTA that produced it, once the segment's
     // other slices (all owned by co-resident CTAs: cooperative launch) have posted their maxima
-    const bool fused = ctx->opt_logmel_fused != 0;
     ctx->stat_last_logmel_mode = fused ? 1 : 0;
     ctx->stat_last_logmel_grid = grid;
     if (fused) {
