@@ -111,6 +111,16 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned by
                  "l"(src), "r"(bytes), "r"(smem_addr(bar))
                  : "memory");
 }
+__device__ __forceinline__ bool elect_one() {        // true on exactly one lane of the (converged) warp
+    unsigned pred;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "elect.sync _|p, 0xffffffff;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n" : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // The tile of slice (seg, fs) is rows fs-2 .. fs+64 of the segment cut into 160-sample rows.  Rows that lie entirely
@@ -132,8 +142,13 @@ __device__ __forceinline__ void stage_bulk(LogmelSmem& sm, const LogmelParams& p
     fence_proxy_async();                             // the tile was last touched by ordinary loads/stores
     if (part == 0 && lane == 0) mbar_expect_tx(&sm.pcm_bar, (unsigned)(nb * WRS_HOP_LENGTH * sizeof(float)));
     const int r0 = t.r_lo + part * half, r1 = min(t.r_hi, r0 + half);
-    for (int r = r0 + lane; r < r1; r += 32)
-        bulk_g2s(sm.pcm + r * kPitch, src + r * WRS_HOP_LENGTH, WRS_HOP_LENGTH * (unsigned)sizeof(float), &sm.pcm_bar);
+    // warp-uniform loop, one elected lane issues: the addresses stay in uniform registers (a per-lane loop would be
+    // serialised lane by lane through R2UR at about 80 cycles per copy)
+    if (elect_one()) {
+#pragma unroll 4
+        for (int r = r0; r < r1; ++r)
+            bulk_g2s(sm.pcm + r * kPitch, src + r * WRS_HOP_LENGTH, WRS_HOP_LENGTH * (unsigned)sizeof(float), &sm.pcm_bar);
+    }
 }
 // the rows outside [r_lo, r_hi): element-wise with reflection at both ends (src/audio.rs:236 center = true), whole CTA
 __device__ __forceinline__ void stage_general(LogmelSmem& sm, const LogmelParams& p, int seg, int fs, TilePlan t, int tid) {
