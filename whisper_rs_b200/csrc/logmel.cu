@@ -64,7 +64,8 @@ struct LogmelSmem {
     float2 tw[16 * 13];                              // 1 664 B
     int lo[WRS_N_MELS], n4[WRS_N_MELS], off4[WRS_N_MELS];
     unsigned long long pcm_bar;                      // mbarrier: bytes of the PCM tile in flight
-    int red_max;
+    int red_max;                                     // max key of the slice in progress (reset by the last warp to add to it)
+    int warps_done;
 #ifdef WRS_TRACE
     long long t_arrive[4];                           // barrier-B arrival times of warps 5, 13, 15 (investigation aid)
 #endif
@@ -275,7 +276,7 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
     for (int i = tid; i < WRS_N_FFT; i += kThreads) sm.tab[i] = c_tab[i];
     for (int i = tid; i < 16 * 13; i += kThreads) sm.tw[i] = c_tw[i];
     for (int i = tid; i < (kPRows - WRS_N_BINS) * 32; i += kThreads) sm.P[WRS_N_BINS * 32 + i] = make_float2(0.0f, 0.0f);
-    if (tid == 0) mbar_init(&sm.pcm_bar, 1);
+    if (tid == 0) { mbar_init(&sm.pcm_bar, 1); sm.red_max = float_key(-INFINITY); sm.warps_done = 0; }
     __syncthreads();
 
     // slices are dealt round-robin; (seg, fs) of the current slice advance without divisions
@@ -305,7 +306,6 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
         const TilePlan nplan = tile_plan(p, nsl * kTW);
         const bool next_bulk = has_next && nplan.r_hi > nplan.r_lo;
         const bool next_edge = has_next && nplan.r_hi - nplan.r_lo < kRows;
-        if (tid == 0) sm.red_max = float_key(-INFINITY);
         // has the oldest pending slice's segment completed?  The answer is asked for here and looked at in stage B, so
         // that the round trip to L2 is off every warp's critical path.
         int poll_a = 0, poll_b = 0;
@@ -488,17 +488,23 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
         // ---- per-slice max -> per-segment max (src/audio.rs:256 `log_spec.max()`)
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) lmax = fmaxf(lmax, __shfl_xor_sync(0xffffffffu, lmax, o));
-        if (lane == 0) atomicMax(&sm.red_max, float_key(lmax));
-        LM_T(4);
-        __syncthreads();
-        LM_T(5);
-
-        // No barrier follows: the next stage A touches nothing stage C reads, and red_max is only reset by thread 0.
-        // the slice has posted once its maximum is out (its raw rows are only ever re-read by this CTA)
-        if (tid == 0) {
-            if (FUSED) st_relaxed(p.slice_max + (int64_t)seg * p.slices_per_seg + sl, sm.red_max);
-            else atomicMax(p.seg_max + seg, sm.red_max);
+        // No CTA barrier closes stage C: a warp goes straight on to stage A of the next slice (which touches nothing
+        // stage C reads).  The last warp to add its maximum posts the slice: once the maximum is out the slice has
+        // posted (its raw rows are only ever re-read by this CTA).
+        if (lane == 0) {
+            atomicMax(&sm.red_max, float_key(lmax));
+            __threadfence_block();
+            if (atomicAdd(&sm.warps_done, 1) == kWarps - 1) {
+                __threadfence_block();
+                const int key = atomicExch(&sm.red_max, float_key(-INFINITY));
+                atomicExch(&sm.warps_done, 0);
+                if (FUSED) st_relaxed(p.slice_max + (int64_t)seg * p.slices_per_seg + sl, key);
+                else atomicMax(p.seg_max + seg, key);
+            }
         }
+        LM_T(4);
+        if (next_edge) __syncthreads();                  // the element-wise rows of the next tile came from every warp
+        LM_T(5);
         if (FUSED) {
             if (pend_fs[kPend - 1] >= 0) {               // queue full (a straggling segment): wait for the oldest
                 __syncthreads();
