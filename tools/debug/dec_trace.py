@@ -27,7 +27,7 @@ t = t[act]
 t0 = t[:, 0].min()
 rel = lambda c: (t[:, c] - t0) / 1e3
 print("warps", len(t))
-for name, c in (("start", 0), ("first unit reduced", 1), ("last unit reduced", 2), ("warp end", 3)):
+for name, c in (("start", 0), ("first unit landed", 1), ("last unit reduced", 2), ("warp end", 3)):
     v = rel(c); print(f"{name:20s} min {v.min():7.2f} med {np.median(v):7.2f} p90 {np.percentile(v,90):7.2f} max {v.max():7.2f} us")
 mg = t[:, 5] > 0
 print("row merges", int(t[:, 5].sum()), "avg us", (t[mg, 4] / t[mg, 5]).mean() / 1e3, "max us", (t[mg, 4] / t[mg, 5]).max() / 1e3)

@@ -16,6 +16,7 @@
 #include <cmath>
 #include <cstring>
 
+#include "async_copy.cuh"
 #include "decode_scan.cuh"
 #include "wrs_internal.cuh"
 
@@ -49,9 +50,11 @@ namespace wrs {
 enum { MODE_BEAM = 0, MODE_GREEDY = 1, MODE_FILTER = 2 };
 constexpr int kMaxBeam = 15;
 constexpr int kMaxCandAudio = kMaxBeam * kMaxK;          // 240
-constexpr int kStageBytes = kUnit * 4;                    // per-warp landing zone of the unit in flight (cp.async)
-constexpr int kScratchBytes = 2688;                      // per-warp scratch behind it (WarpBuf, or the fast beam tail's tables)
-constexpr int kWarpSmem = kStageBytes + kScratchBytes;   // the general beam tail (beam > 5) takes the whole slice
+constexpr int kStages = 3;                               // units a warp keeps in flight (bulk copies, one mbarrier each)
+constexpr int kStageBytes = kUnit * 4;                    // landing zone of one unit
+constexpr int kScratchBytes = 2688;                      // per-warp scratch behind stage 0 (WarpBuf, or the fast beam tail's tables)
+constexpr int kTailBytes = kStageBytes + kScratchBytes;  // the general beam tail (beam > 5) overlays stage 0 + scratch
+constexpr int kWarpSmem = kStages * kStageBytes + kScratchBytes + 32;   // + the stages' mbarriers
 
 // what the row merge leaves for the audio-level tail
 struct __align__(16) RowResult {
@@ -66,6 +69,7 @@ struct StepParams {
     float* logits; int64_t row_stride;                   // read-only except MODE_FILTER
     const int64_t* tokens; int64_t tok_stride;
     int cur_len, sample_begin, n_rows, K, beam, n_groups;
+    int scan_warps;                                      // warps of the scan launch (the unit dealing both launches agree on)
     RuleCfg rc;
     int ts_split, n_text_units, n_ts_units, upr, bm_words;
     const uint32_t* bm;
@@ -179,19 +183,30 @@ __device__ __forceinline__ void run_finish(Run& run, WarpBuf& wb, int K) {
     run.s = (s != s) ? s : s * exp_diff(run.ref_set ? run.ref : -CUDART_INF_F, run.m);   // the reference is a seen maximum: ref <= m
 }
 
-// ---- which warp of the grid owns unit u, when N units are dealt to Wt warps in contiguous runs [g N / Wt, (g+1) N / Wt)
-__device__ __forceinline__ int unit_owner(int64_t u, int64_t Wt, int64_t N) { return (int)(((u + 1) * Wt - 1) / N); }
+// ---- N units are dealt to Wt warps in contiguous runs: the first r = N % Wt warps take q + 1 = N / Wt + 1 units, the
+//      others q (all 32-bit: n_rows < 32768 and a row has a few dozen units)
+struct Deal { int Wt, q, r; };
+__device__ __forceinline__ Deal deal_of(int N, int grid_warps) {
+    Deal d;
+    d.Wt = min(grid_warps, N); d.q = N / d.Wt; d.r = N - d.q * d.Wt;
+    return d;
+}
+__device__ __forceinline__ int deal_begin(const Deal& d, int g) { return g * d.q + min(g, d.r); }
+__device__ __forceinline__ int unit_owner(const Deal& d, int u) {
+    const int big = d.r * (d.q + 1);
+    return u < big ? u / (d.q + 1) : d.r + (u - big) / d.q;
+}
 
 struct RowPartials { int first_owner[2], count[2], base[2]; };
 
-__device__ __forceinline__ RowPartials row_partials(const StepParams& p, int row, int64_t Wt, int64_t N) {
+__device__ __forceinline__ RowPartials row_partials(const StepParams& p, int row, const Deal& d) {
     RowPartials rp;
-    const int64_t u0 = (int64_t)row * p.upr;
+    const int u0 = row * p.upr;
     rp.base[0] = 0; rp.base[1] = p.n_text_units;
-    const int64_t ua[2] = {u0, u0 + p.n_text_units}, ub[2] = {u0 + p.n_text_units, u0 + p.upr};
+    const int ua[2] = {u0, u0 + p.n_text_units}, ub[2] = {u0 + p.n_text_units, u0 + p.upr};
 #pragma unroll
     for (int q = 0; q < 2; ++q) {
-        if (ub[q] > ua[q]) { rp.first_owner[q] = unit_owner(ua[q], Wt, N); rp.count[q] = unit_owner(ub[q] - 1, Wt, N) - rp.first_owner[q] + 1; }
+        if (ub[q] > ua[q]) { rp.first_owner[q] = unit_owner(d, ua[q]); rp.count[q] = unit_owner(d, ub[q] - 1) - rp.first_owner[q] + 1; }
         else { rp.first_owner[q] = 0; rp.count[q] = 0; }
     }
     return rp;
@@ -202,8 +217,8 @@ __device__ __forceinline__ RowPartials row_partials(const StepParams& p, int row
 // with independent 16-byte loads up front, so the usual row (<= 32 partials) costs ONE round trip to L2.
 struct RowOut { float lp; int tok; unsigned flags; };
 
-__device__ __noinline__ RowOut merge_row(const StepParams& p, int row, unsigned rule_flags, const RowPartials& rpz, int64_t Wt,
-                                         int64_t N, WarpBuf& wb) {
+__device__ __noinline__ RowOut merge_row(const StepParams& p, int row, unsigned rule_flags, const RowPartials& rpz, const Deal& deal,
+                                         WarpBuf& wb) {
     const int lane = threadIdx.x & 31;
     const int K = p.K, KQ = (K + 3) >> 2;
     const Partial* __restrict__ parts = p.partials + (int64_t)row * p.upr;
@@ -212,9 +227,8 @@ __device__ __noinline__ RowOut merge_row(const StepParams& p, int row, unsigned 
     // unit of the owning warp's range, or the partition's first unit if the range starts before it
     auto part_of = [&](int i) {
         const int q = i < cT ? 0 : 1;
-        const int64_t g = rpz.first_owner[q] + (q ? i - cT : i);
-        const int64_t j = g * N / Wt - (int64_t)row * p.upr;
-        return parts + (int)max(j, (int64_t)rpz.base[q]);
+        const int g = rpz.first_owner[q] + (q ? i - cT : i);
+        return parts + max(deal_begin(deal, g) - row * p.upr, rpz.base[q]);
     };
     auto load_entries = [&](const Partial* pp, float (&ev)[kMaxK], int (&ei)[kMaxK]) {
 #pragma unroll
@@ -340,7 +354,7 @@ struct TailScratch {
     double sel_score[kMaxBeam], fin_sc[kMaxBeam];
     int sel_src[kMaxBeam], sel_tok[kMaxBeam], fin_src[kMaxBeam];
 };
-static_assert(sizeof(TailScratch) <= kWarpSmem, "tail scratch does not fit the per-warp slice");
+static_assert(sizeof(TailScratch) <= kTailBytes, "tail scratch does not fit the per-warp slice");
 static_assert(sizeof(WarpBuf) <= kScratchBytes, "candidate buffer does not fit the per-warp slice");
 
 // ---- MODE_BEAM tail: BeamSearchTokenExtractor::update for one audio (beam_search.rs:49-146), ONE warp ----
@@ -613,29 +627,79 @@ __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; as
 #define WRS_TR_ADD(slot, v) do {} while (0)
 #endif
 
-template <int MODE>
-__global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const StepParams p) {
+// ---- launch 1 of a step: every warp folds its run of units and leaves one partial per (row, partition) run.  No atomics,
+//      no fences: the kernel boundary hands the partials to the tail.
+__global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const StepParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    // per-warp slice: [stage 0][scratch][stage 1][stage 2][mbarriers]
     unsigned char* slice = smem_raw + warp * kWarpSmem;
-    float4* stage = reinterpret_cast<float4*>(slice);
     unsigned char* scratch = slice + kStageBytes;
     WarpBuf& wb = *reinterpret_cast<WarpBuf*>(scratch);
+    unsigned long long* bars = reinterpret_cast<unsigned long long*>(slice + kStages * kStageBytes + kScratchBytes);
+    auto stage_of = [&](int s) { return reinterpret_cast<float4*>(s == 0 ? slice : slice + kScratchBytes + s * kStageBytes); };
 
     // N units are dealt to the first Wt = min(warps of the grid, N) warps: every active warp owns >= 1 unit, so the
     // owners of consecutive units are consecutive warps (row_partials relies on that)
-    const int64_t N = (int64_t)p.n_rows * p.upr;
-    const int64_t Wt = min((int64_t)gridDim.x * kStepWarps, N);
-    const int64_t gw = (int64_t)blockIdx.x * kStepWarps + warp;
-    if (gw >= Wt) return;
-    const int64_t u_begin = gw * N / Wt, u_end = (gw + 1) * N / Wt;
+    const int N = p.n_rows * p.upr;
+    const Deal deal = deal_of(N, (int)gridDim.x * kStepWarps);
+    const int gw = (int)blockIdx.x * kStepWarps + warp;
+    if (gw >= deal.Wt) return;
+    const int u_begin = deal_begin(deal, gw), u_end = deal_begin(deal, gw + 1);
+    const int n_units = u_end - u_begin;
 #ifdef WRS_TRACE
     if (lane == 0) for (int q = 0; q < 8; ++q) g_trace[gw * 8 + q] = 0;
 #endif
     WRS_TR(0);
 
+    // ---- where unit k of this warp lives: needs nothing but the row pointer's alignment
+    struct Place { int row, j, part, a0, c_lo, c_hi; };
+    auto place_of = [&](int k) {
+        Place q;
+        const int u = u_begin + k;
+        q.row = u / p.upr; q.j = u - q.row * p.upr;
+        const float* rp = p.logits + (int64_t)q.row * p.row_stride;
+        int pb, pe;                                       // the partition's id range
+        if (q.j < p.n_text_units) {
+            q.part = 0; pb = 0; pe = p.ts_split;
+            q.a0 = -(int)((reinterpret_cast<uintptr_t>(rp) >> 2) & 3) + q.j * kUnit;
+        } else {
+            q.part = 1; pb = p.ts_split; pe = p.rc.n_vocab;
+            q.a0 = p.ts_split - (int)((reinterpret_cast<uintptr_t>(rp + p.ts_split) >> 2) & 3) + (q.j - p.n_text_units) * kUnit;
+        }
+        // 16-byte chunks [c_lo, c_hi) of the unit that hold ids of the partition; a chunk that would reach outside the
+        // logits buffer (before row 0, behind the last row) is left out and its <= 3 ids are read one by one instead
+        q.c_lo = (max(q.a0, pb) - q.a0) >> 2;
+        q.c_hi = min(kUnit >> 2, (min(q.a0 + kUnit, pe) - q.a0 + 3) >> 2);
+        if (q.row == 0 && q.a0 + 4 * q.c_lo < 0) ++q.c_lo;
+        if (q.row == p.n_rows - 1 && q.a0 + 4 * q.c_hi > p.rc.n_vocab) --q.c_hi;
+        return q;
+    };
+    // start the flight of unit k into stage k % kStages: one bulk copy, completion by byte count on the stage's mbarrier
+    auto issue = [&](int k) {
+        const Place q = place_of(k);
+        if (elect_one()) {
+            unsigned long long* bar = bars + (k % kStages);
+            const int bytes = (q.c_hi - q.c_lo) * 16;
+            if (bytes > 0) {
+                mbar_expect_tx(bar, (unsigned)bytes);
+                bulk_g2s(reinterpret_cast<unsigned char*>(stage_of(k % kStages)) + 16 * q.c_lo,
+                         p.logits + (int64_t)q.row * p.row_stride + q.a0 + 4 * q.c_lo, (unsigned)bytes, bar);
+            } else {
+                mbar_arrive(bar);
+            }
+        }
+    };
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < kStages; ++s) mbar_init(bars + s, 1);
+    }
+    __syncwarp();
+    // every warp puts its first unit in flight before anything else
+    issue(0);
+
     // rules of the first two rows this warp touches are fetched up front (a later row change costs a bubble)
-    const int row_first = (int)(u_begin / p.upr);
+    const int row_first = u_begin / p.upr;
     int64_t tk_last[2], tk_pen[2];
 #pragma unroll
     for (int q = 0; q < 2; ++q) {
@@ -647,143 +711,117 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const Step
     int rules_row = -1;
     RowRules rules;
     rules.t_lo = rules.t_hi = rules.s_lo = rules.s_hi = 0; rules.flags = 0;
-    int abase[2] = {0, 0};                               // first 16-byte aligned id slot of the row's two partitions
-
     auto rules_for = [&](int row) {
         if (row == rules_row) return;
         if (row == row_first) rules = row_rules_from(p.rc, tk_last[0], tk_pen[0], p.cur_len, p.sample_begin);
         else if (row == row_first + 1) rules = row_rules_from(p.rc, tk_last[1], tk_pen[1], p.cur_len, p.sample_begin);
         else rules = row_rules(p.rc, p.tokens + (int64_t)row * p.tok_stride, p.cur_len, p.sample_begin);
         rules_row = row;
-        const float* rp = p.logits + (int64_t)row * p.row_stride;
-        abase[0] = -(int)((reinterpret_cast<uintptr_t>(rp) >> 2) & 3);
-        abase[1] = p.ts_split - (int)((reinterpret_cast<uintptr_t>(rp + p.ts_split) >> 2) & 3);
     };
-    // unit j of row `row`: ids [a0, a0 + 896) of its partition, clipped to the partition and to the row's rules
-    auto geom_of = [&](int row, int j) {
+    // ids of the unit that survive the row's rules
+    auto geom_of = [&](const Place& q) {
         Geom g;
-        g.row = row;
-        rules_for(row);
-        if (j < p.n_text_units) {
-            g.part = 0; g.a0 = abase[0] + j * kUnit;
-            g.lo = max(max(g.a0, 0), rules.t_lo); g.hi = min(min(g.a0 + kUnit, p.ts_split), rules.t_hi);
-        } else {
-            g.part = 1; g.a0 = abase[1] + (j - p.n_text_units) * kUnit;
-            g.lo = max(max(g.a0, p.ts_split), rules.s_lo); g.hi = min(min(g.a0 + kUnit, p.rc.n_vocab), rules.s_hi);
-        }
+        g.row = q.row; g.part = q.part; g.a0 = q.a0;
+        rules_for(q.row);
+        if (q.part == 0) { g.lo = max(max(q.a0, 0), rules.t_lo); g.hi = min(min(q.a0 + kUnit, p.ts_split), rules.t_hi); }
+        else { g.lo = max(max(q.a0, p.ts_split), rules.s_lo); g.hi = min(min(q.a0 + kUnit, p.rc.n_vocab), rules.s_hi); }
         return g;
     };
-    auto interior = [](const Geom& g) { return g.lo == g.a0 && g.hi == g.a0 + kUnit; };
-    // start the flight of a unit: an interior unit goes to the warp's stage with seven 16-byte cp.async per lane (every
-    // lane later reads back exactly what it copied); a ragged or clipped unit is loaded directly when its turn comes
-    auto prefetch = [&](const Geom& g, uint32_t& bmw) {
-        bmw = 0u;
-        if (g.hi <= g.lo) return;
-        if (interior(g)) {
-            const float* src = p.logits + (int64_t)g.row * p.row_stride + g.a0 + 4 * lane;
-            const unsigned dst = (unsigned)__cvta_generic_to_shared(stage + lane);
+    auto bitmap_of = [&](const Place& q) { return __ldg(p.bm + min((max(q.a0, 0) >> 5) + lane, p.bm_words - 1)); };
+    // bring unit k into registers; slot j of a lane holds ids a0 + 4 (lane + 32 j) ..+3, everything outside [lo, hi)
+    // reads as -inf
+    auto fetch = [&](int k, const Place& q, const Geom& g, float (&x)[kNV][4]) {
+        const float4* st = stage_of(k % kStages);
 #pragma unroll
-            for (int j = 0; j < kNV; ++j)
-                asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(dst + 512u * j), "l"(src + 128 * j) : "memory");
+        for (int j = 0; j < kNV; ++j) {
+            const float4 v = st[lane + 32 * j];
+            x[j][0] = v.x; x[j][1] = v.y; x[j][2] = v.z; x[j][3] = v.w;
         }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-        const int wbase = max(g.a0, 0) >> 5;
-        bmw = __ldg(p.bm + min(wbase + lane, p.bm_words - 1));
-    };
-    // bring the current unit into registers; slot j of a lane holds ids a0 + 4 (lane + 32 j) ..+3, everything outside
-    // [lo, hi) reads as -inf
-    auto fetch = [&](const Geom& g, float (&x)[kNV][4]) {
-        if (interior(g)) {
-            asm volatile("cp.async.wait_group 0;" ::: "memory");
-#pragma unroll
-            for (int j = 0; j < kNV; ++j) {
-                const float4 q = stage[lane + 32 * j];
-                x[j][0] = q.x; x[j][1] = q.y; x[j][2] = q.z; x[j][3] = q.w;
-            }
-        } else {
+        if (g.lo != g.a0 || g.hi != g.a0 + kUnit) {      // ragged or clipped: mask, and fetch what the copy left out
             const float* __restrict__ rp = p.logits + (int64_t)g.row * p.row_stride;
 #pragma unroll
             for (int j = 0; j < kNV; ++j) {
-                const int e = g.a0 + 4 * (lane + 32 * j);
-                if (e >= g.lo && e + 3 < g.hi) {
-                    const float4 q = __ldcs(reinterpret_cast<const float4*>(rp + e));
-                    x[j][0] = q.x; x[j][1] = q.y; x[j][2] = q.z; x[j][3] = q.w;
-                } else {
+                const int c = lane + 32 * j, e = g.a0 + 4 * c;
 #pragma unroll
-                    for (int i = 0; i < 4; ++i) x[j][i] = (e + i >= g.lo && e + i < g.hi) ? __ldcs(rp + e + i) : -CUDART_INF_F;
+                for (int i = 0; i < 4; ++i) {
+                    const bool in = e + i >= g.lo && e + i < g.hi;
+                    if (!in) x[j][i] = -CUDART_INF_F;
+                    else if (c < q.c_lo || c >= q.c_hi) x[j][i] = __ldcs(rp + e + i);
                 }
             }
         }
     };
 
-    int row_n = row_first, j_n = (int)(u_begin - (int64_t)row_first * p.upr);   // (row, unit-in-row) of the unit in flight
-    uint32_t bm_n = 0u;
-    Geom gn = geom_of(row_n, j_n);
-    prefetch(gn, bm_n);
     Run run;
     run_reset(run);
-    int run_j0 = j_n, run_units = 0;                     // first unit-in-row and unit count of the current run
+    Place qc = place_of(0);
+    uint32_t bm_c = bitmap_of(qc);
+    int run_j0 = qc.j, run_units = 0;                    // first unit-in-row and unit count of the current run
 
-    for (int64_t u = u_begin; u < u_end; ++u) {
-        const Geom g = gn;
-        const uint32_t bmw = bm_n;
-        const bool has_next = u + 1 < u_end;
-        {
-            float x[kNV][4];
-            if (g.hi > g.lo) fetch(g, x);
-            __syncwarp();
-            if (has_next) {
-                if (++j_n == p.upr) { j_n = 0; ++row_n; }
-                gn = geom_of(row_n, j_n);
-                prefetch(gn, bm_n);
-            }
-            if (run_units == 0) {                        // a run starts with an empty pending list (merges and tails share wb)
-                if (lane == 0) wb.n = 0;
-                __syncwarp();
-            }
-            if (g.hi > g.lo) reduce_unit(x, g, bmw, max(g.a0, 0) >> 5, p.K, wb, run);
+    for (int k = 0; k < n_units; ++k) {
+        const Place q = qc;
+        const uint32_t bmw = bm_c;
+        const bool has_next = k + 1 < n_units;
+        const Geom g = geom_of(q);
+        if (has_next) { qc = place_of(k + 1); bm_c = bitmap_of(qc); }
+        mbar_wait(bars + (k % kStages), (unsigned)(k / kStages) & 1u);   // also when nothing survives: the stage is reused
+        if (k == 0) {
+            // only now the later units: all first units of the grid (a quarter of the step's bytes) land first and
+            // the arithmetic starts while the rest streams in behind them
+            WRS_TR(1);
+#pragma unroll
+            for (int k2 = 1; k2 < kStages; ++k2)
+                if (k2 < n_units) issue(k2);
         }
+        if (run_units == 0) {                            // a run starts with an empty pending list (merges and tails share wb)
+            if (lane == 0) wb.n = 0;
+            __syncwarp();
+        }
+        if (g.hi > g.lo) {
+            float x[kNV][4];
+            fetch(k, q, g, x);
+            reduce_unit(x, g, bmw, max(g.a0, 0) >> 5, p.K, wb, run);
+        }
+        __syncwarp();                                    // every lane has taken its share of the stage out
+        if (k + kStages < n_units) issue(k + kStages);
         ++run_units;
-        if (u == u_begin) WRS_TR(1);
         WRS_TR(2);
-        if (has_next && gn.row == g.row && gn.part == g.part) continue;
+        if (has_next && qc.row == q.row && qc.part == q.part) continue;
 
-        // ---- end of a (row, partition) run: leave the partial in the slot of the run's first unit, arrive on the row
+        // ---- end of a (row, partition) run: leave the partial in the slot of the run's first unit
         run_finish(run, wb, p.K);
-        Partial* out = p.partials + (int64_t)g.row * p.upr + run_j0;
+        Partial* out = p.partials + (int64_t)q.row * p.upr + run_j0;
         if (lane < kMaxK) { out->v[lane] = run.rv; out->id[lane] = run.ri; }
         if (lane == 0) { out->m = run.m; out->s = run.s; out->n = run.n; }
-        const int units_done = run_units;
         run_reset(run);
-        run_j0 = j_n; run_units = 0;
-        __syncwarp();
-        int last = 0;
-        if (lane == 0) {
-            __threadfence();                             // cumulative: publishes the whole warp's partial (ordered by the syncwarp)
-            const int prev = atomicAdd(p.row_arrive + g.row, units_done);
-            last = (prev + units_done == p.upr) ? 1 : 0;  // every unit of the row has been folded into some partial
-            if (last) { p.row_arrive[g.row] = 0; __threadfence(); }   // self-reset for the next launch (stream-ordered)
-        }
-        last = __shfl_sync(0xffffffffu, last, 0);
-        if (!last) continue;
+        run_j0 = qc.j; run_units = 0;
+    }
 
-        // ---- this warp completed the row: merge it
-        const int row = g.row;
-        const RowPartials rpz = row_partials(p, row, Wt, N);
-        RowRules rr_row;
-        {
-            const int keep = rules_row, ka0 = abase[0], ka1 = abase[1];   // state of the prefetched unit must survive
-            const RowRules keep_rules = rules;
-            rules_for(row);
-            rr_row = rules;
-            rules = keep_rules; rules_row = keep; abase[0] = ka0; abase[1] = ka1;
-        }
+    WRS_TR(3);
+}
+
+// ---- launch 2 of a step: one CTA per group (an audio's beams; a single row for greedy / filter), one warp per row.
+//      Every warp merges its row's partials into k+1 log-probs; in beam mode warp 0 then runs the audio's beam update.
+template <int MODE>
+__global__ void __launch_bounds__(kMaxBeam * 32) decode_tail_kernel(const StepParams p) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned char* slice = smem_raw + warp * kTailBytes;             // [general tail tables | ...][scratch]
+    unsigned char* scratch = slice + kStageBytes;
+    WarpBuf& wb = *reinterpret_cast<WarpBuf*>(scratch);
+    const int row = (int)blockIdx.x * (MODE == MODE_BEAM ? p.beam : 1) + warp;
+    const Deal deal = deal_of(p.n_rows * p.upr, p.scan_warps);
 #ifdef WRS_TRACE
-        const unsigned long long tm0 = gtime();
+    const int gw = row;
+    if (lane == 0) for (int q = 4; q < 8; ++q) g_trace[gw * 8 + q] = 0;
+    const unsigned long long tm0 = gtime();
 #endif
+    {
+        const RowPartials rpz = row_partials(p, row, deal);
+        const RowRules rr_row = row_rules(p.rc, p.tokens + (int64_t)row * p.tok_stride, p.cur_len, p.sample_begin);
         // which later beams of this audio hold an identical prefix (HashMap key = whole sequence, beam_search.rs:74-77):
         // the first 32 positions of up to 4 later beams are fetched before the merge so both latencies overlap
-        const int bj = MODE == MODE_BEAM ? row % p.beam : 0, rbase = row - bj;
+        const int bj = MODE == MODE_BEAM ? warp : 0, rbase = row - bj;
         const int64_t* mine = p.tokens + (int64_t)row * p.tok_stride;
         int64_t pre_m = 0, pre_o[4] = {0, 0, 0, 0};
         if (MODE == MODE_BEAM && lane < p.cur_len) {
@@ -792,7 +830,9 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const Step
             for (int q = 0; q < 4; ++q)
                 if (bj + 1 + q < p.beam) pre_o[q] = p.tokens[(int64_t)(rbase + bj + 1 + q) * p.tok_stride + lane];
         }
-        const RowOut r = merge_row(p, row, rr_row.flags, rpz, Wt, N, wb);
+        if (lane == 0) wb.n = 0;
+        __syncwarp();
+        const RowOut r = merge_row(p, row, rr_row.flags, rpz, deal, wb);
         unsigned same = 0u;
         if (MODE == MODE_BEAM) {
             unsigned diff = 0u;
@@ -819,42 +859,27 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_step_kernel(const Step
         if (lane == 0 && p.dbg_flags) p.dbg_flags[row] = (uint8_t)r.flags;
         if (MODE == MODE_GREEDY) {
             greedy_tail(p, row, r);
-            __syncwarp();
         } else if (MODE == MODE_FILTER) {
             filter_tail(p, row, rr_row, r.flags);
         } else {
             RowResult* res = p.rowres + row;
             if (lane < kMaxK) { res->lp[lane] = r.lp; res->tok[lane] = lane < p.K ? r.tok : INT32_MAX; }
             if (lane == 0) { res->flags = r.flags; res->same = same; }
-            __syncwarp();
-            const int audio = row / p.beam;
-            int last_a = 0;
-            if (lane == 0) {
-                __threadfence();
-                const int prev = atomicAdd(p.audio_arrive + audio, 1);
-                last_a = (prev == p.beam - 1) ? 1 : 0;
-                if (last_a) { p.audio_arrive[audio] = 0; __threadfence(); }
-            }
-            last_a = __shfl_sync(0xffffffffu, last_a, 0);
-            if (last_a) {
-#ifdef WRS_TRACE
-                const unsigned long long tt0 = gtime();
-#endif
-                if (p.beam * p.K <= 32) beam_tail_fast(p, audio, *reinterpret_cast<FastTail*>(scratch));
-                else {
-                    asm volatile("cp.async.wait_group 0;" ::: "memory");     // the tables overlay the stage
-                    __syncwarp();
-                    beam_tail_general(p, audio, *reinterpret_cast<TailScratch*>(slice));
-                    __syncwarp();
-                    if (has_next) prefetch(gn, bm_n);
-                }
-#ifdef WRS_TRACE
-                WRS_TR_ADD(6, gtime() - tt0); WRS_TR_ADD(7, 1);
-#endif
-            }
         }
     }
-    WRS_TR(3);
+    if (MODE != MODE_BEAM) return;
+    __threadfence_block();
+    __syncthreads();                                     // the audio's row results are complete (same CTA wrote them)
+    if (warp != 0) return;
+#ifdef WRS_TRACE
+    const unsigned long long tt0 = gtime();
+#endif
+    const int audio = (int)blockIdx.x;
+    if (p.beam * p.K <= 32) beam_tail_fast(p, audio, *reinterpret_cast<FastTail*>(scratch));
+    else beam_tail_general(p, audio, *reinterpret_cast<TailScratch*>(slice));
+#ifdef WRS_TRACE
+    WRS_TR_ADD(6, gtime() - tt0); WRS_TR_ADD(7, 1);
+#endif
 }
 
 // ---- sparse in-place fills: logits.index_fill_(1, idx, -inf)   suppress_tokens.rs:22, suppress_blanks.rs:41
@@ -918,20 +943,26 @@ StepParams step_params(wrs_decoder* dec, const float* logits, int64_t row_stride
     return p;
 }
 
-// one persistent 512-thread CTA per SM at most; every warp gets at least one unit
+// Launch 1: one 512-thread CTA per SM at most, every warp gets at least one unit.  Launch 2: one CTA per group, one warp
+// per row.
 template <int MODE>
-int launch_step(wrs_decoder* dec, const StepParams& p, cudaStream_t stream) {
+int launch_step(wrs_decoder* dec, StepParams p, cudaStream_t stream) {
     wrs_ctx* ctx = dec->ctx;
-    const size_t smem = (size_t)kStepWarps * kWarpSmem;
+    const size_t smem = (size_t)kStepWarps * kWarpSmem, smem_tail = (size_t)kMaxBeam * kTailBytes;
     if (!dec->smem_attr_set) {
-        WRS_CUDA(ctx, cudaFuncSetAttribute(decode_step_kernel<MODE_BEAM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        WRS_CUDA(ctx, cudaFuncSetAttribute(decode_step_kernel<MODE_GREEDY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        WRS_CUDA(ctx, cudaFuncSetAttribute(decode_step_kernel<MODE_FILTER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        WRS_CUDA(ctx, cudaFuncSetAttribute(decode_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        WRS_CUDA(ctx, cudaFuncSetAttribute(decode_tail_kernel<MODE_BEAM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tail));
+        WRS_CUDA(ctx, cudaFuncSetAttribute(decode_tail_kernel<MODE_GREEDY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tail));
+        WRS_CUDA(ctx, cudaFuncSetAttribute(decode_tail_kernel<MODE_FILTER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tail));
         dec->smem_attr_set = true;
     }
     const int64_t units = (int64_t)p.n_rows * p.upr;
     const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctx->sm_count, (units + kStepWarps - 1) / kStepWarps));
-    decode_step_kernel<MODE><<<grid, kStepThreads, smem, stream>>>(p);
+    p.scan_warps = grid * kStepWarps;
+    decode_scan_kernel<<<grid, kStepThreads, smem, stream>>>(p);
+    WRS_CUDA(ctx, cudaGetLastError());
+    const int rows_per_group = MODE == MODE_BEAM ? p.beam : 1;
+    decode_tail_kernel<MODE><<<p.n_rows / rows_per_group, rows_per_group * 32, (size_t)rows_per_group * kTailBytes, stream>>>(p);
     WRS_CUDA(ctx, cudaGetLastError());
     return WRS_OK;
 }

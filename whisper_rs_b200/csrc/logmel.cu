@@ -19,6 +19,7 @@
 #include <algorithm>
 #include <cmath>
 
+#include "async_copy.cuh"
 #include "logmel_fft.cuh"
 #include "wrs_internal.cuh"
 
@@ -86,43 +87,6 @@ __device__ __forceinline__ float load_reflect(const float* __restrict__ seg, int
     if (i >= n) i = 2 * n - 2 - i;
     return (i >= 0 && i < n) ? __ldg(seg + i) : 0.0f;
 }
-
-// ---- async-proxy plumbing of the PCM tile (cp.async.bulk + mbarrier complete_tx)
-__device__ __forceinline__ unsigned smem_addr(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "WAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra DONE_%=;\n"
-        "bra WAIT_%=;\n"
-        "DONE_%=:\n"
-        "}\n" ::"r"(smem_addr(bar)), "r"(parity) : "memory");
-}
-__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_addr(dst)),
-                 "l"(src), "r"(bytes), "r"(smem_addr(bar))
-                 : "memory");
-}
-__device__ __forceinline__ bool elect_one() {        // true on exactly one lane of the (converged) warp
-    unsigned pred;
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "elect.sync _|p, 0xffffffff;\n"
-        "selp.u32 %0, 1, 0, p;\n"
-        "}\n" : "=r"(pred));
-    return pred != 0;
-}
-__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
 // The tile of slice (seg, fs) is rows fs-2 .. fs+64 of the segment cut into 160-sample rows.  Rows that lie entirely
 // inside the segment are one contiguous range of the input and move as bulk copies (16-byte aligned PCM); the rows
