@@ -14,6 +14,7 @@
 //                src/decode/filter/*.rs)
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "async_copy.cuh"
@@ -217,7 +218,7 @@ __device__ __forceinline__ RowPartials row_partials(const StepParams& p, int row
 // with independent 16-byte loads up front, so the usual row (<= 32 partials) costs ONE round trip to L2.
 struct RowOut { float lp; int tok; unsigned flags; };
 
-__device__ __noinline__ RowOut merge_row(const StepParams& p, int row, unsigned rule_flags, const RowPartials& rpz, const Deal& deal,
+__device__ __forceinline__ RowOut merge_row(const StepParams& p, int row, unsigned rule_flags, const RowPartials& rpz, const Deal& deal,
                                          WarpBuf& wb) {
     const int lane = threadIdx.x & 31;
     const int K = p.K, KQ = (K + 3) >> 2;
@@ -817,8 +818,11 @@ __global__ void __launch_bounds__(kMaxBeam * 32) decode_tail_kernel(const StepPa
     const unsigned long long tm0 = gtime();
 #endif
     {
+        // everything this row needs from memory is requested before the first use: its two newest tokens (rules), the
+        // token prefixes (beam dedup) and, inside merge_row, the partials
         const RowPartials rpz = row_partials(p, row, deal);
-        const RowRules rr_row = row_rules(p.rc, p.tokens + (int64_t)row * p.tok_stride, p.cur_len, p.sample_begin);
+        const int64_t* rt = p.tokens + (int64_t)row * p.tok_stride;
+        const int64_t tk_last = rt[p.cur_len - 1], tk_pen = p.cur_len >= 2 ? rt[p.cur_len - 2] : 0;
         // which later beams of this audio hold an identical prefix (HashMap key = whole sequence, beam_search.rs:74-77):
         // the first 32 positions of up to 4 later beams are fetched before the merge so both latencies overlap
         const int bj = MODE == MODE_BEAM ? warp : 0, rbase = row - bj;
@@ -832,7 +836,9 @@ __global__ void __launch_bounds__(kMaxBeam * 32) decode_tail_kernel(const StepPa
         }
         if (lane == 0) wb.n = 0;
         __syncwarp();
-        const RowOut r = merge_row(p, row, rr_row.flags, rpz, deal, wb);
+        RowOut r = merge_row(p, row, 0u, rpz, deal, wb);
+        const RowRules rr_row = row_rules_from(p.rc, tk_last, tk_pen, p.cur_len, p.sample_begin);
+        r.flags |= rr_row.flags;
         unsigned same = 0u;
         if (MODE == MODE_BEAM) {
             unsigned diff = 0u;
@@ -962,6 +968,7 @@ int launch_step(wrs_decoder* dec, StepParams p, cudaStream_t stream) {
     decode_scan_kernel<<<grid, kStepThreads, smem, stream>>>(p);
     WRS_CUDA(ctx, cudaGetLastError());
     const int rows_per_group = MODE == MODE_BEAM ? p.beam : 1;
+    // (programmatic dependent launch was measured and lost 3 us per step: the early tail CTAs only get in the scan's way)
     decode_tail_kernel<MODE><<<p.n_rows / rows_per_group, rows_per_group * 32, (size_t)rows_per_group * kTailBytes, stream>>>(p);
     WRS_CUDA(ctx, cudaGetLastError());
     return WRS_OK;
