@@ -159,7 +159,9 @@ __device__ __forceinline__ void reduce_unit(float (&x)[kNV][4], const Geom& g, u
     }
     __syncwarp();
     const int n_tot = wb.n;
-    if (n_tot <= kCandCap / 2) { run.np = n_tot; return; }
+    // once the list is full its K-th value is an exact bar and later units add only a few stragglers: those wait for a
+    // cheap register merge (list + pending <= 32 entries); the first unit of a run merges at once to set that bar
+    if (run.n >= K && n_tot + K <= 32) { run.np = n_tot; return; }
     if (n_tot <= kCandCap - kMaxK) run_merge(run, wb, n_tot, K);
     else {
         // massive ties: merge what was pending before this unit, then select exactly straight from the registers
@@ -655,10 +657,11 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const Step
 
     // ---- where unit k of this warp lives: needs nothing but the row pointer's alignment
     struct Place { int row, j, part, a0, c_lo, c_hi; };
-    auto place_of = [&](int k) {
+    struct Cursor { int row, j; };                        // (row, unit in row); a warp's units are consecutive
+    auto advance = [&](Cursor& c) { if (++c.j == p.upr) { c.j = 0; ++c.row; } };
+    auto place_at = [&](const Cursor& c) {
         Place q;
-        const int u = u_begin + k;
-        q.row = u / p.upr; q.j = u - q.row * p.upr;
+        q.row = c.row; q.j = c.j;
         const float* rp = p.logits + (int64_t)q.row * p.row_stride;
         int pb, pe;                                       // the partition's id range
         if (q.j < p.n_text_units) {
@@ -676,20 +679,27 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const Step
         if (q.row == p.n_rows - 1 && q.a0 + 4 * q.c_hi > p.rc.n_vocab) --q.c_hi;
         return q;
     };
-    // start the flight of unit k into stage k % kStages: one bulk copy, completion by byte count on the stage's mbarrier
-    auto issue = [&](int k) {
-        const Place q = place_of(k);
+    // start the flight of the next unit not yet requested into the next stage: one bulk copy, completion by byte
+    // count on the stage's mbarrier
+    const int row_first = u_begin / p.upr;
+    Cursor cur_issue = {row_first, u_begin - row_first * p.upr};
+    int stage_issue = 0, n_issued = 0;
+    auto issue_next = [&]() {
+        const Place q = place_at(cur_issue);
         if (elect_one()) {
-            unsigned long long* bar = bars + (k % kStages);
+            unsigned long long* bar = bars + stage_issue;
             const int bytes = (q.c_hi - q.c_lo) * 16;
             if (bytes > 0) {
                 mbar_expect_tx(bar, (unsigned)bytes);
-                bulk_g2s(reinterpret_cast<unsigned char*>(stage_of(k % kStages)) + 16 * q.c_lo,
+                bulk_g2s(reinterpret_cast<unsigned char*>(stage_of(stage_issue)) + 16 * q.c_lo,
                          p.logits + (int64_t)q.row * p.row_stride + q.a0 + 4 * q.c_lo, (unsigned)bytes, bar);
             } else {
                 mbar_arrive(bar);
             }
         }
+        advance(cur_issue);
+        stage_issue = stage_issue + 1 == kStages ? 0 : stage_issue + 1;
+        ++n_issued;
     };
     if (lane == 0) {
 #pragma unroll
@@ -697,10 +707,9 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const Step
     }
     __syncwarp();
     // every warp puts its first unit in flight before anything else
-    issue(0);
+    issue_next();
 
     // rules of the first two rows this warp touches are fetched up front (a later row change costs a bubble)
-    const int row_first = u_begin / p.upr;
     int64_t tk_last[2], tk_pen[2];
 #pragma unroll
     for (int q = 0; q < 2; ++q) {
@@ -731,8 +740,8 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const Step
     auto bitmap_of = [&](const Place& q) { return __ldg(p.bm + min((max(q.a0, 0) >> 5) + lane, p.bm_words - 1)); };
     // bring unit k into registers; slot j of a lane holds ids a0 + 4 (lane + 32 j) ..+3, everything outside [lo, hi)
     // reads as -inf
-    auto fetch = [&](int k, const Place& q, const Geom& g, float (&x)[kNV][4]) {
-        const float4* st = stage_of(k % kStages);
+    auto fetch = [&](int stage, const Place& q, const Geom& g, float (&x)[kNV][4]) {
+        const float4* st = stage_of(stage);
 #pragma unroll
         for (int j = 0; j < kNV; ++j) {
             const float4 v = st[lane + 32 * j];
@@ -755,24 +764,27 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const Step
 
     Run run;
     run_reset(run);
-    Place qc = place_of(0);
+    Cursor cur = {row_first, u_begin - row_first * p.upr};
+    Place qc = place_at(cur);
     uint32_t bm_c = bitmap_of(qc);
     int run_j0 = qc.j, run_units = 0;                    // first unit-in-row and unit count of the current run
+    int stage = 0;                                       // stage and mbarrier phase of the unit being folded
+    unsigned phase = 0u;
 
     for (int k = 0; k < n_units; ++k) {
         const Place q = qc;
         const uint32_t bmw = bm_c;
         const bool has_next = k + 1 < n_units;
         const Geom g = geom_of(q);
-        if (has_next) { qc = place_of(k + 1); bm_c = bitmap_of(qc); }
-        mbar_wait(bars + (k % kStages), (unsigned)(k / kStages) & 1u);   // also when nothing survives: the stage is reused
+        if (has_next) { advance(cur); qc = place_at(cur); bm_c = bitmap_of(qc); }
+        mbar_wait(bars + stage, phase);                  // also when nothing survives: the stage is reused
         if (k == 0) {
             // only now the later units: all first units of the grid (a quarter of the step's bytes) land first and
             // the arithmetic starts while the rest streams in behind them
             WRS_TR(1);
 #pragma unroll
             for (int k2 = 1; k2 < kStages; ++k2)
-                if (k2 < n_units) issue(k2);
+                if (k2 < n_units) issue_next();
         }
         if (run_units == 0) {                            // a run starts with an empty pending list (merges and tails share wb)
             if (lane == 0) wb.n = 0;
@@ -780,11 +792,12 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const Step
         }
         if (g.hi > g.lo) {
             float x[kNV][4];
-            fetch(k, q, g, x);
+            fetch(stage, q, g, x);
             reduce_unit(x, g, bmw, max(g.a0, 0) >> 5, p.K, wb, run);
         }
         __syncwarp();                                    // every lane has taken its share of the stage out
-        if (k + kStages < n_units) issue(k + kStages);
+        if (n_issued < n_units) issue_next();
+        if (++stage == kStages) { stage = 0; phase ^= 1u; }
         ++run_units;
         WRS_TR(2);
         if (has_next && qc.row == q.row && qc.part == q.part) continue;
