@@ -31,6 +31,11 @@ N_SEG, N_SAMPLES, N_MELS, N_FRAMES = 64, 480000, 80, 3000
 N_AUDIO, BEAM, VOCAB = 32, 5, 51865
 LOGMEL_BYTES_PER_SEG = N_SAMPLES * 4 + N_MELS * N_FRAMES * 4          # 2 880 000 B  
 DECODE_BYTES_PER_ROW = VOCAB * 4                                      # 207 460 B
+# dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed ncu --set full captures of this same
+# command (profiles/r1_v4_logmel_ncu.txt, profiles/r1_v4_decode_ncu.txt); re-measure when a kernel's traffic changes
+LOGMEL_DRAM_TRAFFIC_PER_LAUNCH = 122.96e6 + 28.82e6                   # 64 segments: PCM read once, output half evicted
+DECODE_DRAM_TRAFFIC_PER_STEP = 33.27e6                                # 160 rows: logits read once (scan launch)
+TRAFFIC_SOURCE = "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch (profiles/r1_v4_*_ncu.txt)"
 
 
 def peaks():
@@ -344,8 +349,10 @@ def main():
                    "logmel_mode": "fused single launch" if logmel_mode == 1 else "two launches",
                    "parallelism": f"segment-sharded x{world}, no collective"},
         "roofline": {"bound": "hbm", "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
-                     "traffic": None, "peak_source": peak_src, "frac_of_8TBps": ach / 8000.0,
-                     "algorithmic_bytes_per_launch": N_SEG * LOGMEL_BYTES_PER_SEG, "kernel": "wrs::logmel_kernel"},
+                     "traffic": LOGMEL_DRAM_TRAFFIC_PER_LAUNCH, "traffic_source": TRAFFIC_SOURCE,
+                     "peak_source": peak_src, "frac_of_8TBps": ach / 8000.0,
+                     "algorithmic_bytes_per_launch": N_SEG * LOGMEL_BYTES_PER_SEG,
+                     "kernel": "wrs::logmel_kernel<true> (persistent, cooperative; one launch per batch)"},
         "cpu_baseline": cpu,
         "e2e": {"value": world * N_SEG * e2e_steps / t_e2e, "unit": "segments/s",
                 "h2d_bytes_per_step": N_SEG * N_SAMPLES * 4, "d2h_bytes_per_step": N_SEG * N_MELS * N_FRAMES * 4,
@@ -361,15 +368,17 @@ def main():
                                    "TimestampTokens + log_softmax + top-6 + beam merge", "step_kind": "mixed histories",
                        "cache": f"logits rotate over {DBUF} buffers (266 MB > L2)"},
             "roofline": {"bound": "hbm", "achieved": dec_ach, "peak": hbm_peak, "unit": "GB/s", "frac": dec_ach / hbm_peak,
-                         "traffic": None, "frac_of_8TBps": dec_ach / 8000.0,
+                         "traffic": DECODE_DRAM_TRAFFIC_PER_STEP, "traffic_source": TRAFFIC_SOURCE,
+                         "frac_of_8TBps": dec_ach / 8000.0,
                          "algorithmic_bytes_per_launch": R * DECODE_BYTES_PER_ROW,
-                         "kernel": "wrs::decode_step_kernel<0> (scan + row merge + beam merge, one launch)"},
+                         "kernel": "wrs::decode_scan_kernel (reads the logits once) + wrs::decode_tail_kernel<0> (row merge, "
+                                   "beam update); achieved = algorithmic bytes / time of the whole two-launch step"},
             "cpu_baseline": cpu_dec,
             "e2e": {"value": e2e_dec["device_logits"], "unit": "row-steps/s", "h2d_bytes_per_step": 0,
                     "d2h_bytes_per_step": R * (Lcur + 1) * 8 + R * 4 + 4,
                     "api": "wrs_beam_step on device logits + D2H of tokens, scores, completed each step",
                     "with_host_logits": {"value": e2e_dec["host_logits"], "h2d_bytes_per_step": R * VOCAB * 4}},
-            "gpu_launches": dec_steps,
+            "gpu_launches": 2 * dec_steps,
         },
     }
     print(json.dumps(line), flush=True)

@@ -56,15 +56,18 @@ constexpr int kStageBytes = kUnit * 4;                    // landing zone of one
 constexpr int kScratchBytes = 2688;                      // per-warp scratch behind stage 0 (WarpBuf, or the fast beam tail's tables)
 constexpr int kTailBytes = kStageBytes + kScratchBytes;  // the general beam tail (beam > 5) overlays stage 0 + scratch
 constexpr int kWarpSmem = kStages * kStageBytes + kScratchBytes + 32;   // + the stages' mbarriers
+constexpr int kTailHead = kMaxBeam * 144;                // tail launch: the group's row results in front of the warp slices
 
 // what the row merge leaves for the audio-level tail
-struct __align__(16) RowResult {
+struct __align__(16) RowResult {                        // 144 bytes (kTailHead)
     float lp[kMaxK];
     int tok[kMaxK];
     unsigned flags;
     unsigned same;         // bit j2: beam j2 (> this row's beam index) holds an identical token prefix
     int pad[2];
 };
+
+static_assert(sizeof(RowResult) * kMaxBeam <= kTailHead, "row results do not fit the head of the tail launch's shared memory");
 
 struct StepParams {
     float* logits; int64_t row_stride;                   // read-only except MODE_FILTER
@@ -513,29 +516,42 @@ struct FastTail {
 };
 static_assert(sizeof(FastTail) <= kScratchBytes, "fast tail scratch does not fit the per-warp slice");
 
-__device__ __noinline__ void beam_tail_fast(const StepParams& p, int audio, FastTail& fs) {
+// what the fast tail needs from global memory that does not depend on the row merges: fetched by warp 0 before its own merge
+struct FastPre { float sum; int have; long long tv[8]; };
+__device__ __forceinline__ FastPre beam_tail_fast_prefetch(const StepParams& p, int audio) {
+    const int k = p.beam, K = p.K, n_c = k * K, L = p.cur_len;
+    const int lane = threadIdx.x & 31;
+    const int row0 = audio * k;
+    const int j = lane < n_c ? lane / K : 0;
+    FastPre pre;
+    pre.sum = p.sum_in[row0 + j];
+    pre.have = lane == 0 ? p.fin_n[audio] : 0;
+    if (k * L <= 256) {
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+            const int idx = lane + 32 * q;
+            const int jj = idx / L, t = idx - jj * L;
+            pre.tv[q] = idx < k * L ? p.tokens[(int64_t)(row0 + jj) * p.tok_stride + t] : 0;
+        }
+    }
+    return pre;
+}
+
+// rr_s: the audio's k row results in shared memory (written by the merging warps of this CTA)
+__device__ __forceinline__ void beam_tail_fast(const StepParams& p, int audio, FastTail& fs, const FastPre& pre, const RowResult* rr_s) {
     const int k = p.beam, K = p.K, n_c = k * K, L = p.cur_len;
     const int lane = threadIdx.x & 31;
     const int row0 = audio * k;
     const bool valid = lane < n_c;
     const int j = valid ? lane / K : 0, i = valid ? lane - j * K : 0;
-    // ---- phase 0: every load
-    const RowResult* rr = p.rowres + row0 + j;
-    const float lp = __ldcg(&rr->lp[i]);
-    int tok = __ldcg(&rr->tok[i]);
-    const unsigned fl = __ldcg(&rr->flags), same = __ldcg(&rr->same);
-    const float sum = p.sum_in[row0 + j];
-    int have = lane == 0 ? p.fin_n[audio] : 0;
+    const RowResult* rr = rr_s + j;
+    const float lp = rr->lp[i];
+    int tok = rr->tok[i];
+    const unsigned fl = rr->flags, same = rr->same;
+    const float sum = pre.sum;
+    int have = pre.have;
     const bool staged = k * L <= 256;
-    long long tv[8];
-    if (staged) {
-#pragma unroll
-        for (int q = 0; q < 8; ++q) {
-            const int idx = lane + 32 * q;
-            const int jj = idx / L, t = idx - jj * L;
-            tv[q] = idx < k * L ? p.tokens[(int64_t)(row0 + jj) * p.tok_stride + t] : 0;
-        }
-    }
+    const long long (&tv)[8] = pre.tv;
     // ---- candidates: score = f64(sum_logprobs[row]) + f64(logprob)   (beam_search.rs:70-71)
     const double score = (double)sum + (double)lp;
     const bool nan_seen = __any_sync(0xffffffffu, valid && (fl & 128u));
@@ -820,7 +836,8 @@ template <int MODE>
 __global__ void __launch_bounds__(kMaxBeam * 32) decode_tail_kernel(const StepParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    unsigned char* slice = smem_raw + warp * kTailBytes;             // [general tail tables | ...][scratch]
+    RowResult* rr_s = reinterpret_cast<RowResult*>(smem_raw);          // the group's row results, handed to warp 0
+    unsigned char* slice = smem_raw + kTailHead + warp * kTailBytes;   // [general tail tables | ...][scratch]
     unsigned char* scratch = slice + kStageBytes;
     WarpBuf& wb = *reinterpret_cast<WarpBuf*>(scratch);
     const int row = (int)blockIdx.x * (MODE == MODE_BEAM ? p.beam : 1) + warp;
@@ -849,6 +866,9 @@ __global__ void __launch_bounds__(kMaxBeam * 32) decode_tail_kernel(const StepPa
         }
         if (lane == 0) wb.n = 0;
         __syncwarp();
+        FastPre pre;
+        const bool fast_tail = MODE == MODE_BEAM && p.beam * p.K <= 32;
+        if (fast_tail && warp == 0) pre = beam_tail_fast_prefetch(p, (int)blockIdx.x);
         RowOut r = merge_row(p, row, 0u, rpz, deal, wb);
         const RowRules rr_row = row_rules_from(p.rc, tk_last, tk_pen, p.cur_len, p.sample_begin);
         r.flags |= rr_row.flags;
@@ -881,21 +901,29 @@ __global__ void __launch_bounds__(kMaxBeam * 32) decode_tail_kernel(const StepPa
         } else if (MODE == MODE_FILTER) {
             filter_tail(p, row, rr_row, r.flags);
         } else {
-            RowResult* res = p.rowres + row;
+            RowResult* res = fast_tail ? rr_s + warp : p.rowres + row;
             if (lane < kMaxK) { res->lp[lane] = r.lp; res->tok[lane] = lane < p.K ? r.tok : INT32_MAX; }
             if (lane == 0) { res->flags = r.flags; res->same = same; }
         }
+        if (MODE != MODE_BEAM) return;
+        __threadfence_block();
+        __syncthreads();                                 // the audio's row results are complete (same CTA wrote them)
+        if (warp != 0) return;
+        if (fast_tail) {
+#ifdef WRS_TRACE
+            const unsigned long long tt0 = gtime();
+#endif
+            beam_tail_fast(p, (int)blockIdx.x, *reinterpret_cast<FastTail*>(scratch), pre, rr_s);
+#ifdef WRS_TRACE
+            WRS_TR_ADD(6, gtime() - tt0); WRS_TR_ADD(7, 1);
+#endif
+            return;
+        }
     }
-    if (MODE != MODE_BEAM) return;
-    __threadfence_block();
-    __syncthreads();                                     // the audio's row results are complete (same CTA wrote them)
-    if (warp != 0) return;
 #ifdef WRS_TRACE
     const unsigned long long tt0 = gtime();
 #endif
-    const int audio = (int)blockIdx.x;
-    if (p.beam * p.K <= 32) beam_tail_fast(p, audio, *reinterpret_cast<FastTail*>(scratch));
-    else beam_tail_general(p, audio, *reinterpret_cast<TailScratch*>(slice));
+    beam_tail_general(p, (int)blockIdx.x, *reinterpret_cast<TailScratch*>(slice));
 #ifdef WRS_TRACE
     WRS_TR_ADD(6, gtime() - tt0); WRS_TR_ADD(7, 1);
 #endif
@@ -967,7 +995,7 @@ StepParams step_params(wrs_decoder* dec, const float* logits, int64_t row_stride
 template <int MODE>
 int launch_step(wrs_decoder* dec, StepParams p, cudaStream_t stream) {
     wrs_ctx* ctx = dec->ctx;
-    const size_t smem = (size_t)kStepWarps * kWarpSmem, smem_tail = (size_t)kMaxBeam * kTailBytes;
+    const size_t smem = (size_t)kStepWarps * kWarpSmem, smem_tail = (size_t)kTailHead + (size_t)kMaxBeam * kTailBytes;
     if (!dec->smem_attr_set) {
         WRS_CUDA(ctx, cudaFuncSetAttribute(decode_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         WRS_CUDA(ctx, cudaFuncSetAttribute(decode_tail_kernel<MODE_BEAM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tail));
@@ -982,7 +1010,7 @@ int launch_step(wrs_decoder* dec, StepParams p, cudaStream_t stream) {
     WRS_CUDA(ctx, cudaGetLastError());
     const int rows_per_group = MODE == MODE_BEAM ? p.beam : 1;
     // (programmatic dependent launch was measured and lost 3 us per step: the early tail CTAs only get in the scan's way)
-    decode_tail_kernel<MODE><<<p.n_rows / rows_per_group, rows_per_group * 32, (size_t)rows_per_group * kTailBytes, stream>>>(p);
+    decode_tail_kernel<MODE><<<p.n_rows / rows_per_group, rows_per_group * 32, (size_t)kTailHead + (size_t)rows_per_group * kTailBytes, stream>>>(p);
     WRS_CUDA(ctx, cudaGetLastError());
     return WRS_OK;
 }
