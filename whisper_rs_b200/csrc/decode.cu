@@ -191,16 +191,23 @@ __device__ __forceinline__ void run_finish(Run& run, WarpBuf& wb, int K) {
 
 // ---- N units are dealt to Wt warps in contiguous runs: the first r = N % Wt warps take q + 1 = N / Wt + 1 units, the
 //      others q (all 32-bit: n_rows < 32768 and a row has a few dozen units)
-struct Deal { int Wt, q, r; };
+struct Deal { int Wt, q, r; float inv_q, inv_q1; };
 __device__ __forceinline__ Deal deal_of(int N, int grid_warps) {
     Deal d;
     d.Wt = min(grid_warps, N); d.q = N / d.Wt; d.r = N - d.q * d.Wt;
+    d.inv_q = 1.0f / (float)d.q; d.inv_q1 = 1.0f / (float)(d.q + 1);
     return d;
 }
 __device__ __forceinline__ int deal_begin(const Deal& d, int g) { return g * d.q + min(g, d.r); }
+// owner of unit u: a float estimate (u < 2^21 is exact in fp32, the quotient is off by at most one) put right against
+// the owner's range -- an integer division by a run-time divisor costs several times as much
 __device__ __forceinline__ int unit_owner(const Deal& d, int u) {
     const int big = d.r * (d.q + 1);
-    return u < big ? u / (d.q + 1) : d.r + (u - big) / d.q;
+    int g = u < big ? (int)((float)u * d.inv_q1) : d.r + (int)((float)(u - big) * d.inv_q);
+    g = max(0, min(g, d.Wt - 1));
+    if (deal_begin(d, g) > u) --g;
+    else if (deal_begin(d, g + 1) <= u) ++g;
+    return g;
 }
 
 struct RowPartials { int first_owner[2], count[2], base[2]; };
