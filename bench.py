@@ -33,7 +33,7 @@ LOGMEL_BYTES_PER_SEG = N_SAMPLES * 4 + N_MELS * N_FRAMES * 4          # 2 880 00
 DECODE_BYTES_PER_ROW = VOCAB * 4                                      # 207 460 B
 # dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed ncu --set full captures of this same
 # command (profiles/r1_v4_logmel_ncu.txt, profiles/r1_v4_decode_ncu.txt); re-measure when a kernel's traffic changes
-LOGMEL_DRAM_TRAFFIC_PER_LAUNCH = 122.96e6 + 28.82e6                   # 64 segments: PCM read once, output half evicted
+LOGMEL_DRAM_TRAFFIC_PER_LAUNCH = 122.96e6 + 30.77e6                   # 64 segments: PCM read once, output half evicted
 DECODE_DRAM_TRAFFIC_PER_STEP = 33.27e6                                # 160 rows: logits read once (scan launch)
 TRAFFIC_SOURCE = "ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch (profiles/r1_v4_*_ncu.txt)"
 
