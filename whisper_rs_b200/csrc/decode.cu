@@ -800,7 +800,14 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const Step
         const bool has_next = k + 1 < n_units;
         const Geom g = geom_of(q);
         if (has_next) { advance(cur); qc = place_at(cur); bm_c = bitmap_of(qc); }
+#ifdef WRS_TRACE
+        const unsigned long long tw0 = gtime();
+#endif
         mbar_wait(bars + stage, phase);                  // also when nothing survives: the stage is reused
+#ifdef WRS_TRACE
+        const unsigned long long tw1 = gtime();
+        WRS_TR_ADD(4, tw1 - tw0);
+#endif
         if (k == 0) {
             // only now the later units: all first units of the grid (a quarter of the step's bytes) land first and
             // the arithmetic starts while the rest streams in behind them
@@ -819,6 +826,9 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const Step
             reduce_unit(x, g, bmw, max(g.a0, 0) >> 5, p.K, wb, run);
         }
         __syncwarp();                                    // every lane has taken its share of the stage out
+#ifdef WRS_TRACE
+        WRS_TR_ADD(5, gtime() - tw1);
+#endif
         if (n_issued < n_units) issue_next();
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
         ++run_units;
