@@ -316,6 +316,36 @@ def main():
         torch.cuda.synchronize()
         e2e_dec[name] = world * R * n / max_over_ranks(time.perf_counter() - t0)
     ctx.check(stream)
+
+    # ---------------- KV-cache beam reorder: base-shaped decoder, config 3 rows ----------------
+    # Cached::update_cache (src/model.rs:53-62) on every cached K/V of a 6-block, 512-wide decoder (examples/transcribe.rs
+    # dims): self-attention caches [160, 32, 512] and cross-attention caches [160, 1500, 512], f32, 24 tensors, one launch.
+    KV_LAYERS, KV_STATE, KV_SELF, KV_CROSS = 6, 512, 32, 1500
+    kv_src, kv_dst = [], []
+    for _ in range(KV_LAYERS):
+        for ctx_len in (KV_SELF, KV_SELF, KV_CROSS, KV_CROSS):       # self K, self V, cross K, cross V
+            kv_src.append(torch.empty((R, ctx_len, KV_STATE), dtype=torch.float32, device=dev).normal_())
+            kv_dst.append(torch.empty_like(kv_src[-1]))
+    kv_bytes = 2 * sum(t.numel() * 4 for t in kv_src)                # every byte read once and written once
+    rng = np.random.default_rng(7 + rank)
+    kv_idx = torch.from_numpy(np.concatenate([a * BEAM + rng.integers(0, BEAM, size=BEAM) for a in range(N_AUDIO)])
+                              .astype(np.int32)).to(dev)
+    from whisper_rs_b200 import cache as wcache
+
+    def kv_step(i):
+        if i % 2 == 0:
+            wcache.update_cache(kv_src, kv_idx, kv_dst)
+        else:
+            wcache.update_cache(kv_dst, kv_idx, kv_src)
+
+    kv_steps = max(4, min(args.steps, 40))
+    for i in range(4):
+        kv_step(i)
+    t_kv = max_over_ranks(timed(kv_step, kv_steps, barrier))
+    kv_ach = kv_bytes / (t_kv / kv_steps) / 1e9
+    kv_ok = bool(torch.equal(kv_src[2][kv_idx.long()], wcache.update_cache(kv_src[2:3], kv_idx)[0]))
+    ctx.check(stream)
+    del kv_src, kv_dst
     t_gpu1 = time.time()
     clocks = sampler.stop(t_gpu0, t_gpu1) if sampler else None
 
@@ -338,6 +368,22 @@ def main():
         td = cpu_decode_time({k: (v.copy() if isinstance(v, np.ndarray) else v) for k, v in case.items()}, ids, nd, threads)
         cpu_dec = {"value": R * nd / td, "unit": "row-steps/s", "cores": threads, "kind": "port",
                    "sample": f"{nd} steps of 160 rows x V {VOCAB}: 3 filters + BeamSearchTokenExtractor::update restatement"}
+
+    cpu_kv = None
+    if world == 1 and not args.no_cpu_baseline:
+        from oracle import cache as ocache
+        torch.set_num_threads(threads)
+        blk = [torch.randn((R, n, KV_STATE)) for n in (KV_SELF, KV_SELF, KV_CROSS, KV_CROSS)]
+        hidx = kv_idx.cpu().long()
+        ocache.update_cache(blk, hidx)
+        reps = 3
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            ocache.update_cache(blk, hidx)
+        tk = (time.perf_counter() - t0) / reps * KV_LAYERS           # one block timed, scaled to the decoder's six
+        cpu_kv = {"value": R / tk, "unit": "row-steps/s", "cores": threads, "kind": "port",
+                  "sample": f"one of the {KV_LAYERS} decoder blocks (4 tensors, 1.0 GB read + 1.0 GB written), x{KV_LAYERS}: "
+                            "torch CPU Tensor.index, the call src/model.rs:59 makes"}
 
     line = {
         "metric": "log-mels/s (30 s segments)", "value": seg_per_s, "unit": "segments/s", "n_gpus": world,
@@ -379,6 +425,17 @@ def main():
                     "api": "wrs_beam_step on device logits + D2H of tokens, scores, completed each step",
                     "with_host_logits": {"value": e2e_dec["host_logits"], "h2d_bytes_per_step": R * VOCAB * 4}},
             "gpu_launches": 2 * dec_steps,
+        },
+        "kv_reorder": {
+            "metric": "KV-cache beam reorder", "value": world * R * kv_steps / t_kv, "unit": "row-steps/s",
+            "ms_per_step": 1e3 * t_kv / kv_steps, "steps": kv_steps,
+            "config": {"workload": f"Cached::update_cache on a base-shaped decoder: {KV_LAYERS} blocks x (self K, V "
+                                   f"[{R}, {KV_SELF}, {KV_STATE}] + cross K, V [{R}, {KV_CROSS}, {KV_STATE}]) f32, 24 tensors, "
+                                   f"one launch, beam-shaped source indices",
+                       "cache": "12 GB of caches per step, ping-pong between two sets (>> L2)"},
+            "roofline": {"bound": "hbm", "achieved": kv_ach, "peak": hbm_peak, "unit": "GB/s", "frac": kv_ach / hbm_peak,
+                         "traffic": None, "algorithmic_bytes_per_launch": kv_bytes, "kernel": "wrs::kv_reorder_kernel"},
+            "cpu_baseline": cpu_kv, "parity_spot_check": kv_ok, "gpu_launches": kv_steps,
         },
     }
     print(json.dumps(line), flush=True)

@@ -189,6 +189,23 @@ int wrs_beam_finalize(wrs_decoder* dec, const int64_t* tokens, int64_t tok_strid
 int wrs_rank_max_likelihood_host(const double* sum_logprobs_host, const int32_t* lengths_host, int32_t n_audio,
                                  int32_t n_cand, int32_t has_penalty, double alpha, int32_t* selected_host);
 
+/* ------------------------------------------------------------------------------------------------
+ * KV-cache beam reorder: Cached::update_cache  src/model.rs:53-62  (cache.index(&[Some(sources_indices)]))
+ * applied to every cached tensor of the decoder (src/model.rs:208-211, 321-327, 524-528, 591-594) in one launch.
+ * tensors_host: n_tensors descriptors of device arrays [n_rows][row_bytes] with contiguous rows;
+ * dst[i][r] = src[i][source_idx[r]], source_idx a DEVICE array [n_rows] (the one wrs_beam_step writes).
+ * src != dst (ping-pong the two buffers between steps).  An index outside [0, n_rows) copies the row's own
+ * source and is reported by wrs_ctx_check (WRS_ERR_INVALID).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct {
+    const void* src;
+    void* dst;
+    int64_t row_bytes;
+} wrs_kv_tensor;
+
+int wrs_kv_reorder(wrs_ctx* ctx, const wrs_kv_tensor* tensors_host, int32_t n_tensors, int64_t n_rows,
+                   const int32_t* source_idx, wrs_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -31,6 +31,11 @@ class StepDebug(C.Structure):
                 ("fin_count", C.c_void_p), ("fin_source", C.c_void_p), ("fin_score", C.c_void_p)]
 
 
+class KvTensor(C.Structure):
+    """wrs_kv_tensor (include/wrs.h): one cached K or V array, rows contiguous."""
+    _fields_ = [("src", C.c_void_p), ("dst", C.c_void_p), ("row_bytes", C.c_int64)]
+
+
 # name -> (restype, argtypes); every symbol declared in include/wrs.h
 _P, _I32, _I64, _F, _D = C.c_void_p, C.c_int32, C.c_int64, C.c_float, C.c_double
 SIGNATURES = {
@@ -56,6 +61,7 @@ SIGNATURES = {
                                   C.POINTER(StepDebug), _P]),
     "wrs_beam_finalize": (C.c_int, [_P, _P, _I64, _I64, _I64, _P, _I32, _P, _P, _P, _P, _P]),
     "wrs_rank_max_likelihood_host": (C.c_int, [_P, _P, _I32, _I32, _I32, _D, _P]),
+    "wrs_kv_reorder": (C.c_int, [_P, C.POINTER(KvTensor), _I32, _I64, _P, _P]),
 }
 
 _lib = None

@@ -136,9 +136,10 @@ int wrs_ctx_check(wrs_ctx* ctx, wrs_stream_t stream) {
     wrs::DevStatus st;
     WRS_CUDA(ctx, cudaMemcpyAsync(&st, ctx->d_status, sizeof(st), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     WRS_CUDA(ctx, cudaStreamSynchronize((cudaStream_t)stream));
-    if (st.timeout || st.nan_rows) {
+    if (st.timeout || st.nan_rows || st.bad_index) {
         WRS_CUDA(ctx, cudaMemsetAsync(ctx->d_status, 0, sizeof(st), (cudaStream_t)stream));
         if (st.timeout) return wrs::fail(ctx, WRS_ERR_TIMEOUT, "device-side bounded wait expired");
+        if (st.bad_index) return wrs::fail(ctx, WRS_ERR_INVALID, "wrs_kv_reorder: a source index was outside [0, n_rows)");
         return wrs::fail(ctx, WRS_ERR_NUMERIC, "NaN reached the softmax (the reference panics here)");
     }
     return WRS_OK;

@@ -30,6 +30,8 @@ struct MelBank {
 struct DevStatus {
     int timeout;
     int nan_rows;
+    int bad_index;      // K3: a source index outside [0, n_rows)
+    int pad;
 };
 
 }  // namespace wrs
