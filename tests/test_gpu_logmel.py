@@ -104,6 +104,25 @@ def test_reference_signature_whole_clip_and_custom_filter():
     assert (got.cpu() - want).abs().max().item() <= TOL
 
 
+def test_long_clip_takes_the_two_launch_form():
+    """a whole clip as one segment (src/transcribe.rs:112, maximum over the clip).  More slices than
+    the grid holds in one round cannot use the in-kernel hand-over (waits could become circular): two launches."""
+    from whisper_rs_b200 import _lib
+    x = synth.audio_segment("am_noise", 11, 12 * 60 * 16000)                # 72 000 frames, 1125 slices
+    got = audio.log_mel_spectrogram(torch.from_numpy(x).cuda(), audio.mel_filter())
+    assert _lib.context(0).get_stat("logmel_mode") == 0
+    want = oa.log_mel_spectrogram(torch.from_numpy(x), oa.mel_filter())
+    assert got.shape == (80, 72000)
+    assert (got.cpu() - want).abs().max().item() <= TOL
+    # seek windowing of the clip's mel (src/transcribe.rs:150-152): narrow to a window, pad_or_trim to 3000 frames
+    for seek in (0, 40000, 71000):
+        win = got[:, seek:seek + C.N_FRAMES]
+        w = audio.pad_or_trim(win, C.N_FRAMES)
+        ref = oa.pad_or_trim(want[:, seek:seek + C.N_FRAMES], C.N_FRAMES)
+        assert w.shape == (80, C.N_FRAMES) and torch.equal(w.cpu(), torch.where(ref == 0, ref, w.cpu()))
+        assert (w.cpu() - ref).abs().max().item() <= TOL
+
+
 def test_host_entry_point_matches_device_entry_point():
     pcm = synth.audio_batch(5, seed=40, n_samples=160 * 500)
     host = audio.log_mel_spectrogram_batch(torch.from_numpy(pcm))       # wrs_logmel_batch_host

@@ -603,7 +603,21 @@ int wrs_logmel_batch(wrs_ctx* ctx, const float* pcm, int64_t n_segments, int64_t
     p.bank = ctx->d_bank;
     p.status = ctx->d_status;
 
-    const bool fused = ctx->opt_logmel_fused != 0;
+    const size_t smem = sizeof(LogmelSmem);
+    if (ctx->logmel_max_ctas_per_sm == 0) {
+        WRS_CUDA(ctx, cudaFuncSetAttribute(logmel_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        WRS_CUDA(ctx, cudaFuncSetAttribute(logmel_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int occ = 0;
+        WRS_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, logmel_kernel<true>, kThreads, smem));
+        if (occ < 1) return fail(ctx, WRS_ERR_CUDA, "logmel kernel does not fit on an SM");
+        ctx->logmel_max_ctas_per_sm = occ;
+    }
+    const int resident = ctx->sm_count * ctx->logmel_max_ctas_per_sm;
+    const int grid = (int)std::min<int64_t>(total, resident);
+    // The single fused launch needs a segment's slices to be dealt within one round of the grid: then every slice is
+    // posted by a CTA that has not had to wait yet, and no wait can be circular.  Longer segments (a whole clip as one
+    // "segment": src/transcribe.rs:112 takes the maximum over the clip) take the two-launch form.
+    const bool fused = ctx->opt_logmel_fused != 0 && p.slices_per_seg <= grid;
     const int64_t need = fused ? total : n_segments;     // fused: one word per slice; two launches: one per segment
     if (need > ctx->seg_cap) {
         WRS_CUDA(ctx, cudaStreamSynchronize(stream));
@@ -618,17 +632,6 @@ int wrs_logmel_batch(wrs_ctx* ctx, const float* pcm, int64_t n_segments, int64_t
     // 0x80808080: kSlotEmpty for the per-slice words, and (decoding to about -3.4e38) "minus infinity" for atomicMax
     WRS_CUDA(ctx, cudaMemsetAsync(ctx->d_seg_state, 0x80, sizeof(int) * need, stream));
 
-    const size_t smem = sizeof(LogmelSmem);
-    if (ctx->logmel_max_ctas_per_sm == 0) {
-        WRS_CUDA(ctx, cudaFuncSetAttribute(logmel_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        WRS_CUDA(ctx, cudaFuncSetAttribute(logmel_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        int occ = 0;
-        WRS_CUDA(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, logmel_kernel<true>, kThreads, smem));
-        if (occ < 1) return fail(ctx, WRS_ERR_CUDA, "logmel kernel does not fit on an SM");
-        ctx->logmel_max_ctas_per_sm = occ;
-    }
-    const int resident = ctx->sm_count * ctx->logmel_max_ctas_per_sm;
-    const int grid = (int)std::min<int64_t>(total, resident);
     // fused: the floor/scale of a slice is applied one slice later by the CTA that produced it, once the segment's
     // other slices (all owned by co-resident CTAs: cooperative launch) have posted their maxima
     ctx->stat_last_logmel_mode = fused ? 1 : 0;
