@@ -292,6 +292,20 @@ def main():
     rows_per_s = world * R * dec_steps / t_dec
     dec_ach = R * DECODE_BYTES_PER_ROW / (t_dec / dec_steps) / 1e9
 
+    # step-0 no-speech probability (src/decode/mod.rs:250-255): one unfiltered softmax per row
+    d_ns = torch.empty(R, dtype=torch.float32, device=dev)
+    ns_graph = torch.cuda.CUDAGraph()
+    torch.cuda.synchronize()
+    with torch.cuda.graph(ns_graph, stream=cap_stream):
+        cs = torch.cuda.current_stream(dev).cuda_stream
+        for b in range(GSTEPS):
+            lg = d_logits[b]
+            _lib.check(L.wrs_no_speech_probs(dec.handle, lg.data_ptr(), lg.stride(0), R, d_ns.data_ptr(), cs), ctx.handle)
+    for i in range(3):
+        ns_graph.replay()
+    t_ns = max_over_ranks(timed(lambda i: ns_graph.replay(), n_replays, barrier))
+    ns_ach = R * DECODE_BYTES_PER_ROW / (t_ns / dec_steps) / 1e9
+
     # end to end as the reference's caller sees it (decode/mod.rs:257-276): logits are already on the device
     # (north_star: raw device pointers from the tch forward), the host reads back tokens + scores + completed.
     def decode_e2e(i, h2d_logits):
@@ -425,6 +439,16 @@ def main():
                     "api": "wrs_beam_step on device logits + D2H of tokens, scores, completed each step",
                     "with_host_logits": {"value": e2e_dec["host_logits"], "h2d_bytes_per_step": R * VOCAB * 4}},
             "gpu_launches": 2 * dec_steps,
+        },
+        "no_speech_probs": {
+            "metric": "step-0 no-speech probability", "value": world * R * dec_steps / t_ns, "unit": "row-steps/s",
+            "ms_per_step": 1e3 * t_ns / dec_steps, "steps": dec_steps,
+            "config": {"workload": f"softmax over the unfiltered row, P(<|nospeech|>): {R} rows x V {VOCAB} (src/decode/mod.rs:250-255)",
+                       "launch": f"CUDA graph of {GSTEPS} calls replayed {n_replays}x"},
+            "roofline": {"bound": "hbm", "achieved": ns_ach, "peak": hbm_peak, "unit": "GB/s", "frac": ns_ach / hbm_peak,
+                         "traffic": None, "algorithmic_bytes_per_launch": R * DECODE_BYTES_PER_ROW,
+                         "kernel": "wrs::no_speech_kernel"},
+            "gpu_launches": dec_steps,
         },
         "kv_reorder": {
             "metric": "KV-cache beam reorder", "value": world * R * kv_steps / t_kv, "unit": "row-steps/s",

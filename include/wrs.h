@@ -189,6 +189,16 @@ int wrs_beam_finalize(wrs_decoder* dec, const int64_t* tokens, int64_t tok_strid
 int wrs_rank_max_likelihood_host(const double* sum_logprobs_host, const int32_t* lengths_host, int32_t n_audio,
                                  int32_t n_cand, int32_t has_penalty, double alpha, int32_t* selected_host);
 
+/* Step-0 no-speech probability  src/decode/mod.rs:250-255:
+ *   probs_at_sot = logits.i((.., sot_idx)).softmax(-1); no_speech_probs = probs_at_sot[.., token_id_no_speech]
+ * `logits` is the UNFILTERED row at sot_idx (the last position of the first forward pass: sot is the last initial token,
+ * src/decode/mod.rs:46-66), [n_rows][row_stride] f32 on the device; out_probs [n_rows] f32 on the device. */
+int wrs_no_speech_probs(wrs_decoder* dec, const float* logits, int64_t row_stride, int64_t n_rows, float* out_probs,
+                        wrs_stream_t stream);
+
+/* avg_logprob of the selected candidates  src/decode/mod.rs:389-397 (pure host): sum_logprob / (n_tokens + 1). */
+int wrs_avg_logprob_host(const double* sum_logprobs_host, const int32_t* n_tokens_host, int32_t n, double* out_host);
+
 /* ------------------------------------------------------------------------------------------------
  * KV-cache beam reorder: Cached::update_cache  src/model.rs:53-62  (cache.index(&[Some(sources_indices)]))
  * applied to every cached tensor of the decoder (src/model.rs:208-211, 321-327, 524-528, 591-594) in one launch.

@@ -368,3 +368,14 @@ def decode_step_reference(case: dict, ids, opt: Optional[DecodeOptions] = None, 
                fin_count=fin_count, fin_score=fin_score, completed=np.array(completed),
                stored_finished=np.array([len(s) for s in ex.finished_sequences], dtype=np.int32))
     return res
+
+
+def no_speech_probs(logits: torch.Tensor, no_speech: int) -> torch.Tensor:
+    """src/decode/mod.rs:250-255: `logits.i((.., sot_idx)).softmax(-1)` then column token_id_no_speech.
+    `logits` is the [rows, V] slice at sot_idx (unfiltered)."""
+    return logits.softmax(-1)[:, no_speech]
+
+
+def avg_logprobs(sum_logprobs, n_tokens):
+    """src/decode/mod.rs:389-397: lp / (t.size()[0] as f64 + 1.)."""
+    return [float(lp) / (float(n) + 1.0) for lp, n in zip(sum_logprobs, n_tokens)]

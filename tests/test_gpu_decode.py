@@ -134,3 +134,25 @@ def test_option_combinations(timestamps, suppress_blank, non_speech, mit):
         if not timestamps:
             want["row_flags"] = np.zeros_like(got["row_flags"])
         assert_beam_parity(got, want, 5)
+
+
+def test_no_speech_probs_match_softmax():
+    """SURVEY.md 8f row 2 (src/decode/mod.rs:250-255): probability of <|nospeech|> under the unfiltered softmax."""
+    from whisper_rs_b200.decode import core
+    for ids, rows in ((C.MULTILINGUAL, 160), (C.GPT2_EN, 7)):
+        g = torch.Generator().manual_seed(rows)
+        logits = 3.0 * torch.randn((rows, ids.n_vocab), generator=g)
+        logits[1, ids.no_speech] += 12.0                      # a confident "no speech" row
+        logits[2, 17] = float("-inf")                         # masked entries upstream are legal inputs
+        prompt = wd.DecodePrompt(None, ids)
+        step = wd.FusedDecodeStep(wd.DecodeOptions(), ids, [prompt], max_rows=rows if rows % 5 == 0 else 10)
+        got = step.decoder.no_speech_probs(logits[:step.decoder.max_rows].cuda())
+        want = od.no_speech_probs(logits[:step.decoder.max_rows], ids.no_speech)
+        assert np.allclose(got.cpu().numpy(), want.numpy(), rtol=2e-5, atol=1e-12)   # f32 softmax, different summation order
+    # strided rows (the reference slices [R, T, V] at sot_idx: row stride T * V)
+    big = 3.0 * torch.randn((10, 3, C.MULTILINGUAL.n_vocab), generator=torch.Generator().manual_seed(5))
+    dev = big.cuda()
+    step = wd.FusedDecodeStep(wd.DecodeOptions(), C.MULTILINGUAL, [wd.DecodePrompt(None, C.MULTILINGUAL)], max_rows=10)
+    got = step.decoder.no_speech_probs(dev[:, 2])
+    assert np.allclose(got.cpu().numpy(), od.no_speech_probs(big[:, 2], C.MULTILINGUAL.no_speech).numpy(), rtol=2e-5, atol=1e-12)
+    assert np.allclose(core.avg_logprobs([-3.0, -10.5], [5, 20]), od.avg_logprobs([-3.0, -10.5], [5, 20]))

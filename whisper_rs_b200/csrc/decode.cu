@@ -1122,6 +1122,15 @@ void wrs_decoder_destroy(wrs_decoder* d) {
     delete d;
 }
 
+// internal (not in wrs.h): what no_speech.cu borrows from a decoder -- the partial buffer as {max, sum} pairs
+// ([max_rows][units per row] x 144 B is far more than [max_rows][8] x 8 B) and the self-resetting row counters
+int wrs_decoder_scratch_(wrs_decoder* dec, wrs_ctx** ctx, int32_t* max_rows, int32_t* n_vocab, int32_t* no_speech,
+                         void** pairs, int32_t** counters) {
+    *ctx = dec->ctx; *max_rows = dec->max_rows; *n_vocab = dec->cfg.n_vocab; *no_speech = dec->cfg.no_speech;
+    *pairs = dec->d_partials; *counters = dec->d_arrive;
+    return WRS_OK;
+}
+
 int wrs_decoder_reset(wrs_decoder* d, wrs_stream_t stream) {
     if (!d) return fail(nullptr, WRS_ERR_INVALID, "wrs_decoder_reset: null decoder");
     WRS_CUDA(d->ctx, cudaSetDevice(d->ctx->device));

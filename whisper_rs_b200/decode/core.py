@@ -181,6 +181,16 @@ class Decoder:
             out.update(bufs)
         return out
 
+    def no_speech_probs(self, logits: torch.Tensor) -> torch.Tensor:
+        """src/decode/mod.rs:250-255: softmax of the unfiltered step-0 logits row at sot_idx, probability of
+        token_id_no_speech -> [rows] f32 on the device."""
+        if logits.dtype != torch.float32 or logits.dim() != 2 or logits.stride(1) != 1 or not logits.is_cuda:
+            raise TypeError("logits must be a CUDA f32 [rows, vocab] tensor with unit inner stride")
+        out = torch.empty(logits.shape[0], dtype=torch.float32, device=self.device)
+        _lib.check(_lib.lib().wrs_no_speech_probs(self.handle, logits.data_ptr(), logits.stride(0), logits.shape[0],
+                                                  out.data_ptr(), self._stream()), self.ctx.handle)
+        return out
+
     def greedy_step(self, logits, tokens, sample_begin, sum_logprobs, next_tokens=None, sum_out=None, debug=False):
         self._check_io(logits, tokens)
         R, L = tokens.shape
@@ -220,3 +230,13 @@ class Decoder:
         if len({int(n) for n in out_n}) != 1:
             raise RuntimeError("ragged candidate lists (the reference panics in Tensor::stack, beam_search.rs:203)")
         return cands, out_sc[:, :int(out_n[0])].copy()
+
+
+def avg_logprobs(sum_logprobs: Sequence[float], n_tokens: Sequence[int]) -> np.ndarray:
+    """src/decode/mod.rs:389-397: sum_logprob / (len(tokens) + 1) per selected candidate (host arithmetic, f64)."""
+    lp = np.ascontiguousarray(sum_logprobs, dtype=np.float64)
+    nt = np.ascontiguousarray(n_tokens, dtype=np.int32)
+    out = np.empty(len(lp), dtype=np.float64)
+    _lib.check(_lib.lib().wrs_avg_logprob_host(lp.ctypes.data_as(C.c_void_p), nt.ctypes.data_as(C.c_void_p), len(lp),
+                                               out.ctypes.data_as(C.c_void_p)))
+    return out
