@@ -301,6 +301,35 @@ __device__ __forceinline__ RowOut merge_row(const StepParams& p, int row, unsign
     const float logtot = nan_seen ? CUDART_NAN_F : logf(tot);
     if (Mx == -CUDART_INF_F) r.flags |= 128u;   // everything masked: the reference yields NaN log-probs
     // ---- pass B: candidates of the surviving partitions (each partial's list is sorted: entry 0 is its maximum)
+    if (cnt <= 32) {
+        // the usual row: one partial per lane.  K rounds of "best head wins, its lane moves on to its next entry"
+        // (value desc, id asc; ids are unique across partials) -- a k-way merge of sorted lists, two warp reductions
+        // per output
+        int pn = (int)__float_as_int(h0.z);
+        const bool alive = lane < cnt && (lane >= cT || !ts_over_text);
+        pn = alive ? min(pn, K) : 0;
+        int taken = 0;
+        float hv = pn > 0 ? ev0[0] : -CUDART_INF_F;
+        int hi = pn > 0 ? ei0[0] : INT32_MAX;
+        float ov = -CUDART_INF_F; int oi = INT32_MAX;
+        for (int rnd = 0; rnd < K; ++rnd) {
+            const float m = warp_max(hv);
+            if (m == -CUDART_INF_F) break;
+            const int w = __reduce_min_sync(0xffffffffu, hv == m ? hi : INT32_MAX);
+            if (lane == rnd) { ov = m; oi = w; }
+            if (hv == m && hi == w) {
+                ++taken;
+#pragma unroll
+                for (int e = 0; e + 1 < kMaxK; ++e) { ev0[e] = ev0[e + 1]; ei0[e] = ei0[e + 1]; }
+                ev0[kMaxK - 1] = -CUDART_INF_F;
+                hv = taken < pn ? ev0[0] : -CUDART_INF_F;
+                hi = taken < pn ? ei0[0] : INT32_MAX;
+            }
+        }
+        r.tok = oi;
+        r.lp = (ov - Mx) - logtot;
+        return r;
+    }
     Run cand;
     run_reset(cand);
     for (int rr = 0; 32 * rr < cnt; ++rr) {
