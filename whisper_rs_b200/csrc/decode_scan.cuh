@@ -154,6 +154,18 @@ __device__ __forceinline__ void run_reset(Run& run) {
     run.m = -CUDART_INF_F; run.s = 0.0f; run.rv = -CUDART_INF_F; run.ri = INT32_MAX; run.n = 0; run.np = 0;
 }
 
+// Many candidates: rank-sort in shared memory (the old list is appended behind the new candidates).  Out of line and
+// by value: it is rare, and inlined three times it made up a sixth of the scan kernel's code.
+__device__ __noinline__ Run run_merge_slow(Run run, WarpBuf& wb, int n_new, int K) {
+    const int lane = threadIdx.x & 31;
+    if (lane < run.n) { wb.v[n_new + lane] = run.rv; wb.id[n_new + lane] = run.ri; }
+    __syncwarp();
+    const int n = warp_compact(wb, n_new + run.n, K);
+    run.rv = lane < n ? wb.v[lane] : -CUDART_INF_F; run.ri = lane < n ? wb.id[lane] : INT32_MAX; run.n = n;
+    __syncwarp();
+    return run;
+}
+
 // Merge the n_new gathered candidates wb[0, n_new) into the run's list, keeping the best K.
 __device__ __forceinline__ void run_merge(Run& run, WarpBuf& wb, int n_new, int K) {
     const int lane = threadIdx.x & 31;
@@ -177,12 +189,7 @@ __device__ __forceinline__ void run_merge(Run& run, WarpBuf& wb, int n_new, int 
         __syncwarp();
         return;
     }
-    // many candidates: rank-sort in shared memory (the old list is appended behind the new candidates)
-    if (lane < run.n) { wb.v[n_new + lane] = run.rv; wb.id[n_new + lane] = run.ri; }
-    __syncwarp();
-    const int n = warp_compact(wb, n_new + run.n, K);
-    run.rv = lane < n ? wb.v[lane] : -CUDART_INF_F; run.ri = lane < n ? wb.id[lane] : INT32_MAX; run.n = n;
-    __syncwarp();
+    run = run_merge_slow(run, wb, n_new, K);
 }
 
 // Exact fallback for massive ties: K rounds of warp-wide selection over {run list} U {the lane's NE elements}, each
