@@ -379,3 +379,68 @@ def no_speech_probs(logits: torch.Tensor, no_speech: int) -> torch.Tensor:
 def avg_logprobs(sum_logprobs, n_tokens):
     """src/decode/mod.rs:389-397: lp / (t.size()[0] as f64 + 1.)."""
     return [float(lp) / (float(n) + 1.0) for lp, n in zip(sum_logprobs, n_tokens)]
+
+
+# --------------------------------------------------------------------------------------------------
+# DecodeTask  (src/decode/mod.rs:220-418): main_loop + run_inner around a caller-supplied model
+# --------------------------------------------------------------------------------------------------
+@dataclass
+class DecodeOutput:
+    tokens: List[int]
+    avg_logprob: float
+    no_speech_prob: float
+    sum_logprob: float
+    n_steps: int
+
+
+def decode_task_reference(model, ids, opt: DecodeOptions, mel: torch.Tensor, prompt: Optional[torch.Tensor] = None,
+                          trace: Optional[list] = None) -> List[DecodeOutput]:
+    """`DecodeTask::run` with the filters / extractor / ranker of this file on CPU copies of the logits.  `model` is
+    the duck-typed forward of whisper_rs_b200.decode.task (it may live on any device); its `update_cache` receives
+    the extractor's source rows like beam_search.rs:111-114.  `trace`, if given, collects the token tensor of every
+    step."""
+    dev = mel.device
+    p = DecodePrompt.new(prompt, ids)
+    prompt_ref = [p]
+    filters = build_filters(opt, ids, prompt_ref)
+    ex = GreedyTokenExtractor(ids.eot) if opt.greedy else BeamSearchTokenExtractor(opt.beam_size, ids.eot, opt.patience)
+    n_group = ex.group_size()
+    sample_len = opt.sample_len if opt.sample_len is not None else model.dims.n_text_ctxs // 2      # :129-131
+    with torch.no_grad():
+        n_audio = mel.shape[0]
+        feats = model.encoder(mel).repeat_interleave(n_group, 0)                                     # :293,307-311
+        tokens = p.initial_tokens.repeat(n_audio, 1).repeat_interleave(n_group, 0)
+        model.clear_cache()
+        ex.reset()
+        # ---- main_loop :220-282
+        sums = torch.zeros(tokens.shape[0])
+        no_speech = torch.full((tokens.shape[0],), float("nan"))
+        n_steps = 0
+        for i in range(sample_len):
+            t_in = tokens[:, -1:] if tokens.shape[-1] > p.sample_begin else tokens
+            logits = model.decoder.forward_ext(t_in.to(dev), feats, i).float().cpu()
+            if i == 0:
+                no_speech = no_speech_probs(logits[:, p.sot_idx], ids.no_speech)
+            last = logits[:, -1].clone()
+            for f in filters:
+                f.apply(last, tokens)
+            tokens, completed = ex.update(tokens, last, sums)
+            if not opt.greedy and hasattr(model, "update_cache"):
+                model.update_cache(ex.last_sources.to(dev))
+            n_steps += 1
+            if trace is not None:
+                trace.append(tokens.clone())
+            if completed or tokens.shape[-1] > model.dims.n_text_ctxs:
+                break
+        model.clear_cache()
+    # ---- run_inner :335-418
+    L = tokens.shape[1]
+    cands, scores = ex.finalize(tokens.reshape(n_audio, n_group, L), sums.reshape(n_audio, n_group))
+    cands = [[[int(t) for t in seq] for seq in group] for group in cands]
+    sliced = slice_candidates(cands, p.sample_begin, ids.eot)
+    scores = torch.as_tensor(np.asarray(scores), dtype=torch.float64)
+    sel = MaximumLikelihoodRanker(opt.len_penalty).rank(sliced, scores)
+    chosen = [group[s] for group, s in zip(sliced, sel)]
+    lps = [float(scores[a][s]) for a, s in enumerate(sel)]
+    avg = avg_logprobs(lps, [len(t) for t in chosen])
+    return [DecodeOutput(chosen[a], avg[a], float(no_speech[a * n_group]), lps[a], n_steps) for a in range(n_audio)]
