@@ -124,15 +124,19 @@ __device__ __forceinline__ void reduce_unit(float (&x)[kNV][4], const Geom& g, u
 #pragma unroll
     for (int j = 0; j < kNV; ++j) tmax = fmaxf(tmax, fmaxf(fmaxf(x[j][0], x[j][1]), fmaxf(x[j][2], x[j][3])));
     run.lm = fmaxf(run.lm, tmax);
-    if (!run.ref_set || __any_sync(0xffffffffu, tmax > run.ref + 64.0f)) {
+    // the reference lives in the log2 domain and is an INTEGER R = rint(max * log2 e): x * log2 e - R is then one fused
+    // operation with one rounding of a small number (a rounded -ref * log2 e would shift every term of the run by the
+    // same ~1e-5 relative at |logit| ~ 100), and moving the reference scales the sum by an exact power of two
+    if (!run.ref_set || __any_sync(0xffffffffu, fmaf(tmax, kLog2e, -run.ref) > 92.0f)) {
         const float wm = warp_max(tmax);
         if (wm > -CUDART_INF_F) {
-            if (run.ref_set) run.ls *= ex2((run.ref - wm) * kLog2e);
-            run.ref = wm; run.ref_set = true;
+            const float R = rintf(wm * kLog2e);
+            if (run.ref_set) run.ls *= ex2(run.ref - R);
+            run.ref = R; run.ref_set = true;
         }
     }
     {
-        const float nref = -run.ref * kLog2e;
+        const float nref = -run.ref;
         float s0 = 0.0f, s1 = 0.0f;
 #pragma unroll
         for (int j = 0; j < kNV; ++j) {
@@ -186,7 +190,8 @@ __device__ __forceinline__ void run_finish(Run& run, WarpBuf& wb, int K) {
     float s = run.ls;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
-    run.s = (s != s) ? s : s * exp_diff(run.ref_set ? run.ref : -CUDART_INF_F, run.m);   // the reference is a seen maximum: ref <= m
+    // sum exp(x - m) = 2^(R - m log2 e) * sum 2^(x log2 e - R); R is within half a unit of a seen maximum's image: no overflow
+    run.s = (s != s || !run.ref_set) ? s : s * ex2(fmaf(-run.m, kLog2e, run.ref));
 }
 
 // ---- N units are dealt to Wt warps in contiguous runs: the first r = N % Wt warps take q + 1 = N / Wt + 1 units, the

@@ -142,8 +142,8 @@ __device__ __forceinline__ void warp_pick(float& bv, int& bi) {
 }
 
 // The running statistics of the (row, partition) run a warp is reducing.
-//   softmax: every lane sums exp(x - ref) for its own elements against a reference fixed by the run's first unit
-//            (re-based only if a later unit tops it by more than 64), so a unit costs no cross-lane traffic;
+//   softmax: every lane sums 2^(x log2 e - ref) for its own elements against an integer reference fixed by the run's first
+//            unit (re-based only if a later unit tops it by more than 2^92), so a unit costs no cross-lane traffic;
 //   top-K:   lane r < n holds the run's r-th best candidate (rv, ri) in (value desc, id asc) order, other lanes hold
 //            (-inf, INT32_MAX); wb[0, np) holds gathered candidates not merged yet; tau is a value the run's K-th best
 //            is known to reach (-inf while unknown).
