@@ -384,13 +384,15 @@ __device__ __forceinline__ RowOut merge_row(const StepParams& p, int row, unsign
 
 // `completed` of a step: every group adds 1 (+ 1 << 16 when it is "done") to one word; the last group to arrive
 // publishes whether all were done and re-arms the word for the next launch.
-__device__ __forceinline__ void publish_completed(const StepParams& p, int done) {
-    const int prev = atomicAdd(p.sync, 1 + (done << 16));
+// (two halves so that a caller can put its output stores between the atomic and the use of its result)
+__device__ __forceinline__ int publish_arrive(const StepParams& p, int done) { return atomicAdd(p.sync, 1 + (done << 16)); }
+__device__ __forceinline__ void publish_finish(const StepParams& p, int prev, int done) {
     if ((prev & 0xffff) == p.n_groups - 1) {
         *p.completed = ((prev >> 16) + done == p.n_groups) ? 1 : 0;
         atomicExch(p.sync, 0);
     }
 }
+__device__ __forceinline__ void publish_completed(const StepParams& p, int done) { publish_finish(p, publish_arrive(p, done), done); }
 
 // per-warp tables of the beam tail (alias the WarpBuf: the warp's run has been flushed when a tail starts)
 struct TailScratch {
@@ -610,8 +612,10 @@ __device__ __forceinline__ void beam_tail_fast(const StepParams& p, int audio, F
     long long kb = __double_as_longlong(score);
     kb = kb < 0 ? ~kb : (kb | (long long)0x8000000000000000ull);            // order-preserving: unsigned compare
     const unsigned long long key = (unsigned long long)kb;
+    // (all 32 lanes, unrolled: the shuffles are independent and overlap; lanes >= n_c count as shadowed and sort last)
     int rank = 0;
-    for (int d = 0; d < n_c; ++d) {
+#pragma unroll
+    for (int d = 0; d < 32; ++d) {
         const unsigned long long kd = __shfl_sync(0xffffffffu, key, d);
         const int shd = __shfl_sync(0xffffffffu, sh, d);
         const bool before = shd != sh ? shd < sh : (kd != key ? kd > key : d < lane);
@@ -645,8 +649,10 @@ __device__ __forceinline__ void beam_tail_fast(const StepParams& p, int audio, F
         p.fin_n[audio] = have + n_store;
         if (p.dbg_fin_count) p.dbg_fin_count[audio] = nf;
         if (nan_seen) atomicAdd(&p.status->nan_rows, 1);
-        publish_completed(p, (have + n_store >= p.max_cand) ? 1 : 0);   // (:141-146)
     }
+    const int done = (have + n_store >= p.max_cand) ? 1 : 0;           // (:141-146)
+    int arrived = 0;
+    if (lane == 0) arrived = publish_arrive(p, done);                   // its round trip overlaps the output stores
     if (lane < k) {
         if (p.dbg_fin_source) p.dbg_fin_source[audio * k + lane] = lane < nf ? row0 + fs.fin_src[lane] : -1;
         if (p.dbg_fin_score) p.dbg_fin_score[audio * k + lane] = lane < nf ? fs.fin_sc[lane] : 0.0;
@@ -673,6 +679,7 @@ __device__ __forceinline__ void beam_tail_fast(const StepParams& p, int audio, F
             p.fin_score[audio * p.max_cand + slot] = fs.fin_sc[r];
         }
     }
+    if (lane == 0) publish_finish(p, arrived, done);
     __syncwarp();
 }
 
