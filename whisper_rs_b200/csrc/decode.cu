@@ -51,12 +51,17 @@ namespace wrs {
 enum { MODE_BEAM = 0, MODE_GREEDY = 1, MODE_FILTER = 2 };
 constexpr int kMaxBeam = 15;
 constexpr int kMaxCandAudio = kMaxBeam * kMaxK;          // 240
-constexpr int kStages = 3;                               // units a warp keeps in flight (bulk copies, one mbarrier each)
+#ifndef WRS_STAGES
+#define WRS_STAGES 3
+#endif
+constexpr int kStages = WRS_STAGES;                               // units a warp keeps in flight (bulk copies, one mbarrier each)
 constexpr int kStageBytes = kUnit * 4;                    // landing zone of one unit
 constexpr int kScratchBytes = 2688;                      // per-warp scratch behind stage 0 (WarpBuf, or the fast beam tail's tables)
 constexpr int kTailBytes = kStageBytes + kScratchBytes;  // the general beam tail (beam > 5) overlays stage 0 + scratch
-constexpr int kWarpSmem = kStages * kStageBytes + kScratchBytes + 32;   // + the stages' mbarriers
-constexpr int kTailHead = kMaxBeam * 144;                // tail launch: the group's row results in front of the warp slices
+constexpr int kScanScratch = 1056;                       // scan launch: per-warp scratch behind stage 0 (WarpBuf only)
+constexpr int kWarpSmem = kStages * kStageBytes + kScanScratch + 32;   // + the stages' mbarriers
+constexpr int kTailRows = kMaxBeam * 144;                // tail launch: the group's row results ...
+constexpr int kTailHead = kTailRows + 3200;              // ... and the fast beam tail's tables, in front of the warp slices
 
 // what the row merge leaves for the audio-level tail
 struct __align__(16) RowResult {                        // 144 bytes (kTailHead)
@@ -67,13 +72,13 @@ struct __align__(16) RowResult {                        // 144 bytes (kTailHead)
     int pad[2];
 };
 
-static_assert(sizeof(RowResult) * kMaxBeam <= kTailHead, "row results do not fit the head of the tail launch's shared memory");
+static_assert(sizeof(RowResult) * kMaxBeam <= kTailRows, "row results do not fit the head of the tail launch's shared memory");
 
 struct StepParams {
     float* logits; int64_t row_stride;                   // read-only except MODE_FILTER
     const int64_t* tokens; int64_t tok_stride;
     int cur_len, sample_begin, n_rows, K, beam, n_groups;
-    int scan_warps;                                      // warps of the scan launch (the unit dealing both launches agree on)
+    int deal_q, runs_base, runs_rem; unsigned long long deal_magic;  // unit dealing of the scan launch (run_of), set by launch_step
     RuleCfg rc;
     int ts_split, n_text_units, n_ts_units, upr, bm_words;
     const uint32_t* bm;
@@ -194,38 +199,25 @@ __device__ __forceinline__ void run_finish(Run& run, WarpBuf& wb, int K) {
     run.s = (s != s || !run.ref_set) ? s : s * ex2(fmaf(-run.m, kLog2e, run.ref));
 }
 
-// ---- N units are dealt to Wt warps in contiguous runs: the first r = N % Wt warps take q + 1 = N / Wt + 1 units, the
-//      others q (all 32-bit: n_rows < 32768 and a row has a few dozen units)
-struct Deal { int Wt, q, r; float inv_q, inv_q1; };
-__device__ __forceinline__ Deal deal_of(int N, int grid_warps) {
-    Deal d;
-    d.Wt = min(grid_warps, N); d.q = N / d.Wt; d.r = N - d.q * d.Wt;
-    d.inv_q = 1.0f / (float)d.q; d.inv_q1 = 1.0f / (float)(d.q + 1);
-    return d;
-}
-__device__ __forceinline__ int deal_begin(const Deal& d, int g) { return g * d.q + min(g, d.r); }
-// owner of unit u: a float estimate (u < 2^21 is exact in fp32, the quotient is off by at most one) put right against
-// the owner's range -- an integer division by a run-time divisor costs several times as much
-__device__ __forceinline__ int unit_owner(const Deal& d, int u) {
-    const int big = d.r * (d.q + 1);
-    int g = u < big ? (int)((float)u * d.inv_q1) : d.r + (int)((float)(u - big) * d.inv_q);
-    g = max(0, min(g, d.Wt - 1));
-    if (deal_begin(d, g) > u) --g;
-    else if (deal_begin(d, g + 1) <= u) ++g;
-    return g;
+// ---- The N = n_rows x upr units of a step are cut into RUNS of deal_q consecutive units (the last one may be short);
+//      run g = units [g q, min(N, g q + q)) is folded by one warp of the scan launch and leaves one partial per (row,
+//      partition) it touches.  q = ceil(N / warps of the grid) and a reciprocal for u / q come from the host, so
+//      neither launch divides; the runs are spread evenly over the CTAs (runs_base, runs_rem).
+__device__ __forceinline__ int run_of(const StepParams& p, int u) {   // u / deal_q (launch_step checks the exactness bound)
+    return (int)(((unsigned long long)(unsigned)u * p.deal_magic) >> 40);
 }
 
-struct RowPartials { int first_owner[2], count[2], base[2]; };
+struct RowPartials { int first_run[2], count[2], base[2]; };
 
-__device__ __forceinline__ RowPartials row_partials(const StepParams& p, int row, const Deal& d) {
+__device__ __forceinline__ RowPartials row_partials(const StepParams& p, int row) {
     RowPartials rp;
     const int u0 = row * p.upr;
     rp.base[0] = 0; rp.base[1] = p.n_text_units;
     const int ua[2] = {u0, u0 + p.n_text_units}, ub[2] = {u0 + p.n_text_units, u0 + p.upr};
 #pragma unroll
     for (int q = 0; q < 2; ++q) {
-        if (ub[q] > ua[q]) { rp.first_owner[q] = unit_owner(d, ua[q]); rp.count[q] = unit_owner(d, ub[q] - 1) - rp.first_owner[q] + 1; }
-        else { rp.first_owner[q] = 0; rp.count[q] = 0; }
+        if (ub[q] > ua[q]) { rp.first_run[q] = run_of(p, ua[q]); rp.count[q] = run_of(p, ub[q] - 1) - rp.first_run[q] + 1; }
+        else { rp.first_run[q] = 0; rp.count[q] = 0; }
     }
     return rp;
 }
@@ -235,18 +227,18 @@ __device__ __forceinline__ RowPartials row_partials(const StepParams& p, int row
 // with independent 16-byte loads up front, so the usual row (<= 32 partials) costs ONE round trip to L2.
 struct RowOut { float lp; int tok; unsigned flags; };
 
-__device__ __forceinline__ RowOut merge_row(const StepParams& p, int row, unsigned rule_flags, const RowPartials& rpz, const Deal& deal,
-                                         WarpBuf& wb) {
+__device__ __forceinline__ RowOut merge_row(const StepParams& p, int row, unsigned rule_flags, const RowPartials& rpz, WarpBuf& wb,
+                                         unsigned char* lists) {
     const int lane = threadIdx.x & 31;
     const int K = p.K, KQ = (K + 3) >> 2;
     const Partial* __restrict__ parts = p.partials + (int64_t)row * p.upr;
     const int cT = rpz.count[0], cnt = rpz.count[0] + rpz.count[1];
-    // partial i of the list [text partials | timestamp partials] sits in the slot of its run's first unit: the first
-    // unit of the owning warp's range, or the partition's first unit if the range starts before it
+    // partial i of the list [text partials | timestamp partials] sits in the slot of its run's first unit of the
+    // partition: the run's first unit, or the partition's first unit if the run starts before it
     auto part_of = [&](int i) {
         const int q = i < cT ? 0 : 1;
-        const int g = rpz.first_owner[q] + (q ? i - cT : i);
-        return parts + max(deal_begin(deal, g) - row * p.upr, rpz.base[q]);
+        const int g = rpz.first_run[q] + (q ? i - cT : i);
+        return parts + max(g * p.deal_q - row * p.upr, rpz.base[q]);
     };
     auto load_entries = [&](const Partial* pp, float (&ev)[kMaxK], int (&ei)[kMaxK]) {
 #pragma unroll
@@ -309,10 +301,15 @@ __device__ __forceinline__ RowOut merge_row(const StepParams& p, int row, unsign
     if (cnt <= 32) {
         // the usual row: one partial per lane.  K rounds of "best head wins, its lane moves on to its next entry"
         // (value desc, id asc; ids are unique across partials) -- a k-way merge of sorted lists, two warp reductions
-        // per output
+        // per output.  The lists wait in shared memory ([entry][lane]): a lane that wins reads its next head from there
+        float* lv = reinterpret_cast<float*>(lists);
+        int* li = reinterpret_cast<int*>(lists) + 32 * kMaxK;
         int pn = (int)__float_as_int(h0.z);
         const bool alive = lane < cnt && (lane >= cT || !ts_over_text);
         pn = alive ? min(pn, K) : 0;
+#pragma unroll
+        for (int e = 1; e < kMaxK; ++e)
+            if (e < K) { lv[32 * e + lane] = ev0[e]; li[32 * e + lane] = ei0[e]; }
         int taken = 0;
         float hv = pn > 0 ? ev0[0] : -CUDART_INF_F;
         int hi = pn > 0 ? ei0[0] : INT32_MAX;
@@ -324,11 +321,9 @@ __device__ __forceinline__ RowOut merge_row(const StepParams& p, int row, unsign
             if (lane == rnd) { ov = m; oi = w; }
             if (hv == m && hi == w) {
                 ++taken;
-#pragma unroll
-                for (int e = 0; e + 1 < kMaxK; ++e) { ev0[e] = ev0[e + 1]; ei0[e] = ei0[e + 1]; }
-                ev0[kMaxK - 1] = -CUDART_INF_F;
-                hv = taken < pn ? ev0[0] : -CUDART_INF_F;
-                hi = taken < pn ? ei0[0] : INT32_MAX;
+                const bool more = taken < pn;
+                hv = more ? lv[32 * taken + lane] : -CUDART_INF_F;
+                hi = more ? li[32 * taken + lane] : INT32_MAX;
             }
         }
         r.tok = oi;
@@ -404,7 +399,7 @@ struct TailScratch {
     int sel_src[kMaxBeam], sel_tok[kMaxBeam], fin_src[kMaxBeam];
 };
 static_assert(sizeof(TailScratch) <= kTailBytes, "tail scratch does not fit the per-warp slice");
-static_assert(sizeof(WarpBuf) <= kScratchBytes, "candidate buffer does not fit the per-warp slice");
+static_assert(sizeof(WarpBuf) <= kScanScratch, "candidate buffer does not fit the per-warp slice");
 
 // ---- MODE_BEAM tail: BeamSearchTokenExtractor::update for one audio (beam_search.rs:49-146), ONE warp ----
 __device__ __noinline__ void beam_tail_general(const StepParams& p, int audio, TailScratch& ts) {
@@ -550,81 +545,80 @@ __device__ __forceinline__ void filter_tail(const StepParams& p, int row, const 
     if (lane == 0 && p.no_timestamps >= 0 && p.no_timestamps < V) rp[p.no_timestamps] = -CUDART_INF_F;
 }
 
-// ---- MODE_BEAM tail, k * (k + 1) <= 32 (beam <= 5): one candidate per lane, everything in registers; every global
-// read the tail needs is issued up front, so it costs one round trip to L2 before the outputs are written.
-struct FastTail {
+// ---- MODE_BEAM tail, k * (k + 1) <= 32 (beam <= 5): one candidate per lane, spread over the CTA's k warps.
+//   phase 1 (every warp, before the first barrier): row merge; the row's results and token prefix go to shared memory
+//   phase 2 (every warp): the candidate's score key; warp w counts how many of row w's candidates precede it
+//   phase 3 (warp 0): ranks, the walk of beam_search.rs:87-104, the selection tables, sums / sources / finished count
+//   phase 4 (warp r): token row r of the next step and finished sequence r are copied out
+constexpr int kFastBeam = 5;                        // k (k + 1) <= 32
+struct FastTail {                                   // CTA-level tables (behind the row results in the tail's shared memory)
     long long tok_stage[256];                       // the audio's k token prefixes when k * cur_len <= 256
     double sel_score[kMaxK], fin_sc[kMaxK];
     int sel_src[kMaxK], sel_tok[kMaxK], fin_src[kMaxK];
+    int rank_part[kFastBeam][32];
+    int have, n_store, nf, arrived;
 };
-static_assert(sizeof(FastTail) <= kScratchBytes, "fast tail scratch does not fit the per-warp slice");
 
-// what the fast tail needs from global memory that does not depend on the row merges: fetched by warp 0 before its own merge
-struct FastPre { float sum; int have; long long tv[8]; };
-__device__ __forceinline__ FastPre beam_tail_fast_prefetch(const StepParams& p, int audio) {
-    const int k = p.beam, K = p.K, n_c = k * K, L = p.cur_len;
-    const int lane = threadIdx.x & 31;
-    const int row0 = audio * k;
-    const int j = lane < n_c ? lane / K : 0;
-    FastPre pre;
-    pre.sum = p.sum_in[row0 + j];
-    pre.have = lane == 0 ? p.fin_n[audio] : 0;
-    if (k * L <= 256) {
-#pragma unroll
-        for (int q = 0; q < 8; ++q) {
-            const int idx = lane + 32 * q;
-            const int jj = idx / L, t = idx - jj * L;
-            pre.tv[q] = idx < k * L ? p.tokens[(int64_t)(row0 + jj) * p.tok_stride + t] : 0;
-        }
-    }
-    return pre;
-}
+static_assert(sizeof(FastTail) <= kTailHead - kTailRows, "fast tail tables do not fit the head of the tail launch's shared memory");
 
-// rr_s: the audio's k row results in shared memory (written by the merging warps of this CTA)
-__device__ __forceinline__ void beam_tail_fast(const StepParams& p, int audio, FastTail& fs, const FastPre& pre, const RowResult* rr_s) {
-    const int k = p.beam, K = p.K, n_c = k * K, L = p.cur_len;
+// phase 2: lane c < k K is candidate (beam j = c / K, entry i = c % K).  Returns the lane's candidate and leaves this
+// warp's share of the ranks in fs.rank_part[warp]
+struct FastCand { double score; int tok, j; bool ok; unsigned fl; };
+__device__ __forceinline__ FastCand beam_fast_rank_part(const StepParams& p, FastTail& fs, const RowResult* rr_s, float sum, int warp) {
+    const int k = p.beam, K = p.K, n_c = k * K;
     const int lane = threadIdx.x & 31;
-    const int row0 = audio * k;
     const bool valid = lane < n_c;
-    const int j = valid ? lane / K : 0, i = valid ? lane - j * K : 0;
-    const RowResult* rr = rr_s + j;
+    FastCand c;
+    c.j = valid ? lane / K : 0;
+    const int i = valid ? lane - c.j * K : 0;
+    const RowResult* rr = rr_s + c.j;
     const float lp = rr->lp[i];
-    int tok = rr->tok[i];
-    const unsigned fl = rr->flags, same = rr->same;
-    const float sum = pre.sum;
-    int have = pre.have;
-    const bool staged = k * L <= 256;
-    const long long (&tv)[8] = pre.tv;
-    // ---- candidates: score = f64(sum_logprobs[row]) + f64(logprob)   (beam_search.rs:70-71)
-    const double score = (double)sum + (double)lp;
-    const bool nan_seen = __any_sync(0xffffffffu, valid && (fl & 128u));
+    c.tok = rr->tok[i];
+    c.fl = rr->flags;
+    const unsigned same = rr->same;
+    // ---- score = f64(sum_logprobs[row]) + f64(logprob)   (beam_search.rs:70-71)
+    c.score = (double)sum + (double)lp;
     // a later beam with the same prefix proposing the same token overwrites this map entry (:74-77)
     bool shadowed = false;
     if (__any_sync(0xffffffffu, valid && same != 0u)) {
         for (int j2 = 1; j2 < k; ++j2)
             for (int i2 = 0; i2 < K; ++i2) {
-                const int t2 = __shfl_sync(0xffffffffu, tok, j2 * K + i2);
-                if (j2 > j && ((same >> j2) & 1u) && t2 == tok) shadowed = true;
+                const int t2 = __shfl_sync(0xffffffffu, c.tok, j2 * K + i2);
+                if (j2 > c.j && ((same >> j2) & 1u) && t2 == c.tok) shadowed = true;
             }
     }
-    const int sh = (!valid || shadowed || tok == INT32_MAX) ? 1 : 0;
+    const int sh = (!valid || shadowed || c.tok == INT32_MAX) ? 1 : 0;
+    c.ok = valid && !sh;
     // ---- rank by (score desc, source row asc, token asc) == (score desc, lane asc); shadowed entries go last
-    long long kb = __double_as_longlong(score);
+    long long kb = __double_as_longlong(c.score);
     kb = kb < 0 ? ~kb : (kb | (long long)0x8000000000000000ull);            // order-preserving: unsigned compare
     const unsigned long long key = (unsigned long long)kb;
-    // (all 32 lanes, unrolled: the shuffles are independent and overlap; lanes >= n_c count as shadowed and sort last)
-    int rank = 0;
+    int part = 0;
 #pragma unroll
-    for (int d = 0; d < 32; ++d) {
+    for (int t = 0; t < kFastBeam + 1; ++t) {
+        const int d = min(warp * K + t, 31);
         const unsigned long long kd = __shfl_sync(0xffffffffu, key, d);
         const int shd = __shfl_sync(0xffffffffu, sh, d);
         const bool before = shd != sh ? shd < sh : (kd != key ? kd > key : d < lane);
-        rank += before ? 1 : 0;
+        part += (t < K && before) ? 1 : 0;
     }
+    fs.rank_part[warp][lane] = part;
+    return c;
+}
+
+// phase 3 (warp 0 only)
+__device__ __forceinline__ void beam_fast_walk(const StepParams& p, int audio, FastTail& fs, const FastCand& c, int have) {
+    const int k = p.beam;
+    const int lane = threadIdx.x & 31;
+    const int row0 = audio * k;
+    int rank = 0;
+#pragma unroll
+    for (int w = 0; w < kFastBeam; ++w)
+        if (w < k) rank += fs.rank_part[w][lane];
+    const bool nan_seen = __any_sync(0xffffffffu, lane < k * p.K && (c.fl & 128u));
     // ---- walk (beam_search.rs:87-104): EOT-terminated -> finished, others kept until k are saved.  An entry is
     //      visited iff fewer than k live entries precede it in sorted order.
-    const bool ok = valid && !sh;
-    const bool live = ok && tok != p.eot, fin = ok && tok == p.eot;
+    const bool live = c.ok && c.tok != p.eot, fin = c.ok && c.tok == p.eot;
     const unsigned below = (1u << rank) - 1u;
     const unsigned live_sorted = __reduce_or_sync(0xffffffffu, live ? (1u << rank) : 0u);
     const int live_before = __popc(live_sorted & below);
@@ -632,55 +626,53 @@ __device__ __forceinline__ void beam_tail_fast(const StepParams& p, int audio, F
     const unsigned fin_sorted = __reduce_or_sync(0xffffffffu, (fin && visited) ? (1u << rank) : 0u);
     const int fidx = __popc(fin_sorted & below);
     const int nf = min(__popc(fin_sorted), kMaxBeam), saved = min(__popc(live_sorted), k);
-    if (live && visited) { fs.sel_src[live_before] = j; fs.sel_tok[live_before] = tok; fs.sel_score[live_before] = score; }
-    if (fin && visited && fidx < kMaxBeam) { fs.fin_src[fidx] = j; fs.fin_sc[fidx] = score; }
-    if (staged) {
-#pragma unroll
-        for (int q = 0; q < 8; ++q)
-            if (lane + 32 * q < k * L) fs.tok_stage[lane + 32 * q] = tv[q];
-    }
+    if (live && visited) { fs.sel_src[live_before] = c.j; fs.sel_tok[live_before] = c.tok; fs.sel_score[live_before] = c.score; }
+    if (fin && visited && fidx < kMaxBeam) { fs.fin_src[fidx] = c.j; fs.fin_sc[fidx] = c.score; }
     // fewer than k live candidates cannot happen with >= k+1 finite logits per row; keep the row count anyway
     if (lane >= saved && lane < k) { fs.sel_src[lane] = 0; fs.sel_tok[lane] = p.eot; fs.sel_score[lane] = -CUDART_INF; }
-    __syncwarp();
     // finished store: append in descending score until round(patience*k) entries (:124-138)
     have = __shfl_sync(0xffffffffu, have, 0);
     const int n_store = min(nf, max(0, p.max_cand - have));
+    const int done = (have + n_store >= p.max_cand) ? 1 : 0;           // (:141-146)
     if (lane == 0) {
+        fs.have = have; fs.n_store = n_store; fs.nf = nf;
         p.fin_n[audio] = have + n_store;
         if (p.dbg_fin_count) p.dbg_fin_count[audio] = nf;
         if (nan_seen) atomicAdd(&p.status->nan_rows, 1);
+        fs.arrived = publish_arrive(p, done);                           // its round trip overlaps the output stores
     }
-    const int done = (have + n_store >= p.max_cand) ? 1 : 0;           // (:141-146)
-    int arrived = 0;
-    if (lane == 0) arrived = publish_arrive(p, done);                   // its round trip overlaps the output stores
+    __syncwarp();
     if (lane < k) {
         if (p.dbg_fin_source) p.dbg_fin_source[audio * k + lane] = lane < nf ? row0 + fs.fin_src[lane] : -1;
         if (p.dbg_fin_score) p.dbg_fin_score[audio * k + lane] = lane < nf ? fs.fin_sc[lane] : 0.0;
         p.source_idx[row0 + lane] = row0 + fs.sel_src[lane];
         p.sum_out[row0 + lane] = (float)fs.sel_score[lane];   // index_put_(.., score as f32) :91-95
     }
-    // ---- outputs
-    const int L1 = L + 1;
-    for (int idx = lane; idx < k * L1; idx += 32) {
-        const int r = idx / L1, t = idx - r * L1;
+}
+
+// phase 4 (warp r): next_tokens row r = source prefix + chosen token; finished sequence r = source prefix + EOT
+__device__ __forceinline__ void beam_fast_outputs(const StepParams& p, int audio, const FastTail& fs, int r) {
+    const int k = p.beam, L = p.cur_len, L1 = L + 1;
+    const int lane = threadIdx.x & 31;
+    const int row0 = audio * k;
+    const bool staged = k * L <= 256;
+    {
         const int src = fs.sel_src[r];
-        long long v = (long long)fs.sel_tok[r];
-        if (t < L) v = staged ? fs.tok_stage[src * L + t] : p.tokens[(int64_t)(row0 + src) * p.tok_stride + t];
-        p.next_tokens[(int64_t)(row0 + r) * p.next_stride + t] = v;
+        const long long tokv = (long long)fs.sel_tok[r];
+        const int64_t* from = p.tokens + (int64_t)(row0 + src) * p.tok_stride;
+        int64_t* to = p.next_tokens + (int64_t)(row0 + r) * p.next_stride;
+        for (int t = lane; t < L1; t += 32) to[t] = t < L ? (staged ? fs.tok_stage[src * L + t] : from[t]) : tokv;
     }
-    for (int idx = lane; idx < n_store * L1; idx += 32) {
-        const int r = idx / L1, t = idx - r * L1;
-        const int slot = have + r, src = fs.fin_src[r];
-        long long v = (long long)p.eot;
-        if (t < L) v = staged ? fs.tok_stage[src * L + t] : p.tokens[(int64_t)(row0 + src) * p.tok_stride + t];
-        p.fin_tokens[((int64_t)audio * p.max_cand + slot) * p.max_len + t] = v;
-        if (t == 0) {
+    if (r < fs.n_store) {
+        const int slot = fs.have + r, src = fs.fin_src[r];
+        const int64_t* from = p.tokens + (int64_t)(row0 + src) * p.tok_stride;
+        int64_t* to = p.fin_tokens + ((int64_t)audio * p.max_cand + slot) * p.max_len;
+        for (int t = lane; t < L1; t += 32) to[t] = t < L ? (staged ? fs.tok_stage[src * L + t] : from[t]) : (long long)p.eot;
+        if (lane == 0) {
             p.fin_len[audio * p.max_cand + slot] = L1;
             p.fin_score[audio * p.max_cand + slot] = fs.fin_sc[r];
         }
     }
-    if (lane == 0) publish_finish(p, arrived, done);
-    __syncwarp();
 }
 
 #ifdef WRS_TRACE
@@ -703,16 +695,15 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const Step
     unsigned char* slice = smem_raw + warp * kWarpSmem;
     unsigned char* scratch = slice + kStageBytes;
     WarpBuf& wb = *reinterpret_cast<WarpBuf*>(scratch);
-    unsigned long long* bars = reinterpret_cast<unsigned long long*>(slice + kStages * kStageBytes + kScratchBytes);
-    auto stage_of = [&](int s) { return reinterpret_cast<float4*>(s == 0 ? slice : slice + kScratchBytes + s * kStageBytes); };
+    unsigned long long* bars = reinterpret_cast<unsigned long long*>(slice + kStages * kStageBytes + kScanScratch);
+    auto stage_of = [&](int s) { return reinterpret_cast<float4*>(s == 0 ? slice : slice + kScanScratch + s * kStageBytes); };
 
-    // N units are dealt to the first Wt = min(warps of the grid, N) warps: every active warp owns >= 1 unit, so the
-    // owners of consecutive units are consecutive warps (row_partials relies on that)
+    // this warp's run of units (run_of): CTA b folds runs [b runs_base + min(b, runs_rem), ...), one per warp
     const int N = p.n_rows * p.upr;
-    const Deal deal = deal_of(N, (int)gridDim.x * kStepWarps);
-    const int gw = (int)blockIdx.x * kStepWarps + warp;
-    if (gw >= deal.Wt) return;
-    const int u_begin = deal_begin(deal, gw), u_end = deal_begin(deal, gw + 1);
+    const int b = (int)blockIdx.x;
+    if (warp >= p.runs_base + (b < p.runs_rem ? 1 : 0)) return;
+    const int gw = b * p.runs_base + min(b, p.runs_rem) + warp;
+    const int u_begin = gw * p.deal_q, u_end = min(N, u_begin + p.deal_q);
     const int n_units = u_end - u_begin;
 #ifdef WRS_TRACE
     if (lane == 0) for (int q = 0; q < 8; ++q) g_trace[gw * 8 + q] = 0;
@@ -894,90 +885,101 @@ template <int MODE>
 __global__ void __launch_bounds__(kMaxBeam * 32) decode_tail_kernel(const StepParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    RowResult* rr_s = reinterpret_cast<RowResult*>(smem_raw);          // the group's row results, handed to warp 0
-    unsigned char* slice = smem_raw + kTailHead + warp * kTailBytes;   // [general tail tables | ...][scratch]
+    RowResult* rr_s = reinterpret_cast<RowResult*>(smem_raw);          // the group's row results
+    FastTail& fs = *reinterpret_cast<FastTail*>(smem_raw + kTailRows);
+    unsigned char* slice = smem_raw + kTailHead + warp * kTailBytes;   // [merge lists / general tail tables | ...][scratch]
     unsigned char* scratch = slice + kStageBytes;
     WarpBuf& wb = *reinterpret_cast<WarpBuf*>(scratch);
     const int row = (int)blockIdx.x * (MODE == MODE_BEAM ? p.beam : 1) + warp;
-    const Deal deal = deal_of(p.n_rows * p.upr, p.scan_warps);
+    const bool fast_tail = MODE == MODE_BEAM && p.beam * p.K <= 32;
 #ifdef WRS_TRACE
     const int gw = row;
     if (lane == 0) for (int q = 4; q < 8; ++q) g_trace[gw * 8 + q] = 0;
     const unsigned long long tm0 = gtime();
 #endif
-    {
-        // everything this row needs from memory is requested before the first use: its two newest tokens (rules), the
-        // token prefixes (beam dedup) and, inside merge_row, the partials
-        const RowPartials rpz = row_partials(p, row, deal);
-        const int64_t* rt = p.tokens + (int64_t)row * p.tok_stride;
-        const int64_t tk_last = rt[p.cur_len - 1], tk_pen = p.cur_len >= 2 ? rt[p.cur_len - 2] : 0;
-        // which later beams of this audio hold an identical prefix (HashMap key = whole sequence, beam_search.rs:74-77):
-        // the first 32 positions of up to 4 later beams are fetched before the merge so both latencies overlap
-        const int bj = MODE == MODE_BEAM ? warp : 0, rbase = row - bj;
-        const int64_t* mine = p.tokens + (int64_t)row * p.tok_stride;
-        int64_t pre_m = 0, pre_o[4] = {0, 0, 0, 0};
-        if (MODE == MODE_BEAM && lane < p.cur_len) {
+    // everything this row needs from memory is requested before the first use: its two newest tokens (rules), the
+    // token prefixes (beam dedup), the running sums and, inside merge_row, the partials
+    const RowPartials rpz = row_partials(p, row);
+    const int64_t* mine = p.tokens + (int64_t)row * p.tok_stride;
+    const int64_t tk_last = mine[p.cur_len - 1], tk_pen = p.cur_len >= 2 ? mine[p.cur_len - 2] : 0;
+    // which later beams of this audio hold an identical prefix (HashMap key = whole sequence, beam_search.rs:74-77):
+    // the first 32 positions of up to 4 later beams are fetched before the merge so both latencies overlap
+    const int bj = MODE == MODE_BEAM ? warp : 0, rbase = row - bj;
+    int64_t pre_m = 0, pre_m1 = 0, pre_o[4] = {0, 0, 0, 0};
+    float cand_sum = 0.0f;
+    int have = 0;
+    const bool staged = fast_tail && p.beam * p.cur_len <= 256;
+    if (MODE == MODE_BEAM) {
+        if (lane < p.cur_len) {
             pre_m = mine[lane];
 #pragma unroll
             for (int q = 0; q < 4; ++q)
                 if (bj + 1 + q < p.beam) pre_o[q] = p.tokens[(int64_t)(rbase + bj + 1 + q) * p.tok_stride + lane];
         }
-        if (lane == 0) wb.n = 0;
-        __syncwarp();
-        FastPre pre;
-        const bool fast_tail = MODE == MODE_BEAM && p.beam * p.K <= 32;
-        if (fast_tail && warp == 0) pre = beam_tail_fast_prefetch(p, (int)blockIdx.x);
-        RowOut r = merge_row(p, row, 0u, rpz, deal, wb);
-        const RowRules rr_row = row_rules_from(p.rc, tk_last, tk_pen, p.cur_len, p.sample_begin);
-        r.flags |= rr_row.flags;
-        unsigned same = 0u;
-        if (MODE == MODE_BEAM) {
-            unsigned diff = 0u;
-#pragma unroll
-            for (int q = 0; q < 4; ++q)
-                if (pre_o[q] != pre_m) diff |= 1u << (bj + 1 + q);          // lanes >= cur_len hold 0 == 0
-            for (int j2 = bj + 5; j2 < p.beam; ++j2)
-                if (lane < p.cur_len && p.tokens[(int64_t)(rbase + j2) * p.tok_stride + lane] != pre_m) diff |= 1u << j2;
-            for (int t = lane + 32; t < p.cur_len; t += 32) {
-                const int64_t mt = mine[t];
-                for (int j2 = bj + 1; j2 < p.beam; ++j2)
-                    if (p.tokens[(int64_t)(rbase + j2) * p.tok_stride + t] != mt) diff |= 1u << j2;
-            }
-            diff = __reduce_or_sync(0xffffffffu, diff);
-            same = ~diff & ((1u << p.beam) - 1u) & ~((2u << bj) - 1u);
-        }
-#ifdef WRS_TRACE
-        WRS_TR_ADD(4, gtime() - tm0); WRS_TR_ADD(5, 1);
-#endif
-        if (lane < p.K) {
-            if (p.dbg_lp) p.dbg_lp[(int64_t)row * p.K + lane] = r.lp;
-            if (p.dbg_tok) p.dbg_tok[(int64_t)row * p.K + lane] = r.tok;
-        }
-        if (lane == 0 && p.dbg_flags) p.dbg_flags[row] = (uint8_t)r.flags;
-        if (MODE == MODE_GREEDY) {
-            greedy_tail(p, row, r);
-        } else if (MODE == MODE_FILTER) {
-            filter_tail(p, row, rr_row, r.flags);
-        } else {
-            RowResult* res = fast_tail ? rr_s + warp : p.rowres + row;
-            if (lane < kMaxK) { res->lp[lane] = r.lp; res->tok[lane] = lane < p.K ? r.tok : INT32_MAX; }
-            if (lane == 0) { res->flags = r.flags; res->same = same; }
-        }
-        if (MODE != MODE_BEAM) return;
-        __threadfence_block();
-        __syncthreads();                                 // the audio's row results are complete (same CTA wrote them)
-        if (warp != 0) return;
+        if (staged && lane + 32 < p.cur_len) pre_m1 = mine[lane + 32];
         if (fast_tail) {
-#ifdef WRS_TRACE
-            const unsigned long long tt0 = gtime();
-#endif
-            beam_tail_fast(p, (int)blockIdx.x, *reinterpret_cast<FastTail*>(scratch), pre, rr_s);
-#ifdef WRS_TRACE
-            WRS_TR_ADD(6, gtime() - tt0); WRS_TR_ADD(7, 1);
-#endif
-            return;
+            if (lane < p.beam * p.K) cand_sum = p.sum_in[rbase + lane / p.K];
+            if (warp == 0 && lane == 0) have = p.fin_n[blockIdx.x];
         }
     }
+    if (lane == 0) wb.n = 0;
+    __syncwarp();
+    RowOut r = merge_row(p, row, 0u, rpz, wb, slice);
+    const RowRules rr_row = row_rules_from(p.rc, tk_last, tk_pen, p.cur_len, p.sample_begin);
+    r.flags |= rr_row.flags;
+    unsigned same = 0u;
+    if (MODE == MODE_BEAM) {
+        unsigned diff = 0u;
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+            if (pre_o[q] != pre_m) diff |= 1u << (bj + 1 + q);          // lanes >= cur_len hold 0 == 0
+        for (int j2 = bj + 5; j2 < p.beam; ++j2)
+            if (lane < p.cur_len && p.tokens[(int64_t)(rbase + j2) * p.tok_stride + lane] != pre_m) diff |= 1u << j2;
+        for (int t = lane + 32; t < p.cur_len; t += 32) {
+            const int64_t mt = mine[t];
+            for (int j2 = bj + 1; j2 < p.beam; ++j2)
+                if (p.tokens[(int64_t)(rbase + j2) * p.tok_stride + t] != mt) diff |= 1u << j2;
+        }
+        diff = __reduce_or_sync(0xffffffffu, diff);
+        same = ~diff & ((1u << p.beam) - 1u) & ~((2u << bj) - 1u);
+    }
+#ifdef WRS_TRACE
+    WRS_TR_ADD(4, gtime() - tm0); WRS_TR_ADD(5, 1);
+#endif
+    if (lane < p.K) {
+        if (p.dbg_lp) p.dbg_lp[(int64_t)row * p.K + lane] = r.lp;
+        if (p.dbg_tok) p.dbg_tok[(int64_t)row * p.K + lane] = r.tok;
+    }
+    if (lane == 0 && p.dbg_flags) p.dbg_flags[row] = (uint8_t)r.flags;
+    if (MODE == MODE_GREEDY) { greedy_tail(p, row, r); return; }
+    if (MODE == MODE_FILTER) { filter_tail(p, row, rr_row, r.flags); return; }
+    {
+        RowResult* res = fast_tail ? rr_s + warp : p.rowres + row;
+        if (lane < kMaxK) { res->lp[lane] = r.lp; res->tok[lane] = lane < p.K ? r.tok : INT32_MAX; }
+        if (lane == 0) { res->flags = r.flags; res->same = same; }
+    }
+    if (staged) {
+        if (lane < p.cur_len) fs.tok_stage[warp * p.cur_len + lane] = pre_m;
+        if (lane + 32 < p.cur_len) fs.tok_stage[warp * p.cur_len + lane + 32] = pre_m1;
+    }
+    __threadfence_block();
+    __syncthreads();                                     // the audio's row results are complete (same CTA wrote them)
+    if (fast_tail) {
+#ifdef WRS_TRACE
+        const unsigned long long tt0 = gtime();
+#endif
+        const FastCand c = beam_fast_rank_part(p, fs, rr_s, cand_sum, warp);
+        __syncthreads();
+        if (warp == 0) beam_fast_walk(p, (int)blockIdx.x, fs, c, have);
+        __syncthreads();
+        beam_fast_outputs(p, (int)blockIdx.x, fs, warp);
+        if (warp == 0 && lane == 0) publish_finish(p, fs.arrived, (fs.have + fs.n_store >= p.max_cand) ? 1 : 0);
+#ifdef WRS_TRACE
+        WRS_TR_ADD(6, gtime() - tt0); WRS_TR_ADD(7, 1);
+#endif
+        return;
+    }
+    if (warp != 0) return;
 #ifdef WRS_TRACE
     const unsigned long long tt0 = gtime();
 #endif
@@ -1063,7 +1065,12 @@ int launch_step(wrs_decoder* dec, StepParams p, cudaStream_t stream) {
     }
     const int64_t units = (int64_t)p.n_rows * p.upr;
     const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctx->sm_count, (units + kStepWarps - 1) / kStepWarps));
-    p.scan_warps = grid * kStepWarps;
+    // runs of q = ceil(units / warps of the grid) units; u / q = (u * ceil(2^40 / q)) >> 40, exact while u (q - 1) < 2^40
+    const int64_t q = (units + (int64_t)grid * kStepWarps - 1) / ((int64_t)grid * kStepWarps), n_runs = (units + q - 1) / q;
+    if (units >= (1ll << 31) || units * (q - 1) >= (1ll << 40))
+        return fail(ctx, WRS_ERR_UNSUPPORTED, "decode step: n_rows x units per row too large for the unit dealing");
+    p.deal_q = (int)q; p.deal_magic = ((1ull << 40) + (uint64_t)q - 1) / (uint64_t)q;
+    p.runs_base = (int)(n_runs / grid); p.runs_rem = (int)(n_runs % grid);
     decode_scan_kernel<<<grid, kStepThreads, smem, stream>>>(p);
     WRS_CUDA(ctx, cudaGetLastError());
     const int rows_per_group = MODE == MODE_BEAM ? p.beam : 1;

@@ -21,7 +21,10 @@
 
 namespace wrs {
 
-constexpr int kStepWarps = 16;                           // one 512-thread CTA per SM, up to 128 registers per thread
+#ifndef WRS_STEP_WARPS
+#define WRS_STEP_WARPS 16
+#endif
+constexpr int kStepWarps = WRS_STEP_WARPS;               // one CTA per SM: 16 warps, up to 128 registers per thread
 constexpr int kStepThreads = kStepWarps * 32;
 constexpr int kNV = 7;                                   // float4 slots per lane per unit
 constexpr int kUnit = 32 * 4 * kNV;                      // 896 elements per unit, 16-byte aligned in memory
