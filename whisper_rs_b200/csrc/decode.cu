@@ -19,6 +19,7 @@
 
 #include "async_copy.cuh"
 #include "decode_scan.cuh"
+#include "logmel_fft.cuh"   // packed FP32 helpers (f32x2)
 #include "wrs_internal.cuh"
 
 namespace wrs { struct RowResult; }
@@ -78,7 +79,9 @@ struct StepParams {
     float* logits; int64_t row_stride;                   // read-only except MODE_FILTER
     const int64_t* tokens; int64_t tok_stride;
     int cur_len, sample_begin, n_rows, K, beam, n_groups;
-    int deal_q, runs_base, runs_rem; unsigned long long deal_magic;  // unit dealing of the scan launch (run_of), set by launch_step
+    // unit dealing of the scan launch (run_in_row), set by launch_step: every row is cut into rt text runs and rs
+    // timestamp runs of consecutive units; a run never crosses a partition
+    int rt, rs, rpr, n_runs, t_base, t_rem, s_base, s_rem; unsigned long long rpr_magic;
     RuleCfg rc;
     int ts_split, n_text_units, n_ts_units, upr, bm_words;
     const uint32_t* bm;
@@ -91,6 +94,19 @@ struct StepParams {
     DevStatus* status;
 };
 
+#ifdef WRS_TRACE
+// investigation aid (tools/debug/dec_trace.py): per-warp event times in ns, [warp][8]
+__device__ unsigned long long g_trace[148 * kStepWarps * 8];
+__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define WRS_TR(slot) do { if (lane == 0) g_trace[gw * 8 + (slot)] = gtime(); } while (0)
+#define WRS_TR_ADD(slot, v) do { if (lane == 0) g_trace[gw * 8 + (slot)] += (v); } while (0)
+#define WRS_TR_CNT(slot, v) do { if ((threadIdx.x & 31) == 0) g_trace[((threadIdx.x >> 5) * gridDim.x + blockIdx.x) * 8 + (slot)] += (v); } while (0)
+#else
+#define WRS_TR_CNT(slot, v) do {} while (0)
+#define WRS_TR(slot) do {} while (0)
+#define WRS_TR_ADD(slot, v) do {} while (0)
+#endif
+
 // geometry of one unit as a warp sees it (all warp-uniform)
 struct Geom {
     int row, part;      // part 0 = text ids, 1 = timestamp ids
@@ -98,36 +114,32 @@ struct Geom {
     int a0;             // id of the unit's first element slot (16-byte aligned in the row's memory; may be < lo)
 };
 
-// Fold one unit (already in registers, masked ranges loaded as -inf) into the run.
-__device__ __forceinline__ void reduce_unit(float (&x)[kNV][4], const Geom& g, uint32_t bmw, int wbase, int K, WarpBuf& wb,
+// SuppressTokens / SuppressBlank (suppress_tokens.rs:22, suppress_blanks.rs:41) on a unit that has landed in its
+// shared-memory stage: lane l holds bitmap word word0 + l (bit set = masked) and writes -inf over the ids it names.
+// Most words are zero, so this costs a test; the registers are loaded after it.
+__device__ __forceinline__ void poke_suppressed(float* st, uint32_t bmw, int word0, int a0) {
+    if (bmw) {
+        const int base = ((word0 + (int)(threadIdx.x & 31)) << 5) - a0;       // slot of the word's bit 0
+        do {
+            const unsigned pos = (unsigned)(base + __ffs((int)bmw) - 1);
+            bmw &= bmw - 1u;
+            if (pos < (unsigned)kUnit) st[pos] = -CUDART_INF_F;
+        } while (bmw);
+    }
+}
+
+// Fold one unit (already in registers, masked ids loaded as -inf) into the run.  `st` is the unit's stage (suppressed ids
+// poked, range masks not applied: `ragged` says whether the unit has any).
+__device__ __forceinline__ void reduce_unit(float (&x)[kNV][4], const Geom& g, const float4* st, bool ragged, int K, WarpBuf& wb,
                                             Run& run) {
     const int lane = threadIdx.x & 31;
-    // ---- 1. suppress bitmap -> -inf (bit set = masked).  Lane l holds bitmap word wbase + l; most 128-id slots
-    //         hold no suppressed id at all and are skipped on a warp-uniform test
-    const uint32_t nz = __ballot_sync(0xffffffffu, bmw != 0u);
-    if (nz) {
+    // ---- 1. slot and lane maxima; exp-sum against the run's reference (no cross-lane traffic unless the reference moves)
+    float sm[kNV];
 #pragma unroll
-        for (int j = 0; j < kNV; ++j) {
-            const int e0 = g.a0 + 128 * j;                                   // first id of the slot (lane 0)
-            const int rel0 = max((e0 >> 5) - wbase, 0);
-            if ((nz >> rel0) & 0x1Fu) {                                      // 128 ids span at most 5 words
-                const int e = e0 + 4 * lane;
-                const int rel = max((e >> 5) - wbase, 0);
-                const uint32_t w0 = __shfl_sync(0xffffffffu, bmw, rel), w1 = __shfl_sync(0xffffffffu, bmw, rel + 1);
-                // e < 0 (row start not 16-byte aligned): ids e..-1 do not exist, ids 0..e+3 take the low bits of word 0
-                const uint32_t bits = (e >= 0 ? __funnelshift_r(w0, w1, e & 31) : (w0 << (-e))) & 0xFu;
-                if (bits) {
+    for (int j = 0; j < kNV; ++j) sm[j] = fmaxf(fmaxf(x[j][0], x[j][1]), fmaxf(x[j][2], x[j][3]));
+    float tmax = sm[0];
 #pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                        if (bits & (1u << i)) x[j][i] = -CUDART_INF_F;
-                }
-            }
-        }
-    }
-    // ---- 2. lane max; exp-sum against the run's reference (no cross-lane traffic unless the reference moves)
-    float tmax = -CUDART_INF_F;
-#pragma unroll
-    for (int j = 0; j < kNV; ++j) tmax = fmaxf(tmax, fmaxf(fmaxf(x[j][0], x[j][1]), fmaxf(x[j][2], x[j][3])));
+    for (int j = 1; j < kNV; ++j) tmax = fmaxf(tmax, sm[j]);
     run.lm = fmaxf(run.lm, tmax);
     // the reference lives in the log2 domain and is an INTEGER R = rint(max * log2 e): x * log2 e - R is then one fused
     // operation with one rounding of a small number (a rounded -ref * log2 e would shift every term of the run by the
@@ -141,48 +153,103 @@ __device__ __forceinline__ void reduce_unit(float (&x)[kNV][4], const Geom& g, u
         }
     }
     {
-        const float nref = -run.ref;
-        float s0 = 0.0f, s1 = 0.0f;
+        // packed FP32 (FFMA2 / FADD2): the four sums of a lane run side by side; NaN inputs keep the sum NaN
+        const f32x2 l2e = pack2(kLog2e, kLog2e), nref = pack2(-run.ref, -run.ref);
+        f32x2 s01 = pack2(0.0f, 0.0f), s23 = s01;
 #pragma unroll
         for (int j = 0; j < kNV; ++j) {
-            s0 += ex2(fmaf(x[j][0], kLog2e, nref)) + ex2(fmaf(x[j][1], kLog2e, nref));   // NaN inputs keep the sum NaN
-            s1 += ex2(fmaf(x[j][2], kLog2e, nref)) + ex2(fmaf(x[j][3], kLog2e, nref));
+            float a0, a1, a2, a3;
+            unpack2(fma_(pack2(x[j][0], x[j][1]), l2e, nref), a0, a1);
+            unpack2(fma_(pack2(x[j][2], x[j][3]), l2e, nref), a2, a3);
+            s01 = add_(s01, pack2(ex2(a0), ex2(a1)));
+            s23 = add_(s23, pack2(ex2(a2), ex2(a3)));
         }
-        run.ls += s0 + s1;
+        float t0, t1;
+        unpack2(add_(s01, s23), t0, t1);
+        run.ls += t0 + t1;
     }
-    // ---- 3. top-K: gather everything that reaches tau, a value the run's K-th best is known to reach
+    // ---- 2. top-K: gather everything that reaches tau, a value the run's K-th best is known to reach
     if (run.tau == -CUDART_INF_F) run.tau = kth_threshold(tmax, K);      // at least K elements of this unit reach it
-    const float tau = run.tau;
-    const bool mine = tmax >= tau && tmax > -CUDART_INF_F;
-    if (!__any_sync(0xffffffffu, mine)) return;
-    const int np0 = run.np;
-    if (mine) {
-#pragma unroll
-        for (int j = 0; j < kNV; ++j) {
-            if (fmaxf(fmaxf(x[j][0], x[j][1]), fmaxf(x[j][2], x[j][3])) >= tau) {
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    if (x[j][i] >= tau && x[j][i] > -CUDART_INF_F) {
-                        const int pos = atomicAdd(&wb.n, 1);
-                        if (pos < kCandCap - kMaxK) { wb.v[pos] = x[j][i]; wb.id[pos] = g.a0 + 4 * (lane + 32 * j) + i; }
-                    }
-            }
-        }
+    bool mine = tmax >= run.tau && tmax > -CUDART_INF_F;
+    unsigned hb = __ballot_sync(0xffffffffu, mine);
+    if (!hb) return;
+    if (run.np > 0 && run.np + __popc(hb) + K > 32) {
+        // the pending candidates would outgrow the one-entry-per-lane merge: merge them now (that also raises the bar)
+        run_merge(run, wb, run.np, K);
+        run.np = 0;
+        run.tau = fmaxf(run.tau, __shfl_sync(0xffffffffu, run.rv, K - 1));
+        mine = tmax >= run.tau && tmax > -CUDART_INF_F;
+        hb = __ballot_sync(0xffffffffu, mine);
+        if (!hb) return;
     }
-    __syncwarp();
-    const int n_tot = wb.n;
-    // once the list is full its K-th value is an exact bar and later units add only a few stragglers: those wait for a
-    // cheap register merge (list + pending <= 32 entries); the first unit of a run merges at once to set that bar
-    if (run.n >= K && n_tot + K <= 32) { run.np = n_tot; return; }
-    if (n_tot <= kCandCap - kMaxK) run_merge(run, wb, n_tot, K);
-    else {
+    const float tau = run.tau;
+    const int np0 = run.np;
+    // slot census: the usual lane of hb has ONE slot that reaches tau.  Then the slot is read back from the stage (the
+    // unit is still there, suppressed ids already -inf) and every lane of hb runs the same few instructions, whatever
+    // its slot; lanes with several slots, or a unit whose range masks live in registers only, take the general path
+    int jj = 0, ns = 0;
+#pragma unroll
+    for (int j = 0; j < kNV; ++j) { const bool h = sm[j] >= tau; ns += h ? 1 : 0; jj = h ? j : jj; }
+    const bool simple = !ragged && !__any_sync(0xffffffffu, mine && ns > 1);
+    float y[4]; bool h[4];
+    int c = 0;
+    if (simple) {
+        const float4 v = st[lane + 32 * jj];
+        y[0] = v.x; y[1] = v.y; y[2] = v.z; y[3] = v.w;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { h[i] = mine && y[i] >= tau && y[i] > -CUDART_INF_F; c += h[i] ? 1 : 0; }
+    } else if (mine) {
+        WRS_TR_CNT(6, 1);
+#pragma unroll
+        for (int j = 0; j < kNV; ++j)
+            if (sm[j] >= tau) {
+#pragma unroll
+                for (int i = 0; i < 4; ++i) c += (x[j][i] >= tau && x[j][i] > -CUDART_INF_F) ? 1 : 0;
+            }
+    }
+    // where the lane's elements go behind the pending ones
+    int pos, total;
+    if (!__any_sync(0xffffffffu, c > 1)) {                               // one element per lane of hb
+        pos = __popc(hb & ((1u << lane) - 1u)); total = __popc(hb);
+    } else {
+        int incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+        pos = incl - c; total = __shfl_sync(0xffffffffu, incl, 31);
+    }
+    const int n_tot = np0 + total;
+    if (n_tot > kCandCap - kMaxK) {
         // massive ties: merge what was pending before this unit, then select exactly straight from the registers
+        WRS_TR_CNT(7, 1000000);
         run_merge(run, wb, np0, K);
         run_exact<4 * kNV>(run, K, [&](int e) { return x[e >> 2][e & 3]; },
                            [&](int e) { return g.a0 + 4 * (lane + 32 * (e >> 2)) + (e & 3); });
+    } else {
+        int w = np0 + pos;
+        if (simple) {
+            const int id0 = g.a0 + 4 * (lane + 32 * jj);
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+                if (h[i]) { wb.v[w] = y[i]; wb.id[w] = id0 + i; ++w; }
+        } else if (mine) {
+#pragma unroll
+            for (int j = 0; j < kNV; ++j)
+                if (sm[j] >= tau) {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i)
+                        if (x[j][i] >= tau && x[j][i] > -CUDART_INF_F) {
+                            wb.v[w] = x[j][i]; wb.id[w] = g.a0 + 4 * (lane + 32 * j) + i; ++w;
+                        }
+                }
+        }
+        __syncwarp();
+        // once the list is full its K-th value is an exact bar and later units add only a few stragglers: those wait for a
+        // cheap register merge (list + pending <= 32 entries); the first unit of a run merges at once to set that bar
+        if (run.n >= K && n_tot + K <= 32) { run.np = n_tot; return; }
+        WRS_TR_CNT(7, n_tot + K > 32 ? 1000 : 1);
+        run_merge(run, wb, n_tot, K);
     }
     run.np = 0;
-    if (lane == 0) wb.n = 0;
     run.tau = fmaxf(run.tau, __shfl_sync(0xffffffffu, run.rv, K - 1));   // -inf while the list holds fewer than K
     __syncwarp();
 }
@@ -199,27 +266,19 @@ __device__ __forceinline__ void run_finish(Run& run, WarpBuf& wb, int K) {
     run.s = (s != s || !run.ref_set) ? s : s * ex2(fmaf(-run.m, kLog2e, run.ref));
 }
 
-// ---- The N = n_rows x upr units of a step are cut into RUNS of deal_q consecutive units (the last one may be short);
-//      run g = units [g q, min(N, g q + q)) is folded by one warp of the scan launch and leaves one partial per (row,
-//      partition) it touches.  q = ceil(N / warps of the grid) and a reciprocal for u / q come from the host, so
-//      neither launch divides; the runs are spread evenly over the CTAs (runs_base, runs_rem).
-__device__ __forceinline__ int run_of(const StepParams& p, int u) {   // u / deal_q (launch_step checks the exactness bound)
-    return (int)(((unsigned long long)(unsigned)u * p.deal_magic) >> 40);
-}
-
-struct RowPartials { int first_run[2], count[2], base[2]; };
-
-__device__ __forceinline__ RowPartials row_partials(const StepParams& p, int row) {
-    RowPartials rp;
-    const int u0 = row * p.upr;
-    rp.base[0] = 0; rp.base[1] = p.n_text_units;
-    const int ua[2] = {u0, u0 + p.n_text_units}, ub[2] = {u0 + p.n_text_units, u0 + p.upr};
-#pragma unroll
-    for (int q = 0; q < 2; ++q) {
-        if (ub[q] > ua[q]) { rp.first_run[q] = run_of(p, ua[q]); rp.count[q] = run_of(p, ub[q] - 1) - rp.first_run[q] + 1; }
-        else { rp.first_run[q] = 0; rp.count[q] = 0; }
+// ---- A row's units are cut into RUNS that never cross a partition: rt runs over the n_text_units text units, rs runs
+//      over the timestamp units, each as even as possible (launch_step picks rt and rs so that the grid's warps get one
+//      run each when the rows allow it).  A run is folded by one warp of the scan launch and leaves ONE partial, in the
+//      slot of its first unit.  All constants come from the host: neither launch divides.
+struct RunGeo { int part, j0, len; };                 // partition, first unit in row, units
+__device__ __forceinline__ RunGeo run_in_row(const StepParams& p, int i) {   // i = run of the row, [text runs | timestamp runs]
+    RunGeo r;
+    if (i < p.rt) { r.part = 0; r.j0 = i * p.t_base + min(i, p.t_rem); r.len = p.t_base + (i < p.t_rem ? 1 : 0); }
+    else {
+        i -= p.rt;
+        r.part = 1; r.j0 = p.n_text_units + i * p.s_base + min(i, p.s_rem); r.len = p.s_base + (i < p.s_rem ? 1 : 0);
     }
-    return rp;
+    return r;
 }
 
 // ---- row merge (one full warp): partials of the row -> K log-probs.  Lane i < K ends with candidate i.
@@ -227,19 +286,13 @@ __device__ __forceinline__ RowPartials row_partials(const StepParams& p, int row
 // with independent 16-byte loads up front, so the usual row (<= 32 partials) costs ONE round trip to L2.
 struct RowOut { float lp; int tok; unsigned flags; };
 
-__device__ __forceinline__ RowOut merge_row(const StepParams& p, int row, unsigned rule_flags, const RowPartials& rpz, WarpBuf& wb,
-                                         unsigned char* lists) {
+__device__ __forceinline__ RowOut merge_row(const StepParams& p, int row, unsigned rule_flags, WarpBuf& wb, unsigned char* lists) {
     const int lane = threadIdx.x & 31;
     const int K = p.K, KQ = (K + 3) >> 2;
     const Partial* __restrict__ parts = p.partials + (int64_t)row * p.upr;
-    const int cT = rpz.count[0], cnt = rpz.count[0] + rpz.count[1];
-    // partial i of the list [text partials | timestamp partials] sits in the slot of its run's first unit of the
-    // partition: the run's first unit, or the partition's first unit if the run starts before it
-    auto part_of = [&](int i) {
-        const int q = i < cT ? 0 : 1;
-        const int g = rpz.first_run[q] + (q ? i - cT : i);
-        return parts + max(g * p.deal_q - row * p.upr, rpz.base[q]);
-    };
+    const int cT = p.rt, cnt = p.rpr;
+    // partial i of the list [text partials | timestamp partials] sits in the slot of its run's first unit
+    auto part_of = [&](int i) { return parts + run_in_row(p, i).j0; };
     auto load_entries = [&](const Partial* pp, float (&ev)[kMaxK], int (&ei)[kMaxK]) {
 #pragma unroll
         for (int q = 0; q < kMaxK / 4; ++q)
@@ -675,19 +728,45 @@ __device__ __forceinline__ void beam_fast_outputs(const StepParams& p, int audio
     }
 }
 
-#ifdef WRS_TRACE
-// investigation aid (tools/debug/dec_trace.py): per-warp event times in ns, [warp][8]
-__device__ unsigned long long g_trace[148 * kStepWarps * 8];
-__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
-#define WRS_TR(slot) do { if (lane == 0) g_trace[gw * 8 + (slot)] = gtime(); } while (0)
-#define WRS_TR_ADD(slot, v) do { if (lane == 0) g_trace[gw * 8 + (slot)] += (v); } while (0)
-#else
-#define WRS_TR(slot) do {} while (0)
-#define WRS_TR_ADD(slot, v) do {} while (0)
-#endif
 
-// ---- launch 1 of a step: every warp folds its run of units and leaves one partial per (row, partition) run.  No atomics,
-//      no fences: the kernel boundary hands the partials to the tail.
+// ---- where the units of a warp's runs live.  A run's units are consecutive units of one partition of one row: the
+//      walker steps through them with one addition and recomputes everything else only when the next run begins
+//      (run g + stride of the same warp; beyond n_runs the walker is exhausted)
+struct Walk {
+    int g;               // run
+    int row, part, pe;   // the run's row, partition (0 text, 1 timestamps) and the id the partition's ids end at
+    int j, j0, j_end;    // current unit in row, the run's first unit and the unit behind its last one
+    int a0;              // id of the unit's first element slot: 16-byte aligned in memory, up to 3 ids in front of the partition
+    const float* rp;     // the row's logits
+};
+__device__ __forceinline__ void walk_enter(const StepParams& p, Walk& w) {    // w.g is set and < n_runs
+    w.row = (int)(((unsigned long long)(unsigned)w.g * p.rpr_magic) >> 40);
+    const RunGeo r = run_in_row(p, w.g - w.row * p.rpr);
+    w.part = r.part; w.j = w.j0 = r.j0; w.j_end = r.j0 + r.len;
+    w.rp = p.logits + (int64_t)w.row * p.row_stride;
+    if (r.part == 0) {
+        w.pe = p.ts_split;
+        w.a0 = w.j * kUnit - (int)((reinterpret_cast<uintptr_t>(w.rp) >> 2) & 3);
+    } else {
+        w.pe = p.rc.n_vocab;
+        w.a0 = p.ts_split + (w.j - p.n_text_units) * kUnit - (int)((reinterpret_cast<uintptr_t>(w.rp + p.ts_split) >> 2) & 3);
+    }
+}
+__device__ __forceinline__ void walk_step(const StepParams& p, Walk& w, int stride) {
+    if (++w.j < w.j_end) { w.a0 += kUnit; return; }
+    w.g += stride;
+    if (w.g < p.n_runs) walk_enter(p, w);
+}
+// 16-byte chunks [c_lo, c_hi) of the unit that are bulk-copied: those that hold ids of the partition, except a chunk that
+// would reach outside the logits buffer (before row 0, behind the last row), whose <= 3 ids are read one by one instead
+__device__ __forceinline__ void walk_chunks(const StepParams& p, const Walk& w, int& c_lo, int& c_hi) {
+    c_lo = (w.row == 0 && w.a0 < 0) ? 1 : 0;
+    c_hi = min(kUnit >> 2, (w.pe - w.a0 + 3) >> 2);
+    if (w.row == p.n_rows - 1 && w.a0 + 4 * c_hi > p.rc.n_vocab) --c_hi;
+}
+
+// ---- launch 1 of a step: every warp folds its run(s) of units and leaves one partial per run.  No atomics, no fences:
+//      the kernel boundary hands the partials to the tail.
 __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const StepParams p) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -698,63 +777,43 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const Step
     unsigned long long* bars = reinterpret_cast<unsigned long long*>(slice + kStages * kStageBytes + kScanScratch);
     auto stage_of = [&](int s) { return reinterpret_cast<float4*>(s == 0 ? slice : slice + kScanScratch + s * kStageBytes); };
 
-    // this warp's run of units (run_of): CTA b folds runs [b runs_base + min(b, runs_rem), ...), one per warp
-    const int N = p.n_rows * p.upr;
-    const int b = (int)blockIdx.x;
-    if (warp >= p.runs_base + (b < p.runs_rem ? 1 : 0)) return;
-    const int gw = b * p.runs_base + min(b, p.runs_rem) + warp;
-    const int u_begin = gw * p.deal_q, u_end = min(N, u_begin + p.deal_q);
-    const int n_units = u_end - u_begin;
+    // Runs are dealt to the grid's warps round-robin over the CTAs: consecutive runs belong to the same row, and rows whose
+    // rules mask most of a partition cost next to nothing -- interleaved, every SM gets the same mix of cheap and full runs
+    const int stride = (int)gridDim.x * kStepWarps;
+#ifdef WRS_DEAL_BLOCKED
+    const int gw = (int)blockIdx.x * kStepWarps + warp;
+#else
+    const int gw = warp * (int)gridDim.x + (int)blockIdx.x;
+#endif
+    if (gw >= p.n_runs) return;
 #ifdef WRS_TRACE
     if (lane == 0) for (int q = 0; q < 8; ++q) g_trace[gw * 8 + q] = 0;
 #endif
     WRS_TR(0);
 
-    // ---- where unit k of this warp lives: needs nothing but the row pointer's alignment
-    struct Place { int row, j, part, a0, c_lo, c_hi; };
-    struct Cursor { int row, j; };                        // (row, unit in row); a warp's units are consecutive
-    auto advance = [&](Cursor& c) { if (++c.j == p.upr) { c.j = 0; ++c.row; } };
-    auto place_at = [&](const Cursor& c) {
-        Place q;
-        q.row = c.row; q.j = c.j;
-        const float* rp = p.logits + (int64_t)q.row * p.row_stride;
-        int pb, pe;                                       // the partition's id range
-        if (q.j < p.n_text_units) {
-            q.part = 0; pb = 0; pe = p.ts_split;
-            q.a0 = -(int)((reinterpret_cast<uintptr_t>(rp) >> 2) & 3) + q.j * kUnit;
-        } else {
-            q.part = 1; pb = p.ts_split; pe = p.rc.n_vocab;
-            q.a0 = p.ts_split - (int)((reinterpret_cast<uintptr_t>(rp + p.ts_split) >> 2) & 3) + (q.j - p.n_text_units) * kUnit;
-        }
-        // 16-byte chunks [c_lo, c_hi) of the unit that hold ids of the partition; a chunk that would reach outside the
-        // logits buffer (before row 0, behind the last row) is left out and its <= 3 ids are read one by one instead
-        q.c_lo = (max(q.a0, pb) - q.a0) >> 2;
-        q.c_hi = min(kUnit >> 2, (min(q.a0 + kUnit, pe) - q.a0 + 3) >> 2);
-        if (q.row == 0 && q.a0 + 4 * q.c_lo < 0) ++q.c_lo;
-        if (q.row == p.n_rows - 1 && q.a0 + 4 * q.c_hi > p.rc.n_vocab) --q.c_hi;
-        return q;
-    };
+    Walk wi;                                              // the next unit to request
+    wi.g = gw;
+    walk_enter(p, wi);
+    Walk wf = wi;                                         // the unit being folded
     // start the flight of the next unit not yet requested into the next stage: one bulk copy, completion by byte
     // count on the stage's mbarrier
-    const int row_first = u_begin / p.upr;
-    Cursor cur_issue = {row_first, u_begin - row_first * p.upr};
-    int stage_issue = 0, n_issued = 0;
+    int stage_issue = 0, in_flight = 0;
     auto issue_next = [&]() {
-        const Place q = place_at(cur_issue);
+        int c_lo, c_hi;
+        walk_chunks(p, wi, c_lo, c_hi);
         if (elect_one()) {
             unsigned long long* bar = bars + stage_issue;
-            const int bytes = (q.c_hi - q.c_lo) * 16;
+            const int bytes = (c_hi - c_lo) * 16;
             if (bytes > 0) {
                 mbar_expect_tx(bar, (unsigned)bytes);
-                bulk_g2s(reinterpret_cast<unsigned char*>(stage_of(stage_issue)) + 16 * q.c_lo,
-                         p.logits + (int64_t)q.row * p.row_stride + q.a0 + 4 * q.c_lo, (unsigned)bytes, bar);
+                bulk_g2s(reinterpret_cast<unsigned char*>(stage_of(stage_issue)) + 16 * c_lo, wi.rp + wi.a0 + 4 * c_lo, (unsigned)bytes, bar);
             } else {
                 mbar_arrive(bar);
             }
         }
-        advance(cur_issue);
+        walk_step(p, wi, stride);
         stage_issue = stage_issue + 1 == kStages ? 0 : stage_issue + 1;
-        ++n_issued;
+        ++in_flight;
     };
     if (lane == 0) {
 #pragma unroll
@@ -764,116 +823,125 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const Step
     // every warp puts its first unit in flight before anything else
     issue_next();
 
-    // rules of the first two rows this warp touches are fetched up front (a later row change costs a bubble)
-    int64_t tk_last[2], tk_pen[2];
-#pragma unroll
-    for (int q = 0; q < 2; ++q) {
-        const int r = min(row_first + q, p.n_rows - 1);
+    // the rules of a run's row come from the row's two newest tokens: those of the first run are fetched now, those of the
+    // warp's next run when a run begins
+    auto load_tokens = [&](int g, int64_t& last, int64_t& pen) {
+        const int r = (int)(((unsigned long long)(unsigned)min(g, p.n_runs - 1) * p.rpr_magic) >> 40);
         const int64_t* rt = p.tokens + (int64_t)r * p.tok_stride;
-        tk_last[q] = rt[p.cur_len - 1];
-        tk_pen[q] = p.cur_len >= 2 ? rt[p.cur_len - 2] : 0;
-    }
-    int rules_row = -1;
-    RowRules rules;
-    rules.t_lo = rules.t_hi = rules.s_lo = rules.s_hi = 0; rules.flags = 0;
-    auto rules_for = [&](int row) {
-        if (row == rules_row) return;
-        if (row == row_first) rules = row_rules_from(p.rc, tk_last[0], tk_pen[0], p.cur_len, p.sample_begin);
-        else if (row == row_first + 1) rules = row_rules_from(p.rc, tk_last[1], tk_pen[1], p.cur_len, p.sample_begin);
-        else rules = row_rules(p.rc, p.tokens + (int64_t)row * p.tok_stride, p.cur_len, p.sample_begin);
-        rules_row = row;
+        last = rt[p.cur_len - 1];
+        pen = p.cur_len >= 2 ? rt[p.cur_len - 2] : 0;
     };
-    // ids of the unit that survive the row's rules
-    auto geom_of = [&](const Place& q) {
-        Geom g;
-        g.row = q.row; g.part = q.part; g.a0 = q.a0;
-        rules_for(q.row);
-        if (q.part == 0) { g.lo = max(max(q.a0, 0), rules.t_lo); g.hi = min(min(q.a0 + kUnit, p.ts_split), rules.t_hi); }
-        else { g.lo = max(max(q.a0, p.ts_split), rules.s_lo); g.hi = min(min(q.a0 + kUnit, p.rc.n_vocab), rules.s_hi); }
-        return g;
-    };
-    auto bitmap_of = [&](const Place& q) { return __ldg(p.bm + min((max(q.a0, 0) >> 5) + lane, p.bm_words - 1)); };
-    // bring unit k into registers; slot j of a lane holds ids a0 + 4 (lane + 32 j) ..+3, everything outside [lo, hi)
-    // reads as -inf
-    auto fetch = [&](int stage, const Place& q, const Geom& g, float (&x)[kNV][4]) {
-        const float4* st = stage_of(stage);
+    int64_t tk_last, tk_pen;
+    load_tokens(gw, tk_last, tk_pen);
+    // lane l takes bitmap word (first id of the unit >> 5) + l: 29 words cover the unit
+    auto bitmap_of = [&](const Walk& q) { return __ldg(p.bm + min((max(q.a0, 0) >> 5) + lane, p.bm_words - 1)); };
+    // bring the unit into registers; slot j of a lane holds ids a0 + 4 (lane + 32 j) ..+3, everything outside [lo, hi)
+    // and every suppressed id reads as -inf
+    auto fetch = [&](int stage, const Walk& q, const Geom& g, uint32_t bmw, float (&x)[kNV][4]) {
+        float4* st = stage_of(stage);
+        float* stf = reinterpret_cast<float*>(st);
+        const bool ragged = g.lo != g.a0 || g.hi != g.a0 + kUnit;
+        if (ragged) {
+            // the <= 3 ids at the head of row 0 / the tail of the last row that the copy left out
+            int c_lo, c_hi;
+            walk_chunks(p, q, c_lo, c_hi);
+            const int e_tail = g.a0 + 4 * c_hi;
+            const bool tail = q.row == p.n_rows - 1 && c_hi < (kUnit >> 2) && e_tail < g.hi;
+            if (c_lo > 0 || tail) {
+                if (lane < 4) {
+                    const int e = g.a0 + lane;
+                    if (c_lo > 0 && e >= g.lo && e < g.hi) stf[lane] = __ldcs(q.rp + e);
+                } else if (lane < 8) {
+                    const int e = e_tail + lane - 4;
+                    if (tail && e < g.hi) stf[4 * c_hi + lane - 4] = __ldcs(q.rp + e);
+                }
+                __syncwarp();
+            }
+        }
+        if (__ballot_sync(0xffffffffu, bmw != 0u)) {
+            poke_suppressed(stf, bmw, max(g.a0, 0) >> 5, g.a0);
+#ifndef WRS_NO_POKE_FENCE
+            fence_proxy_async();                          // the stage is the target of a later bulk copy
+#endif
+            __syncwarp();
+        }
 #pragma unroll
         for (int j = 0; j < kNV; ++j) {
             const float4 v = st[lane + 32 * j];
             x[j][0] = v.x; x[j][1] = v.y; x[j][2] = v.z; x[j][3] = v.w;
         }
-        if (g.lo != g.a0 || g.hi != g.a0 + kUnit) {      // ragged or clipped: mask, and fetch what the copy left out
-            const float* __restrict__ rp = p.logits + (int64_t)g.row * p.row_stride;
+        if (ragged) {
 #pragma unroll
             for (int j = 0; j < kNV; ++j) {
-                const int c = lane + 32 * j, e = g.a0 + 4 * c;
+                const int e = g.a0 + 4 * (lane + 32 * j);
 #pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const bool in = e + i >= g.lo && e + i < g.hi;
-                    if (!in) x[j][i] = -CUDART_INF_F;
-                    else if (c < q.c_lo || c >= q.c_hi) x[j][i] = __ldcs(rp + e + i);
-                }
+                for (int i = 0; i < 4; ++i)
+                    if (e + i < g.lo || e + i >= g.hi) x[j][i] = -CUDART_INF_F;
             }
         }
     };
 
     Run run;
     run_reset(run);
-    Cursor cur = {row_first, u_begin - row_first * p.upr};
-    Place qc = place_at(cur);
-    uint32_t bm_c = bitmap_of(qc);
-    int run_j0 = qc.j, run_units = 0;                    // first unit-in-row and unit count of the current run
+    uint32_t bm_c = bitmap_of(wf);
     int stage = 0;                                       // stage and mbarrier phase of the unit being folded
     unsigned phase = 0u;
+    bool first = true;
+    RowRules rules;
+    rules.t_lo = rules.t_hi = rules.s_lo = rules.s_hi = 0; rules.flags = 0;
 
-    for (int k = 0; k < n_units; ++k) {
-        const Place q = qc;
+    while (wf.g < p.n_runs) {
+        const Walk q = wf;
         const uint32_t bmw = bm_c;
-        const bool has_next = k + 1 < n_units;
-        const Geom g = geom_of(q);
-        if (has_next) { advance(cur); qc = place_at(cur); bm_c = bitmap_of(qc); }
+        if (q.j == q.j0) {                               // a run begins: its row's rules; request the next run's tokens
+            rules = row_rules_from(p.rc, tk_last, tk_pen, p.cur_len, p.sample_begin);
+            if (q.g + stride < p.n_runs) load_tokens(q.g + stride, tk_last, tk_pen);
+        }
+        // ids of the unit that survive the row's rules
+        Geom g;
+        g.row = q.row; g.part = q.part; g.a0 = q.a0;
+        g.lo = max(max(q.a0, q.part ? p.ts_split : 0), q.part ? rules.s_lo : rules.t_lo);
+        g.hi = min(min(q.a0 + kUnit, q.pe), q.part ? rules.s_hi : rules.t_hi);
+        walk_step(p, wf, stride);
+        if (wf.g < p.n_runs) bm_c = bitmap_of(wf);
 #ifdef WRS_TRACE
         const unsigned long long tw0 = gtime();
 #endif
         mbar_wait(bars + stage, phase);                  // also when nothing survives: the stage is reused
+        --in_flight;
 #ifdef WRS_TRACE
         const unsigned long long tw1 = gtime();
         WRS_TR_ADD(4, tw1 - tw0);
 #endif
-        if (k == 0) {
+        if (first) {
             // only now the later units: all first units of the grid (a quarter of the step's bytes) land first and
             // the arithmetic starts while the rest streams in behind them
+            first = false;
             WRS_TR(1);
 #pragma unroll
             for (int k2 = 1; k2 < kStages; ++k2)
-                if (k2 < n_units) issue_next();
-        }
-        if (run_units == 0) {                            // a run starts with an empty pending list (merges and tails share wb)
-            if (lane == 0) wb.n = 0;
-            __syncwarp();
+                if (wi.g < p.n_runs) issue_next();
         }
         if (g.hi > g.lo) {
             float x[kNV][4];
-            fetch(stage, q, g, x);
-            reduce_unit(x, g, bmw, max(g.a0, 0) >> 5, p.K, wb, run);
+            fetch(stage, q, g, bmw, x);
+            reduce_unit(x, g, stage_of(stage), g.lo != g.a0 || g.hi != g.a0 + kUnit, p.K, wb, run);
         }
         __syncwarp();                                    // every lane has taken its share of the stage out
 #ifdef WRS_TRACE
         WRS_TR_ADD(5, gtime() - tw1);
 #endif
-        if (n_issued < n_units) issue_next();
+        if (wi.g < p.n_runs) issue_next();
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
-        ++run_units;
         WRS_TR(2);
-        if (has_next && qc.row == q.row && qc.part == q.part) continue;
+        if (q.j + 1 < q.j_end) continue;
 
-        // ---- end of a (row, partition) run: leave the partial in the slot of the run's first unit
+        // ---- end of the run: leave the partial in the slot of the run's first unit
         run_finish(run, wb, p.K);
-        Partial* out = p.partials + (int64_t)q.row * p.upr + run_j0;
+        Partial* out = p.partials + (int64_t)q.row * p.upr + q.j0;
         if (lane < kMaxK) { out->v[lane] = run.rv; out->id[lane] = run.ri; }
         if (lane == 0) { out->m = run.m; out->s = run.s; out->n = run.n; }
         run_reset(run);
-        run_j0 = qc.j; run_units = 0;
     }
 
     WRS_TR(3);
@@ -899,7 +967,6 @@ __global__ void __launch_bounds__(kMaxBeam * 32) decode_tail_kernel(const StepPa
 #endif
     // everything this row needs from memory is requested before the first use: its two newest tokens (rules), the
     // token prefixes (beam dedup), the running sums and, inside merge_row, the partials
-    const RowPartials rpz = row_partials(p, row);
     const int64_t* mine = p.tokens + (int64_t)row * p.tok_stride;
     const int64_t tk_last = mine[p.cur_len - 1], tk_pen = p.cur_len >= 2 ? mine[p.cur_len - 2] : 0;
     // which later beams of this audio hold an identical prefix (HashMap key = whole sequence, beam_search.rs:74-77):
@@ -924,7 +991,7 @@ __global__ void __launch_bounds__(kMaxBeam * 32) decode_tail_kernel(const StepPa
     }
     if (lane == 0) wb.n = 0;
     __syncwarp();
-    RowOut r = merge_row(p, row, 0u, rpz, wb, slice);
+    RowOut r = merge_row(p, row, 0u, wb, slice);
     const RowRules rr_row = row_rules_from(p.rc, tk_last, tk_pen, p.cur_len, p.sample_begin);
     r.flags |= rr_row.flags;
     unsigned same = 0u;
@@ -1065,14 +1132,35 @@ int launch_step(wrs_decoder* dec, StepParams p, cudaStream_t stream) {
     }
     const int64_t units = (int64_t)p.n_rows * p.upr;
     const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctx->sm_count, (units + kStepWarps - 1) / kStepWarps));
-    // runs of q = ceil(units / warps of the grid) units; u / q = (u * ceil(2^40 / q)) >> 40, exact while u (q - 1) < 2^40
-    const int64_t q = (units + (int64_t)grid * kStepWarps - 1) / ((int64_t)grid * kStepWarps), n_runs = (units + q - 1) / q;
-    if (units >= (1ll << 31) || units * (q - 1) >= (1ll << 40))
-        return fail(ctx, WRS_ERR_UNSUPPORTED, "decode step: n_rows x units per row too large for the unit dealing");
-    p.deal_q = (int)q; p.deal_magic = ((1ull << 40) + (uint64_t)q - 1) / (uint64_t)q;
-    p.runs_base = (int)(n_runs / grid); p.runs_rem = (int)(n_runs % grid);
-    decode_scan_kernel<<<grid, kStepThreads, smem, stream>>>(p);
+    // the shortest longest run q for which the rows' runs fit the grid's warps (one run per warp); if even one run per
+    // partition does not fit, warps take several runs in turn
+    {
+        const int64_t Wt = (int64_t)grid * kStepWarps;
+        const int nt = p.n_text_units, ns = p.n_ts_units;
+        int rt = 1, rs = ns > 0 ? 1 : 0;
+        for (int q = 1; q <= std::max(nt, ns); ++q) {
+            const int a = (nt + q - 1) / q, b2 = ns > 0 ? (ns + q - 1) / q : 0;
+            if ((int64_t)(a + b2) * p.n_rows <= Wt) {
+                rs = b2;
+                rt = (int)std::min<int64_t>(nt, std::max<int64_t>(a, Wt / p.n_rows - b2));   // spare warps shorten the text runs
+                break;
+            }
+        }
+        p.rt = rt; p.rs = rs; p.rpr = rt + rs;
+        p.t_base = nt / rt; p.t_rem = nt % rt;
+        p.s_base = rs > 0 ? ns / rs : 0; p.s_rem = rs > 0 ? ns % rs : 0;
+        const int64_t n_runs = (int64_t)p.rpr * p.n_rows;
+        // g / rpr = (g * ceil(2^40 / rpr)) >> 40, exact while g (rpr - 1) < 2^40
+        if (n_runs >= (1ll << 31) || n_runs * (p.rpr - 1) >= (1ll << 40))
+            return fail(ctx, WRS_ERR_UNSUPPORTED, "decode step: n_rows x runs per row too large for the unit dealing");
+        p.n_runs = (int)n_runs;
+        p.rpr_magic = ((1ull << 40) + (uint64_t)p.rpr - 1) / (uint64_t)p.rpr;
+    }
+    // investigation aid: WRS_DEBUG_ONLY=scan|tail times one launch alone (results are then meaningless)
+    static const char* only = std::getenv("WRS_DEBUG_ONLY");
+    if (!only || only[0] != 't') decode_scan_kernel<<<grid, kStepThreads, smem, stream>>>(p);
     WRS_CUDA(ctx, cudaGetLastError());
+    if (only && only[0] == 's') return WRS_OK;
     const int rows_per_group = MODE == MODE_BEAM ? p.beam : 1;
     // (programmatic dependent launch was measured and lost 3 us per step: the early tail CTAs only get in the scan's way)
     decode_tail_kernel<MODE><<<p.n_rows / rows_per_group, rows_per_group * 32, (size_t)kTailHead + (size_t)rows_per_group * kTailBytes, stream>>>(p);
