@@ -53,12 +53,13 @@ enum { MODE_BEAM = 0, MODE_GREEDY = 1, MODE_FILTER = 2 };
 constexpr int kMaxBeam = 15;
 constexpr int kMaxCandAudio = kMaxBeam * kMaxK;          // 240
 #ifndef WRS_STAGES
-#define WRS_STAGES 3
+#define WRS_STAGES 2
 #endif
 constexpr int kStages = WRS_STAGES;                               // units a warp keeps in flight (bulk copies, one mbarrier each)
 constexpr int kStageBytes = kUnit * 4;                    // landing zone of one unit
 constexpr int kScratchBytes = 2688;                      // per-warp scratch behind stage 0 (WarpBuf, or the fast beam tail's tables)
-constexpr int kTailBytes = kStageBytes + kScratchBytes;  // the general beam tail (beam > 5) overlays stage 0 + scratch
+constexpr int kTailBytes = kStageBytes + kScratchBytes;  // per-warp slice of the tail launch
+constexpr int kTailLists = 2 * 4 * 32 * kMaxK;           // the row merge's cell lists, [entry][lane] values then ids
 constexpr int kScanScratch = 1056;                       // scan launch: per-warp scratch behind stage 0 (WarpBuf only)
 constexpr int kWarpSmem = kStages * kStageBytes + kScanScratch + 32;   // + the stages' mbarriers
 constexpr int kTailRows = kMaxBeam * 144;                // tail launch: the group's row results ...
@@ -96,7 +97,7 @@ struct StepParams {
 
 #ifdef WRS_TRACE
 // investigation aid (tools/debug/dec_trace.py): per-warp event times in ns, [warp][8]
-__device__ unsigned long long g_trace[148 * kStepWarps * 8];
+__device__ unsigned long long g_trace[(148 * kStepWarps + 1024) * 8];   // scan warps, then tail rows
 __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
 #define WRS_TR(slot) do { if (lane == 0) g_trace[gw * 8 + (slot)] = gtime(); } while (0)
 #define WRS_TR_ADD(slot, v) do { if (lane == 0) g_trace[gw * 8 + (slot)] += (v); } while (0)
@@ -254,6 +255,68 @@ __device__ __forceinline__ void reduce_unit(float (&x)[kNV][4], const Geom& g, c
     __syncwarp();
 }
 
+// Fold one unit into the run, scan launch: statistics as in reduce_unit, but the top-K list holds CELLS, not ids.  A cell
+// is (unit, lane): the 28 ids a lane holds of a unit, valued by their maximum.  The K best elements of a row lie in its K
+// best cells (K cells at or above a value are K distinct elements at or above it), so the scan keeps the best cells only
+// -- one candidate per lane and unit, no per-element work -- and the tail reads the few winning cells again.  Cells
+// order by (value desc, cell id asc); a dropped cell that equals the list's K-th value raises run.tie, and the tail then
+// scans the row itself (exact ties between the best cells of a row: quantised logits, not real ones).
+__device__ __forceinline__ void fold_unit(float (&x)[kNV][4], int unit_in_row, int K, WarpBuf& wb, Run& run) {
+    const int lane = threadIdx.x & 31;
+    float tmax = fmaxf(fmaxf(x[0][0], x[0][1]), fmaxf(x[0][2], x[0][3]));
+#pragma unroll
+    for (int j = 1; j < kNV; ++j) tmax = fmaxf(tmax, fmaxf(fmaxf(x[j][0], x[j][1]), fmaxf(x[j][2], x[j][3])));
+    run.lm = fmaxf(run.lm, tmax);
+    // exp-sum against the run's integer log2-domain reference (see reduce_unit)
+    if (!run.ref_set || __any_sync(0xffffffffu, fmaf(tmax, kLog2e, -run.ref) > 92.0f)) {
+        const float wm = warp_max(tmax);
+        if (wm > -CUDART_INF_F) {
+            const float R = rintf(wm * kLog2e);
+            if (run.ref_set) run.ls *= ex2(run.ref - R);
+            run.ref = R; run.ref_set = true;
+        }
+    }
+    {
+        const f32x2 l2e = pack2(kLog2e, kLog2e), nref = pack2(-run.ref, -run.ref);
+        f32x2 s01 = pack2(0.0f, 0.0f), s23 = s01;
+#pragma unroll
+        for (int j = 0; j < kNV; ++j) {
+            float a0, a1, a2, a3;
+            unpack2(fma_(pack2(x[j][0], x[j][1]), l2e, nref), a0, a1);
+            unpack2(fma_(pack2(x[j][2], x[j][3]), l2e, nref), a2, a3);
+            s01 = add_(s01, pack2(ex2(a0), ex2(a1)));
+            s23 = add_(s23, pack2(ex2(a2), ex2(a3)));
+        }
+        float t0, t1;
+        unpack2(add_(s01, s23), t0, t1);
+        run.ls += t0 + t1;
+    }
+    // the unit's cells that reach tau, a value the run's K-th best cell is known to reach
+    if (run.tau == -CUDART_INF_F) run.tau = kth_threshold(tmax, K);
+    bool hit = tmax >= run.tau && tmax > -CUDART_INF_F;
+    unsigned hb = __ballot_sync(0xffffffffu, hit);
+    if (!hb) return;
+    if (run.np > 0 && run.np + __popc(hb) + K > 32) {     // keep the merges one entry per lane
+        run_merge(run, wb, run.np, K);
+        run.np = 0;
+        run.tau = fmaxf(run.tau, __shfl_sync(0xffffffffu, run.rv, K - 1));
+        hit = tmax >= run.tau && tmax > -CUDART_INF_F;
+        hb = __ballot_sync(0xffffffffu, hit);
+        if (!hb) return;
+    }
+    if (hit) {
+        const int pos = run.np + __popc(hb & ((1u << lane) - 1u));
+        wb.v[pos] = tmax; wb.id[pos] = unit_in_row * 32 + lane;
+    }
+    __syncwarp();
+    const int n_tot = run.np + __popc(hb);
+    if (run.n >= K && n_tot + K <= 32) { run.np = n_tot; return; }
+    run_merge(run, wb, n_tot, K);
+    run.np = 0;
+    run.tau = fmaxf(run.tau, __shfl_sync(0xffffffffu, run.rv, K - 1));   // -inf while the list holds fewer than K
+    __syncwarp();
+}
+
 // End of a run: merge the pending candidates and turn the lane-local statistics into {max, sum exp(x - max)}.
 __device__ __forceinline__ void run_finish(Run& run, WarpBuf& wb, int K) {
     if (run.np > 0) run_merge(run, wb, run.np, K);
@@ -281,50 +344,119 @@ __device__ __forceinline__ RunGeo run_in_row(const StepParams& p, int i) {   // 
     return r;
 }
 
-// ---- row merge (one full warp): partials of the row -> K log-probs.  Lane i < K ends with candidate i.
-// Lane l takes partial l of the row's list [text partials | timestamp partials]; header and entries are fetched
-// with independent 16-byte loads up front, so the usual row (<= 32 partials) costs ONE round trip to L2.
-struct RowOut { float lp; int tok; unsigned flags; };
+// ---- the tail reads logits again, cell by cell: the 28 ids that lane L of the scan held of the unit whose first slot id
+//      is a0 (7 pieces of 16 bytes), with the masks the scan applied -- the partition's surviving range [lo, hi) and the
+//      step's suppress bitmap.  Pieces that would reach outside the logits buffer are read id by id.
+__device__ __forceinline__ void load_cell(const StepParams& p, const float* __restrict__ rp, int row, int a0, int L, int lo, int hi,
+                                          bool active, float (&x)[kNV][4]) {
+    // all loads first, without branches (a piece that is not wanted reads a harmless aligned address): one round trip
+    float4 t[kNV]; uint32_t w0[kNV], w1[kNV]; bool need[kNV], inside[kNV];
+    const float4* harmless = reinterpret_cast<const float4*>(p.partials);
+#pragma unroll
+    for (int s = 0; s < kNV; ++s) {
+        const int e0 = a0 + 4 * (L + 32 * s);
+        need[s] = active && e0 < hi && e0 + 3 >= lo;
+        inside[s] = !(row == 0 && e0 < 0) && !(row == p.n_rows - 1 && e0 + 3 >= p.rc.n_vocab);
+        t[s] = __ldcs((need[s] && inside[s]) ? reinterpret_cast<const float4*>(rp + e0) : harmless);
+        w0[s] = __ldg(p.bm + min(max(e0, 0) >> 5, p.bm_words - 1));
+        w1[s] = __ldg(p.bm + min(max(e0 + 3, 0) >> 5, p.bm_words - 1));
+    }
+#pragma unroll
+    for (int s = 0; s < kNV; ++s) {
+        const int e0 = a0 + 4 * (L + 32 * s);
+        float v[4] = {t[s].x, t[s].y, t[s].z, t[s].w};
+        const bool clean = inside[s] && e0 >= lo && e0 + 3 < hi && (w0[s] | w1[s]) == 0u;
+        if (!need[s]) {
+            v[0] = v[1] = v[2] = v[3] = -CUDART_INF_F;
+        } else if (!clean) {                             // the usual piece is wanted whole and names no suppressed id
+            if (need[s] && !inside[s]) {                 // head of row 0 / tail of the last row
+#pragma unroll
+                for (int i = 0; i < 4; ++i) v[i] = (e0 + i >= lo && e0 + i < hi) ? __ldcs(rp + e0 + i) : -CUDART_INF_F;
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int id = e0 + i;
+                const uint32_t w = (id >> 5) == (max(e0, 0) >> 5) ? w0[s] : w1[s];
+                if (!need[s] || id < lo || id >= hi || ((w >> (id & 31)) & 1u)) v[i] = -CUDART_INF_F;
+            }
+        }
+        x[s][0] = v[0]; x[s][1] = v[1]; x[s][2] = v[2]; x[s][3] = v[3];
+    }
+}
+// first slot id and surviving id range of unit u of a row (what the scan's walker and rules give)
+__device__ __forceinline__ void unit_range(const StepParams& p, const float* rp, const RowRules& rr, int u, int& a0, int& lo, int& hi) {
+    if (u < p.n_text_units) {
+        a0 = u * kUnit - (int)((reinterpret_cast<uintptr_t>(rp) >> 2) & 3);
+        lo = max(max(a0, 0), rr.t_lo); hi = min(min(a0 + kUnit, p.ts_split), rr.t_hi);
+    } else {
+        a0 = p.ts_split + (u - p.n_text_units) * kUnit - (int)((reinterpret_cast<uintptr_t>(rp + p.ts_split) >> 2) & 3);
+        lo = max(max(a0, p.ts_split), rr.s_lo); hi = min(min(a0 + kUnit, p.rc.n_vocab), rr.s_hi);
+    }
+}
 
-__device__ __forceinline__ RowOut merge_row(const StepParams& p, int row, unsigned rule_flags, WarpBuf& wb, unsigned char* lists) {
+// ---- the row's K best ids the long way: one warp reads the whole row again (reduce_unit).  Taken when the best cells of
+//      the row tie exactly (quantised logits) or a winning cell holds more candidates than the merge buffers take.
+__device__ __noinline__ void rescan_row(const StepParams& p, int row, const RowRules& rr, bool ts_over_text, WarpBuf& wb, float& out_v,
+                                        int& out_i) {
+    const int lane = threadIdx.x & 31;
+    const float* rp = p.logits + (int64_t)row * p.row_stride;
+    Run cand;
+    run_reset(cand);
+    for (int u = ts_over_text ? p.n_text_units : 0; u < p.upr; ++u) {
+        Geom g;
+        g.row = row; g.part = u < p.n_text_units ? 0 : 1;
+        unit_range(p, rp, rr, u, g.a0, g.lo, g.hi);
+        if (g.hi <= g.lo) continue;
+        float x[kNV][4];
+        load_cell(p, rp, row, g.a0, lane, g.lo, g.hi, true, x);
+        reduce_unit(x, g, nullptr, true, p.K, wb, cand);
+    }
+    run_finish(cand, wb, p.K);
+    out_v = cand.rv; out_i = cand.ri;
+}
+
+// ---- row merge (one full warp): partials of the row -> K log-probs.  Lane i < K ends with candidate i.
+// Lane l takes partial l of the row's list [text partials | timestamp partials] (launch_step keeps a row at <= 32 runs);
+// header and cell list are fetched with independent 16-byte loads up front.  The partials' lists hold CELLS (fold_unit):
+// the K best cells of the row are found by a k-way merge, read again from the logits, and their ids at or above the K-th
+// cell's value compete for the K places.
+struct RowOut {
+    float lp; int tok; unsigned flags;
+#ifdef WRS_TRACE
+    unsigned long long t_sums, t_cells, t_loaded;      // phase times of the merge (global timer)
+#endif
+};
+
+__device__ __forceinline__ RowOut merge_row(const StepParams& p, int row, const RowRules& rr, WarpBuf& wb, unsigned char* lists,
+                                         int* glist) {
     const int lane = threadIdx.x & 31;
     const int K = p.K, KQ = (K + 3) >> 2;
     const Partial* __restrict__ parts = p.partials + (int64_t)row * p.upr;
     const int cT = p.rt, cnt = p.rpr;
-    // partial i of the list [text partials | timestamp partials] sits in the slot of its run's first unit
-    auto part_of = [&](int i) { return parts + run_in_row(p, i).j0; };
-    auto load_entries = [&](const Partial* pp, float (&ev)[kMaxK], int (&ei)[kMaxK]) {
-#pragma unroll
-        for (int q = 0; q < kMaxK / 4; ++q)
-            if (q < KQ) {
-                const float4 a = __ldcg(reinterpret_cast<const float4*>(pp->v) + q);
-                const int4 b = __ldcg(reinterpret_cast<const int4*>(pp->id) + q);
-                ev[4 * q] = a.x; ev[4 * q + 1] = a.y; ev[4 * q + 2] = a.z; ev[4 * q + 3] = a.w;
-                ei[4 * q] = b.x; ei[4 * q + 1] = b.y; ei[4 * q + 2] = b.z; ei[4 * q + 3] = b.w;
-            }
-    };
-    // round 0 in registers
     float4 h0 = make_float4(-CUDART_INF_F, 0.0f, 0.0f, 0.0f);
     float ev0[kMaxK]; int ei0[kMaxK];
 #pragma unroll
     for (int e = 0; e < kMaxK; ++e) { ev0[e] = -CUDART_INF_F; ei0[e] = INT32_MAX; }
     if (lane < cnt) {
-        const Partial* pp = part_of(lane);
+        // partial i sits in the slot of its run's first unit
+        const Partial* pp = parts + run_in_row(p, lane).j0;
         h0 = __ldcg(reinterpret_cast<const float4*>(pp));
-        load_entries(pp, ev0, ei0);
+#pragma unroll
+        for (int q = 0; q < kMaxK / 4; ++q)
+            if (q < KQ) {
+                const float4 a = __ldcg(reinterpret_cast<const float4*>(pp->v) + q);
+                const int4 b = __ldcg(reinterpret_cast<const int4*>(pp->id) + q);
+                ev0[4 * q] = a.x; ev0[4 * q + 1] = a.y; ev0[4 * q + 2] = a.z; ev0[4 * q + 3] = a.w;
+                ei0[4 * q] = b.x; ei0[4 * q + 1] = b.y; ei0[4 * q + 2] = b.z; ei0[4 * q + 3] = b.w;
+            }
     }
     // ---- pass A: partition maxima and sums (text = 0, timestamps = 1)
     float am[2] = {-CUDART_INF_F, -CUDART_INF_F}, as[2] = {0.0f, 0.0f};
     bool nan_seen = false;
-    for (int r = 0; 32 * r < cnt; ++r) {
-        const int i = lane + 32 * r;
-        if (i < cnt) {
-            const float4 h = r == 0 ? h0 : __ldcg(reinterpret_cast<const float4*>(part_of(i)));
-            const int q = i < cT ? 0 : 1;
-            if (h.y != h.y) nan_seen = true;
-            else if (h.x > am[q]) { as[q] = as[q] * exp_diff(am[q], h.x) + h.y; am[q] = h.x; }
-            else as[q] += h.y * exp_diff(h.x, am[q]);
-        }
+    if (lane < cnt) {
+        const int q = lane < cT ? 0 : 1;
+        if (h0.y != h0.y) nan_seen = true;
+        else { as[q] = h0.y; am[q] = h0.x; }
     }
     float M[2], S[2];
 #pragma unroll
@@ -337,7 +469,7 @@ __device__ __forceinline__ RowOut merge_row(const StepParams& p, int row, unsign
     }
     nan_seen = __any_sync(0xffffffffu, nan_seen);
     RowOut r;
-    r.flags = rule_flags;
+    r.flags = 0u;
     if (nan_seen) r.flags |= 128u;
     float Tm = M[0], Ts = S[0];
     const float Sm = M[1], Ss = S[1];
@@ -350,82 +482,124 @@ __device__ __forceinline__ RowOut merge_row(const StepParams& p, int row, unsign
     const float tot = Ts * exp_diff(Tm, Mx) + Ss * exp_diff(Sm, Mx);
     const float logtot = nan_seen ? CUDART_NAN_F : logf(tot);
     if (Mx == -CUDART_INF_F) r.flags |= 128u;   // everything masked: the reference yields NaN log-probs
-    // ---- pass B: candidates of the surviving partitions (each partial's list is sorted: entry 0 is its maximum)
-    if (cnt <= 32) {
-        // the usual row: one partial per lane.  K rounds of "best head wins, its lane moves on to its next entry"
-        // (value desc, id asc; ids are unique across partials) -- a k-way merge of sorted lists, two warp reductions
-        // per output.  The lists wait in shared memory ([entry][lane]): a lane that wins reads its next head from there
-        float* lv = reinterpret_cast<float*>(lists);
-        int* li = reinterpret_cast<int*>(lists) + 32 * kMaxK;
-        int pn = (int)__float_as_int(h0.z);
-        const bool alive = lane < cnt && (lane >= cT || !ts_over_text);
-        pn = alive ? min(pn, K) : 0;
+#ifdef WRS_TRACE
+    r.t_sums = gtime(); r.t_cells = r.t_loaded = 0;
+#endif
+    // ---- pass B: the K best cells of the surviving partitions.  K rounds of "best head wins, its lane moves on to its
+    // next entry" (value desc, cell asc) -- a k-way merge of sorted lists, two warp reductions per round.  The lists wait in
+    // shared memory ([entry][lane]): a lane that wins reads its next head from there
+    float* lv = reinterpret_cast<float*>(lists);
+    int* li = reinterpret_cast<int*>(lists) + 32 * kMaxK;
+    int pn = (int)__float_as_int(h0.z);
+    const bool alive = lane < cnt && (lane >= cT || !ts_over_text);
+    pn = alive ? min(pn, K) : 0;
+    bool rescan = __any_sync(0xffffffffu, alive && __float_as_int(h0.w) != 0);
 #pragma unroll
-        for (int e = 1; e < kMaxK; ++e)
-            if (e < K) { lv[32 * e + lane] = ev0[e]; li[32 * e + lane] = ei0[e]; }
-        int taken = 0;
-        float hv = pn > 0 ? ev0[0] : -CUDART_INF_F;
-        int hi = pn > 0 ? ei0[0] : INT32_MAX;
-        float ov = -CUDART_INF_F; int oi = INT32_MAX;
-        for (int rnd = 0; rnd < K; ++rnd) {
-            const float m = warp_max(hv);
-            if (m == -CUDART_INF_F) break;
-            const int w = __reduce_min_sync(0xffffffffu, hv == m ? hi : INT32_MAX);
-            if (lane == rnd) { ov = m; oi = w; }
-            if (hv == m && hi == w) {
-                ++taken;
-                const bool more = taken < pn;
-                hv = more ? lv[32 * taken + lane] : -CUDART_INF_F;
-                hi = more ? li[32 * taken + lane] : INT32_MAX;
-            }
+    for (int e = 0; e < kMaxK; ++e)
+        if (e < K) { lv[32 * e + lane] = ev0[e]; li[32 * e + lane] = ei0[e]; }
+    int taken = 0;
+    float hv = pn > 0 ? ev0[0] : -CUDART_INF_F;
+    int hi = pn > 0 ? ei0[0] : INT32_MAX;
+    float vK = -CUDART_INF_F;                            // value of the K-th best cell (-inf: the row has fewer than K cells)
+    for (int rnd = 0; rnd < K; ++rnd) {
+        const float m = warp_max(hv);
+        if (m == -CUDART_INF_F) break;
+        const int w = __reduce_min_sync(0xffffffffu, hv == m ? hi : INT32_MAX);
+        if (rnd == K - 1) vK = m;
+        if (hv == m && hi == w) {
+            ++taken;
+            const bool more = taken < pn;
+            hv = more ? lv[32 * taken + lane] : -CUDART_INF_F;
+            hi = more ? li[32 * taken + lane] : INT32_MAX;
         }
-        r.tok = oi;
-        r.lp = (ov - Mx) - logtot;
-        return r;
     }
-    Run cand;
-    run_reset(cand);
-    for (int rr = 0; 32 * rr < cnt; ++rr) {
-        const int i = lane + 32 * rr;
-        float ev[kMaxK]; int ei[kMaxK];
+    // cells that tie the K-th one come along (a list that dropped such a cell has said so: `tie`)
+    while (taken < pn && lv[32 * taken + lane] == vK) ++taken;
+    int incl = taken;
 #pragma unroll
-        for (int e = 0; e < kMaxK; ++e) { ev[e] = ev0[e]; ei[e] = ei0[e]; }
-        int pn = (int)__float_as_int(h0.z);
-        if (rr > 0) {
-#pragma unroll
-            for (int e = 0; e < kMaxK; ++e) { ev[e] = -CUDART_INF_F; ei[e] = INT32_MAX; }
-            pn = 0;
-            if (i < cnt) {
-                const Partial* pp = part_of(i);
-                pn = __ldcg(&pp->n);
-                load_entries(pp, ev, ei);
-            }
-        }
-        const bool alive = i < cnt && (i >= cT || !ts_over_text);
-        pn = alive ? min(pn, K) : 0;
-#pragma unroll
-        for (int e = 0; e < kMaxK; ++e)
-            if (e >= pn) ev[e] = -CUDART_INF_F;
-        const float lmax = ev[0];
-        if (!__any_sync(0xffffffffu, lmax > -CUDART_INF_F)) continue;
-        const float tau = fmaxf(kth_threshold(lmax, K), __shfl_sync(0xffffffffu, cand.rv, K - 1));
-        if (lane == 0) wb.n = 0;
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    const int nG = __shfl_sync(0xffffffffu, incl, 31);
+    if (nG > 32) rescan = true;
+#ifdef WRS_TRACE
+    r.t_cells = gtime();
+#endif
+    float ov = -CUDART_INF_F; int oi = INT32_MAX;
+    if (!rescan) {
+        for (int t = 0; t < taken; ++t) glist[incl - taken + t] = li[32 * t + lane];
         __syncwarp();
-        if (lmax >= tau) {
+        // ---- the winning cells again, one per lane
+        const float* rp = p.logits + (int64_t)row * p.row_stride;
+        const bool have = lane < nG;
+        const int cid = have ? glist[lane] : 0;
+        int a0, lo, hi2;
+        unit_range(p, rp, rr, cid >> 5, a0, lo, hi2);
+        float x[kNV][4];
+        load_cell(p, rp, row, a0, cid & 31, lo, hi2, have, x);
+#ifdef WRS_TRACE
+        if (x[0][0] == 12345.678f) r.flags |= 0x40000000u;   // (wait for the loads)
+        r.t_loaded = gtime();
+#endif
+        const float bar = fmaxf(vK, -CUDART_MAX_NORMAL_F);   // x >= bar: at or above the K-th cell and not -inf
+        // the usual cell holds ONE id at or above the bar, its maximum: then the candidates stay in registers, one per lane
+        float pm[kNV];
+        int np = 0, jj = 0;
 #pragma unroll
-            for (int e = 0; e < kMaxK; ++e)
-                if (ev[e] >= tau && ev[e] > -CUDART_INF_F) {
-                    const int pos = atomicAdd(&wb.n, 1);
-                    if (pos < kCandCap - kMaxK) { wb.v[pos] = ev[e]; wb.id[pos] = ei[e]; }
+        for (int s = 0; s < kNV; ++s) {
+            pm[s] = fmaxf(fmaxf(x[s][0], x[s][1]), fmaxf(x[s][2], x[s][3]));
+            const bool hp = pm[s] >= bar;
+            np += hp ? 1 : 0; jj = hp ? s : jj;
+        }
+        float y[4] = {x[0][0], x[0][1], x[0][2], x[0][3]};
+#pragma unroll
+        for (int s = 1; s < kNV; ++s)
+            if (jj == s) { y[0] = x[s][0]; y[1] = x[s][1]; y[2] = x[s][2]; y[3] = x[s][3]; }
+        int ne = 0, ii = 0;
+#pragma unroll
+        for (int i = 3; i >= 0; --i) { const bool he = y[i] >= bar; ne += he ? 1 : 0; ii = he ? i : ii; }
+        float cv = -CUDART_INF_F; int ci = INT32_MAX;
+        if (np == 1 && ne == 1) { cv = y[0]; cv = ii == 1 ? y[1] : cv; cv = ii == 2 ? y[2] : cv; cv = ii == 3 ? y[3] : cv; ci = a0 + 4 * ((cid & 31) + 32 * jj) + ii; }
+        if (!__any_sync(0xffffffffu, np > 1 || ne > 1)) {
+            for (int rnd = 0; rnd < K; ++rnd) {
+                const float m = warp_max(cv);
+                if (m == -CUDART_INF_F) break;
+                const int w2 = __reduce_min_sync(0xffffffffu, cv == m ? ci : INT32_MAX);
+                if (cv == m && ci == w2) cv = -CUDART_INF_F;
+                if (lane == rnd) { ov = m; oi = w2; }
+            }
+        } else {
+            // several ids of a cell reach the bar: gather them all in shared memory
+            int c = 0;
+#pragma unroll
+            for (int s = 0; s < kNV; ++s)
+                if (pm[s] >= bar) {
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) c += x[s][i] >= bar ? 1 : 0;
                 }
+            int inc2 = c;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, inc2, o); if (lane >= o) inc2 += t; }
+            const int nE = __shfl_sync(0xffffffffu, inc2, 31);
+            if (nE > kCandCap) rescan = true;
+            else {
+                int w = inc2 - c;
+#pragma unroll
+                for (int s = 0; s < kNV; ++s)
+                    if (pm[s] >= bar) {
+#pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            if (x[s][i] >= bar) { wb.v[w] = x[s][i]; wb.id[w] = a0 + 4 * ((cid & 31) + 32 * s) + i; ++w; }
+                    }
+                __syncwarp();
+                bool dropped = false;
+                const int n = warp_compact(wb, nE, K, dropped);
+                if (lane < n) { ov = wb.v[lane]; oi = wb.id[lane]; }
+                __syncwarp();
+            }
         }
-        __syncwarp();
-        const int n_new = wb.n;
-        if (n_new <= kCandCap - kMaxK) run_merge(cand, wb, n_new, K);
-        else run_exact<kMaxK>(cand, K, [&](int e) { return ev[e]; }, [&](int e) { return ei[e]; });
     }
-    r.tok = cand.ri;
-    r.lp = (cand.rv - Mx) - logtot;
+    if (rescan) rescan_row(p, row, rr, ts_over_text, wb, ov, oi);
+    r.tok = oi;
+    r.lp = (ov - Mx) - logtot;
     return r;
 }
 
@@ -453,6 +627,7 @@ struct TailScratch {
 };
 static_assert(sizeof(TailScratch) <= kTailBytes, "tail scratch does not fit the per-warp slice");
 static_assert(sizeof(WarpBuf) <= kScanScratch, "candidate buffer does not fit the per-warp slice");
+static_assert(kTailLists + kScanScratch + 128 <= kTailBytes, "row merge tables do not fit the per-warp slice of the tail launch");
 
 // ---- MODE_BEAM tail: BeamSearchTokenExtractor::update for one audio (beam_search.rs:49-146), ONE warp ----
 __device__ __noinline__ void beam_tail_general(const StepParams& p, int audio, TailScratch& ts) {
@@ -925,7 +1100,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const Step
         if (g.hi > g.lo) {
             float x[kNV][4];
             fetch(stage, q, g, bmw, x);
-            reduce_unit(x, g, stage_of(stage), g.lo != g.a0 || g.hi != g.a0 + kUnit, p.K, wb, run);
+            fold_unit(x, q.j, p.K, wb, run);
         }
         __syncwarp();                                    // every lane has taken its share of the stage out
 #ifdef WRS_TRACE
@@ -940,7 +1115,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const Step
         run_finish(run, wb, p.K);
         Partial* out = p.partials + (int64_t)q.row * p.upr + q.j0;
         if (lane < kMaxK) { out->v[lane] = run.rv; out->id[lane] = run.ri; }
-        if (lane == 0) { out->m = run.m; out->s = run.s; out->n = run.n; }
+        if (lane == 0) { out->m = run.m; out->s = run.s; out->n = run.n; out->tie = run.tie ? 1 : 0; }
         run_reset(run);
     }
 
@@ -955,14 +1130,15 @@ __global__ void __launch_bounds__(kMaxBeam * 32) decode_tail_kernel(const StepPa
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     RowResult* rr_s = reinterpret_cast<RowResult*>(smem_raw);          // the group's row results
     FastTail& fs = *reinterpret_cast<FastTail*>(smem_raw + kTailRows);
-    unsigned char* slice = smem_raw + kTailHead + warp * kTailBytes;   // [merge lists / general tail tables | ...][scratch]
-    unsigned char* scratch = slice + kStageBytes;
-    WarpBuf& wb = *reinterpret_cast<WarpBuf*>(scratch);
+    unsigned char* slice = smem_raw + kTailHead + warp * kTailBytes;   // [merge lists | candidate buffer | winning cells]; the general beam tail's tables overlay it
+    WarpBuf& wb = *reinterpret_cast<WarpBuf*>(slice + kTailLists);
+    int* glist = reinterpret_cast<int*>(slice + kTailLists + kScanScratch);
     const int row = (int)blockIdx.x * (MODE == MODE_BEAM ? p.beam : 1) + warp;
     const bool fast_tail = MODE == MODE_BEAM && p.beam * p.K <= 32;
 #ifdef WRS_TRACE
-    const int gw = row;
-    if (lane == 0) for (int q = 4; q < 8; ++q) g_trace[gw * 8 + q] = 0;
+    const int gw = 148 * kStepWarps + min(row, 1023);
+    if (lane == 0) for (int q = 0; q < 8; ++q) g_trace[gw * 8 + q] = 0;
+    WRS_TR(0);
     const unsigned long long tm0 = gtime();
 #endif
     // everything this row needs from memory is requested before the first use: its two newest tokens (rules), the
@@ -991,8 +1167,8 @@ __global__ void __launch_bounds__(kMaxBeam * 32) decode_tail_kernel(const StepPa
     }
     if (lane == 0) wb.n = 0;
     __syncwarp();
-    RowOut r = merge_row(p, row, 0u, wb, slice);
     const RowRules rr_row = row_rules_from(p.rc, tk_last, tk_pen, p.cur_len, p.sample_begin);
+    RowOut r = merge_row(p, row, rr_row, wb, slice, glist);
     r.flags |= rr_row.flags;
     unsigned same = 0u;
     if (MODE == MODE_BEAM) {
@@ -1011,7 +1187,8 @@ __global__ void __launch_bounds__(kMaxBeam * 32) decode_tail_kernel(const StepPa
         same = ~diff & ((1u << p.beam) - 1u) & ~((2u << bj) - 1u);
     }
 #ifdef WRS_TRACE
-    WRS_TR_ADD(4, gtime() - tm0); WRS_TR_ADD(5, 1);
+    WRS_TR_ADD(4, gtime() - tm0);
+    if (lane == 0) { g_trace[gw * 8 + 5] = r.t_sums - tm0; g_trace[gw * 8 + 6] = r.t_cells - tm0; g_trace[gw * 8 + 7] = r.t_loaded ? r.t_loaded - tm0 : 0; }
 #endif
     if (lane < p.K) {
         if (p.dbg_lp) p.dbg_lp[(int64_t)row * p.K + lane] = r.lp;
@@ -1035,15 +1212,14 @@ __global__ void __launch_bounds__(kMaxBeam * 32) decode_tail_kernel(const StepPa
 #ifdef WRS_TRACE
         const unsigned long long tt0 = gtime();
 #endif
+        WRS_TR(1);
         const FastCand c = beam_fast_rank_part(p, fs, rr_s, cand_sum, warp);
         __syncthreads();
         if (warp == 0) beam_fast_walk(p, (int)blockIdx.x, fs, c, have);
         __syncthreads();
         beam_fast_outputs(p, (int)blockIdx.x, fs, warp);
         if (warp == 0 && lane == 0) publish_finish(p, fs.arrived, (fs.have + fs.n_store >= p.max_cand) ? 1 : 0);
-#ifdef WRS_TRACE
-        WRS_TR_ADD(6, gtime() - tt0); WRS_TR_ADD(7, 1);
-#endif
+        WRS_TR(3);
         return;
     }
     if (warp != 0) return;
@@ -1140,9 +1316,9 @@ int launch_step(wrs_decoder* dec, StepParams p, cudaStream_t stream) {
         int rt = 1, rs = ns > 0 ? 1 : 0;
         for (int q = 1; q <= std::max(nt, ns); ++q) {
             const int a = (nt + q - 1) / q, b2 = ns > 0 ? (ns + q - 1) / q : 0;
-            if ((int64_t)(a + b2) * p.n_rows <= Wt) {
+            if ((int64_t)(a + b2) * p.n_rows <= Wt && a + b2 <= 32) {     // (the tail merges a row's runs one per lane)
                 rs = b2;
-                rt = (int)std::min<int64_t>(nt, std::max<int64_t>(a, Wt / p.n_rows - b2));   // spare warps shorten the text runs
+                rt = (int)std::min<int64_t>(nt, std::max<int64_t>(a, std::min<int64_t>(Wt / p.n_rows, 32) - b2));   // spare warps shorten the text runs
                 break;
             }
         }

@@ -22,9 +22,9 @@
 namespace wrs {
 
 #ifndef WRS_STEP_WARPS
-#define WRS_STEP_WARPS 16
+#define WRS_STEP_WARPS 24
 #endif
-constexpr int kStepWarps = WRS_STEP_WARPS;               // one CTA per SM: 16 warps, up to 128 registers per thread
+constexpr int kStepWarps = WRS_STEP_WARPS;               // one CTA per SM: 24 warps, up to 80 registers per thread
 constexpr int kStepThreads = kStepWarps * 32;
 constexpr int kNV = 7;                                   // float4 slots per lane per unit
 constexpr int kUnit = 32 * 4 * kNV;                      // 896 elements per unit, 16-byte aligned in memory
@@ -35,7 +35,7 @@ constexpr float kLog2e = 1.4426950408889634f;
 // what a warp leaves in global memory for one (row, partition) run
 struct __align__(16) Partial {
     float m, s;            // max and sum of exp(x - m) over the run's surviving ids (m = -inf, s = 0 if none)
-    int n, pad;            // valid entries of v/id
+    int n, tie;            // valid entries of v/id; tie != 0: an entry equal to v[n-1] was dropped
     float v[kMaxK];        // the run's best values, sorted (value desc, id asc), padded with -inf
     int id[kMaxK];
 };
@@ -112,7 +112,7 @@ __device__ __forceinline__ float kth_threshold(float lane_max, int K) {
 }
 
 // Rank-sort entries [0, n) of wb (n <= kCandCap) and keep the best min(n, K) in wb[0..): returns the new count.
-__device__ __forceinline__ int warp_compact(WarpBuf& wb, int n, int K) {
+__device__ __forceinline__ int warp_compact(WarpBuf& wb, int n, int K, bool& tie) {
     const int lane = threadIdx.x & 31;
     constexpr int kPer = kCandCap / 32;
     float mv[kPer]; int mi[kPer], rk[kPer];
@@ -131,6 +131,13 @@ __device__ __forceinline__ int warp_compact(WarpBuf& wb, int n, int K) {
     for (int q = 0; q < kPer; ++q)
         if (lane + 32 * q < n && rk[q] < K) { wb.v[rk[q]] = mv[q]; wb.id[rk[q]] = mi[q]; }
     __syncwarp();
+    if (n > K) {                                         // was an entry equal to the K-th value cut off?
+        const float vk = wb.v[K - 1];
+        bool t = false;
+#pragma unroll
+        for (int q = 0; q < kPer; ++q) t |= lane + 32 * q < n && rk[q] >= K && mv[q] == vk;
+        tie |= __any_sync(0xffffffffu, t);
+    }
     return min(n, K);
 }
 
@@ -150,11 +157,12 @@ __device__ __forceinline__ void warp_pick(float& bv, int& bi) {
 //   top-K:   lane r < n holds the run's r-th best candidate (rv, ri) in (value desc, id asc) order, other lanes hold
 //            (-inf, INT32_MAX); wb[0, np) holds gathered candidates not merged yet; tau is a value the run's K-th best
 //            is known to reach (-inf while unknown).
-struct Run { float ref, ls, lm, tau, rv, m, s; int ri, n, np; bool ref_set; };
+struct Run { float ref, ls, lm, tau, rv, m, s; int ri, n, np; bool ref_set, tie; };
+//   tie:     a candidate equal to the list's K-th value was dropped (the list is then not the whole story at that value)
 
 __device__ __forceinline__ void run_reset(Run& run) {
     run.ref = 0.0f; run.ls = 0.0f; run.lm = -CUDART_INF_F; run.tau = -CUDART_INF_F; run.ref_set = false;
-    run.m = -CUDART_INF_F; run.s = 0.0f; run.rv = -CUDART_INF_F; run.ri = INT32_MAX; run.n = 0; run.np = 0;
+    run.m = -CUDART_INF_F; run.s = 0.0f; run.rv = -CUDART_INF_F; run.ri = INT32_MAX; run.n = 0; run.np = 0; run.tie = false;
 }
 
 // Many candidates: rank-sort in shared memory (the old list is appended behind the new candidates).  Out of line and
@@ -163,7 +171,7 @@ __device__ __noinline__ Run run_merge_slow(Run run, WarpBuf& wb, int n_new, int 
     const int lane = threadIdx.x & 31;
     if (lane < run.n) { wb.v[n_new + lane] = run.rv; wb.id[n_new + lane] = run.ri; }
     __syncwarp();
-    const int n = warp_compact(wb, n_new + run.n, K);
+    const int n = warp_compact(wb, n_new + run.n, K, run.tie);
     run.rv = lane < n ? wb.v[lane] : -CUDART_INF_F; run.ri = lane < n ? wb.id[lane] : INT32_MAX; run.n = n;
     __syncwarp();
     return run;
@@ -179,15 +187,16 @@ __device__ __forceinline__ void run_merge(Run& run, WarpBuf& wb, int n_new, int 
             const int e = lane - K;
             cv = e < n_new ? wb.v[e] : -CUDART_INF_F; ci = e < n_new ? wb.id[e] : INT32_MAX;
         }
-        float nv = -CUDART_INF_F; int ni = INT32_MAX, cnt = 0;
+        float nv = -CUDART_INF_F, m = -CUDART_INF_F; int ni = INT32_MAX, cnt = 0;
         for (int r = 0; r < K; ++r) {
-            const float m = warp_max(cv);
+            m = warp_max(cv);
             if (m == -CUDART_INF_F) break;
             const int w = __reduce_min_sync(0xffffffffu, cv == m ? ci : INT32_MAX);
             if (cv == m && ci == w) cv = -CUDART_INF_F;
             if (lane == r) { nv = m; ni = w; }
             ++cnt;
         }
+        if (cnt == K && __any_sync(0xffffffffu, cv == m)) run.tie = true;   // (m > -inf here: extracted lanes hold -inf)
         run.rv = nv; run.ri = ni; run.n = cnt;
         __syncwarp();
         return;
