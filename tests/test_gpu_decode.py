@@ -99,6 +99,19 @@ def test_planted_ties_lowest_index_wins(step_kind):
     assert np.all(got["cand_token"][tied, 0] < got["cand_token"][tied, 1])
 
 
+@pytest.mark.parametrize("step_kind,quantum", [("mixed", 0.5), ("mixed", 4.0), ("second", 1.0), ("first", 2.0)])
+def test_quantised_logits_massive_ties(step_kind, quantum):
+    """Logits on a coarse grid: the best ids of a row tie exactly by the dozen (quantum 4: by the thousand), the best
+    cells of the scan tie too, and the row is read again by the tail (rescan_row).  Lowest ids must win, bit-exact."""
+    ids = C.MULTILINGUAL
+    case = synth.decode_case(ids, 3, 5, step_kind, seed=11, quantum=quantum)
+    want = od.decode_step_reference(case, ids)
+    got, _ = fused_step(ids, case)
+    assert_beam_parity(got, want, 5)
+    if step_kind != "first":
+        assert (got["cand_logprob"][:, 0] == got["cand_logprob"][:, 1]).any()
+
+
 @pytest.mark.parametrize("beam", [1, 2, 5, 8, 12])
 def test_beam_sizes(beam):
     ids = C.MULTILINGUAL

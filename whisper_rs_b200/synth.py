@@ -56,13 +56,14 @@ def suppress_list(ids: C.TokenIds, suppress_non_speech: bool = True, user=None):
 
 
 def decode_case(ids: C.TokenIds, n_audio: int, beam: int, step_kind: str, seed: int, prompt_len: int = 0,
-                hist_len: int = 6, planted_ties: bool = False, sigma: float = 3.0):
+                hist_len: int = 6, planted_ties: bool = False, sigma: float = 3.0, quantum: float = 0.0):
     """One decode step's inputs.
 
     step_kind:
       "first"  L == sample_begin (all beams of an audio share the prompt, sum_logprobs 0)
       "second" one sampled token per row (penultimate defaults to "timestamp")
       "mixed"  hist_len sampled tokens; rows cycle through the four (penult, last) in {text,ts}^2 cases
+    quantum > 0 rounds the logits to multiples of it: thousands of exact ties per row, also among the best ids.
     Returns a dict of numpy arrays + scalars; logits are f32 [R, V] contiguous.
     """
     rng = np.random.default_rng([seed, n_audio, beam, prompt_len])
@@ -101,6 +102,9 @@ def decode_case(ids: C.TokenIds, n_audio: int, beam: int, step_kind: str, seed: 
     offsets = np.array([-4.0, 0.0, 2.0, 6.0], dtype=np.float32)
     row_off = offsets[(np.arange(R) // 4) % 4]
     logits[:, ids.ts_begin:] += row_off[:, None]
+
+    if quantum > 0.0:
+        logits = (np.round(logits / np.float32(quantum)) * np.float32(quantum)).astype(np.float32)
 
     if planted_ties:
         # several exact ties for the row maximum, in both partitions; lowest index must win
