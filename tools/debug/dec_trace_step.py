@@ -15,7 +15,7 @@ tok = torch.from_numpy(case["tokens"]).cuda(); sums = torch.from_numpy(case["sum
 for b in range(8):
     step.step(tok, lg[b], sums)
 torch.cuda.synchronize()
-NW = 148 * 16
+NW = 148 * 24
 n = (NW + 1024) * 8
 buf = np.zeros(n, dtype=np.uint64)
 h = _lib.lib()

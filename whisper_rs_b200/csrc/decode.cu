@@ -1,17 +1,18 @@
-// K2: the fused per-step logit processing (filters + log-softmax + top-k + beam merge) for sm_100a, ONE launch,
-// no block-level barrier.
+// K2: the fused per-step logit processing (filters + log-softmax + top-k + beam merge) for sm_100a, two launches per
+// step, no host round trip.
 //
-//   decode_step_kernel<MODE>  persistent grid (<= one 512-thread CTA per SM).  The R x units_per_row units of the
-//       batch are dealt to the warps of the grid in contiguous runs (decode_scan.cuh: one read of the logits, masks
-//       as predicates, register double-buffering so the next unit is in flight while this one is reduced).  At the
-//       end of every (row, partition) run the warp leaves a Partial in global memory and arrives on the row's
-//       counter.  The LAST warp to arrive for a row merges the row (timestamp-vs-text rule on the partition sums,
-//       src/decode/filter/timestamp_tokens.rs:83-96, log-softmax of the K candidates), then
-//   MODE_BEAM    arrives on the audio's counter; the last row of an audio runs BeamSearchTokenExtractor::update's
-//                host loop (src/decode/extractor/beam_search.rs:49-146) on device, one warp
-//   MODE_GREEDY  runs GreedyTokenExtractor::update for the row (greedy.rs:24-50)
-//   MODE_FILTER  does the in-place fills of TimestampTokens::apply (LogitFilter::apply equivalents,
-//                src/decode/filter/*.rs)
+//   decode_scan_kernel        one CTA of 24 warps per SM.  Every row's units (decode_scan.cuh) are cut into runs that never
+//       cross the text / timestamp partition; a warp folds a run: bulk copies into its shared-memory stages, suppressed
+//       ids poked to -inf in the stage, rule ranges as register masks, then {max, sum exp, the K best CELLS} -- a cell is
+//       the 28 ids a lane holds of a unit, valued by their maximum (fold_unit).  One Partial per run; the logits are read
+//       once and never written.
+//   decode_tail_kernel<MODE>  one CTA per audio (MODE_BEAM) or row, one warp per row.  merge_row: partition sums,
+//       timestamp-vs-text rule (src/decode/filter/timestamp_tokens.rs:83-96), k-way merge of the runs' cell lists, the K
+//       winning cells read again from the logits (28 ids each), the K best ids and their log-softmax.  Then
+//   MODE_BEAM    BeamSearchTokenExtractor::update's host loop (src/decode/extractor/beam_search.rs:49-146) on device,
+//                spread over the audio's warps (beam <= 5) or on warp 0 (beam_tail_general)
+//   MODE_GREEDY  GreedyTokenExtractor::update for the row (greedy.rs:24-50)
+//   MODE_FILTER  the in-place fills of TimestampTokens::apply (LogitFilter::apply equivalents, src/decode/filter/*.rs)
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
@@ -57,7 +58,7 @@ constexpr int kMaxCandAudio = kMaxBeam * kMaxK;          // 240
 #endif
 constexpr int kStages = WRS_STAGES;                               // units a warp keeps in flight (bulk copies, one mbarrier each)
 constexpr int kStageBytes = kUnit * 4;                    // landing zone of one unit
-constexpr int kScratchBytes = 2688;                      // per-warp scratch behind stage 0 (WarpBuf, or the fast beam tail's tables)
+constexpr int kScratchBytes = 2688;                      // tail launch: rest of a warp's slice behind kStageBytes
 constexpr int kTailBytes = kStageBytes + kScratchBytes;  // per-warp slice of the tail launch
 constexpr int kTailLists = 2 * 4 * 32 * kMaxK;           // the row merge's cell lists, [entry][lane] values then ids
 constexpr int kScanScratch = 1056;                       // scan launch: per-warp scratch behind stage 0 (WarpBuf only)
@@ -129,18 +130,12 @@ __device__ __forceinline__ void poke_suppressed(float* st, uint32_t bmw, int wor
     }
 }
 
-// Fold one unit (already in registers, masked ids loaded as -inf) into the run.  `st` is the unit's stage (suppressed ids
-// poked, range masks not applied: `ragged` says whether the unit has any).
-__device__ __forceinline__ void reduce_unit(float (&x)[kNV][4], const Geom& g, const float4* st, bool ragged, int K, WarpBuf& wb,
-                                            Run& run) {
-    const int lane = threadIdx.x & 31;
-    // ---- 1. slot and lane maxima; exp-sum against the run's reference (no cross-lane traffic unless the reference moves)
-    float sm[kNV];
+// The statistics of one unit (already in registers, masked ids loaded as -inf) folded into the run: the lane maximum is
+// returned, the exp-sum goes against the run's reference (no cross-lane traffic unless the reference moves).
+__device__ __forceinline__ float fold_stats(float (&x)[kNV][4], Run& run) {
+    float tmax = fmaxf(fmaxf(x[0][0], x[0][1]), fmaxf(x[0][2], x[0][3]));
 #pragma unroll
-    for (int j = 0; j < kNV; ++j) sm[j] = fmaxf(fmaxf(x[j][0], x[j][1]), fmaxf(x[j][2], x[j][3]));
-    float tmax = sm[0];
-#pragma unroll
-    for (int j = 1; j < kNV; ++j) tmax = fmaxf(tmax, sm[j]);
+    for (int j = 1; j < kNV; ++j) tmax = fmaxf(tmax, fmaxf(fmaxf(x[j][0], x[j][1]), fmaxf(x[j][2], x[j][3])));
     run.lm = fmaxf(run.lm, tmax);
     // the reference lives in the log2 domain and is an INTEGER R = rint(max * log2 e): x * log2 e - R is then one fused
     // operation with one rounding of a small number (a rounded -ref * log2 e would shift every term of the run by the
@@ -153,101 +148,65 @@ __device__ __forceinline__ void reduce_unit(float (&x)[kNV][4], const Geom& g, c
             run.ref = R; run.ref_set = true;
         }
     }
-    {
-        // packed FP32 (FFMA2 / FADD2): the four sums of a lane run side by side; NaN inputs keep the sum NaN
-        const f32x2 l2e = pack2(kLog2e, kLog2e), nref = pack2(-run.ref, -run.ref);
-        f32x2 s01 = pack2(0.0f, 0.0f), s23 = s01;
+    // packed FP32 (FFMA2 / FADD2): the four sums of a lane run side by side; NaN inputs keep the sum NaN
+    const f32x2 l2e = pack2(kLog2e, kLog2e), nref = pack2(-run.ref, -run.ref);
+    f32x2 s01 = pack2(0.0f, 0.0f), s23 = s01;
 #pragma unroll
-        for (int j = 0; j < kNV; ++j) {
-            float a0, a1, a2, a3;
-            unpack2(fma_(pack2(x[j][0], x[j][1]), l2e, nref), a0, a1);
-            unpack2(fma_(pack2(x[j][2], x[j][3]), l2e, nref), a2, a3);
-            s01 = add_(s01, pack2(ex2(a0), ex2(a1)));
-            s23 = add_(s23, pack2(ex2(a2), ex2(a3)));
-        }
-        float t0, t1;
-        unpack2(add_(s01, s23), t0, t1);
-        run.ls += t0 + t1;
+    for (int j = 0; j < kNV; ++j) {
+        float a0, a1, a2, a3;
+        unpack2(fma_(pack2(x[j][0], x[j][1]), l2e, nref), a0, a1);
+        unpack2(fma_(pack2(x[j][2], x[j][3]), l2e, nref), a2, a3);
+        s01 = add_(s01, pack2(ex2(a0), ex2(a1)));
+        s23 = add_(s23, pack2(ex2(a2), ex2(a3)));
     }
-    // ---- 2. top-K: gather everything that reaches tau, a value the run's K-th best is known to reach
+    float t0, t1;
+    unpack2(add_(s01, s23), t0, t1);
+    run.ls += t0 + t1;
+    return tmax;
+}
+
+// Fold one unit into the run with a top-K list of IDS: what the tail's rescan_row uses when it reads a whole row again.
+__device__ __forceinline__ void reduce_unit(float (&x)[kNV][4], const Geom& g, int K, WarpBuf& wb, Run& run) {
+    const int lane = threadIdx.x & 31;
+    const float tmax = fold_stats(x, run);
+    // gather everything that reaches tau, a value the run's K-th best is known to reach
     if (run.tau == -CUDART_INF_F) run.tau = kth_threshold(tmax, K);      // at least K elements of this unit reach it
-    bool mine = tmax >= run.tau && tmax > -CUDART_INF_F;
-    unsigned hb = __ballot_sync(0xffffffffu, mine);
-    if (!hb) return;
-    if (run.np > 0 && run.np + __popc(hb) + K > 32) {
-        // the pending candidates would outgrow the one-entry-per-lane merge: merge them now (that also raises the bar)
-        run_merge(run, wb, run.np, K);
-        run.np = 0;
-        run.tau = fmaxf(run.tau, __shfl_sync(0xffffffffu, run.rv, K - 1));
-        mine = tmax >= run.tau && tmax > -CUDART_INF_F;
-        hb = __ballot_sync(0xffffffffu, mine);
-        if (!hb) return;
-    }
     const float tau = run.tau;
+    const bool mine = tmax >= tau && tmax > -CUDART_INF_F;
+    const unsigned hb = __ballot_sync(0xffffffffu, mine);
+    if (!hb) return;
     const int np0 = run.np;
-    // slot census: the usual lane of hb has ONE slot that reaches tau.  Then the slot is read back from the stage (the
-    // unit is still there, suppressed ids already -inf) and every lane of hb runs the same few instructions, whatever
-    // its slot; lanes with several slots, or a unit whose range masks live in registers only, take the general path
-    int jj = 0, ns = 0;
-#pragma unroll
-    for (int j = 0; j < kNV; ++j) { const bool h = sm[j] >= tau; ns += h ? 1 : 0; jj = h ? j : jj; }
-    const bool simple = !ragged && !__any_sync(0xffffffffu, mine && ns > 1);
-    float y[4]; bool h[4];
     int c = 0;
-    if (simple) {
-        const float4 v = st[lane + 32 * jj];
-        y[0] = v.x; y[1] = v.y; y[2] = v.z; y[3] = v.w;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) { h[i] = mine && y[i] >= tau && y[i] > -CUDART_INF_F; c += h[i] ? 1 : 0; }
-    } else if (mine) {
-        WRS_TR_CNT(6, 1);
+    if (mine) {
 #pragma unroll
         for (int j = 0; j < kNV; ++j)
-            if (sm[j] >= tau) {
 #pragma unroll
-                for (int i = 0; i < 4; ++i) c += (x[j][i] >= tau && x[j][i] > -CUDART_INF_F) ? 1 : 0;
-            }
+            for (int i = 0; i < 4; ++i) c += (x[j][i] >= tau && x[j][i] > -CUDART_INF_F) ? 1 : 0;
     }
-    // where the lane's elements go behind the pending ones
-    int pos, total;
-    if (!__any_sync(0xffffffffu, c > 1)) {                               // one element per lane of hb
-        pos = __popc(hb & ((1u << lane) - 1u)); total = __popc(hb);
-    } else {
-        int incl = c;
+    int incl = c;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
-        pos = incl - c; total = __shfl_sync(0xffffffffu, incl, 31);
-    }
-    const int n_tot = np0 + total;
+    for (int o = 1; o < 32; o <<= 1) { const int t = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= o) incl += t; }
+    const int n_tot = np0 + __shfl_sync(0xffffffffu, incl, 31);
     if (n_tot > kCandCap - kMaxK) {
         // massive ties: merge what was pending before this unit, then select exactly straight from the registers
-        WRS_TR_CNT(7, 1000000);
         run_merge(run, wb, np0, K);
         run_exact<4 * kNV>(run, K, [&](int e) { return x[e >> 2][e & 3]; },
                            [&](int e) { return g.a0 + 4 * (lane + 32 * (e >> 2)) + (e & 3); });
     } else {
-        int w = np0 + pos;
-        if (simple) {
-            const int id0 = g.a0 + 4 * (lane + 32 * jj);
-#pragma unroll
-            for (int i = 0; i < 4; ++i)
-                if (h[i]) { wb.v[w] = y[i]; wb.id[w] = id0 + i; ++w; }
-        } else if (mine) {
+        if (mine) {
+            int w = np0 + incl - c;
 #pragma unroll
             for (int j = 0; j < kNV; ++j)
-                if (sm[j] >= tau) {
 #pragma unroll
-                    for (int i = 0; i < 4; ++i)
-                        if (x[j][i] >= tau && x[j][i] > -CUDART_INF_F) {
-                            wb.v[w] = x[j][i]; wb.id[w] = g.a0 + 4 * (lane + 32 * j) + i; ++w;
-                        }
-                }
+                for (int i = 0; i < 4; ++i)
+                    if (x[j][i] >= tau && x[j][i] > -CUDART_INF_F) {
+                        wb.v[w] = x[j][i]; wb.id[w] = g.a0 + 4 * (lane + 32 * j) + i; ++w;
+                    }
         }
         __syncwarp();
         // once the list is full its K-th value is an exact bar and later units add only a few stragglers: those wait for a
-        // cheap register merge (list + pending <= 32 entries); the first unit of a run merges at once to set that bar
+        // cheap register merge (list + pending <= 32 entries); the first unit merges at once to set that bar
         if (run.n >= K && n_tot + K <= 32) { run.np = n_tot; return; }
-        WRS_TR_CNT(7, n_tot + K > 32 ? 1000 : 1);
         run_merge(run, wb, n_tot, K);
     }
     run.np = 0;
@@ -255,7 +214,7 @@ __device__ __forceinline__ void reduce_unit(float (&x)[kNV][4], const Geom& g, c
     __syncwarp();
 }
 
-// Fold one unit into the run, scan launch: statistics as in reduce_unit, but the top-K list holds CELLS, not ids.  A cell
+// Fold one unit into the run, scan launch: the top-K list holds CELLS, not ids.  A cell
 // is (unit, lane): the 28 ids a lane holds of a unit, valued by their maximum.  The K best elements of a row lie in its K
 // best cells (K cells at or above a value are K distinct elements at or above it), so the scan keeps the best cells only
 // -- one candidate per lane and unit, no per-element work -- and the tail reads the few winning cells again.  Cells
@@ -263,34 +222,7 @@ __device__ __forceinline__ void reduce_unit(float (&x)[kNV][4], const Geom& g, c
 // scans the row itself (exact ties between the best cells of a row: quantised logits, not real ones).
 __device__ __forceinline__ void fold_unit(float (&x)[kNV][4], int unit_in_row, int K, WarpBuf& wb, Run& run) {
     const int lane = threadIdx.x & 31;
-    float tmax = fmaxf(fmaxf(x[0][0], x[0][1]), fmaxf(x[0][2], x[0][3]));
-#pragma unroll
-    for (int j = 1; j < kNV; ++j) tmax = fmaxf(tmax, fmaxf(fmaxf(x[j][0], x[j][1]), fmaxf(x[j][2], x[j][3])));
-    run.lm = fmaxf(run.lm, tmax);
-    // exp-sum against the run's integer log2-domain reference (see reduce_unit)
-    if (!run.ref_set || __any_sync(0xffffffffu, fmaf(tmax, kLog2e, -run.ref) > 92.0f)) {
-        const float wm = warp_max(tmax);
-        if (wm > -CUDART_INF_F) {
-            const float R = rintf(wm * kLog2e);
-            if (run.ref_set) run.ls *= ex2(run.ref - R);
-            run.ref = R; run.ref_set = true;
-        }
-    }
-    {
-        const f32x2 l2e = pack2(kLog2e, kLog2e), nref = pack2(-run.ref, -run.ref);
-        f32x2 s01 = pack2(0.0f, 0.0f), s23 = s01;
-#pragma unroll
-        for (int j = 0; j < kNV; ++j) {
-            float a0, a1, a2, a3;
-            unpack2(fma_(pack2(x[j][0], x[j][1]), l2e, nref), a0, a1);
-            unpack2(fma_(pack2(x[j][2], x[j][3]), l2e, nref), a2, a3);
-            s01 = add_(s01, pack2(ex2(a0), ex2(a1)));
-            s23 = add_(s23, pack2(ex2(a2), ex2(a3)));
-        }
-        float t0, t1;
-        unpack2(add_(s01, s23), t0, t1);
-        run.ls += t0 + t1;
-    }
+    const float tmax = fold_stats(x, run);
     // the unit's cells that reach tau, a value the run's K-th best cell is known to reach
     if (run.tau == -CUDART_INF_F) run.tau = kth_threshold(tmax, K);
     bool hit = tmax >= run.tau && tmax > -CUDART_INF_F;
@@ -310,7 +242,9 @@ __device__ __forceinline__ void fold_unit(float (&x)[kNV][4], int unit_in_row, i
     }
     __syncwarp();
     const int n_tot = run.np + __popc(hb);
-    if (run.n >= K && n_tot + K <= 32) { run.np = n_tot; return; }
+    // the cells wait for one merge at the end of the run (tau, from the first unit, is a bar K of them reach); a long run
+    // merges whenever the next unit's cells might not fit a lane each, and that raises the bar
+    if (n_tot + K <= 32) { run.np = n_tot; return; }
     run_merge(run, wb, n_tot, K);
     run.np = 0;
     run.tau = fmaxf(run.tau, __shfl_sync(0xffffffffu, run.rv, K - 1));   // -inf while the list holds fewer than K
@@ -409,7 +343,7 @@ __device__ __noinline__ void rescan_row(const StepParams& p, int row, const RowR
         if (g.hi <= g.lo) continue;
         float x[kNV][4];
         load_cell(p, rp, row, g.a0, lane, g.lo, g.hi, true, x);
-        reduce_unit(x, g, nullptr, true, p.K, wb, cand);
+        reduce_unit(x, g, p.K, wb, cand);
     }
     run_finish(cand, wb, p.K);
     out_v = cand.rv; out_i = cand.ri;
@@ -972,7 +906,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const Step
     Walk wf = wi;                                         // the unit being folded
     // start the flight of the next unit not yet requested into the next stage: one bulk copy, completion by byte
     // count on the stage's mbarrier
-    int stage_issue = 0, in_flight = 0;
+    int stage_issue = 0;
     auto issue_next = [&]() {
         int c_lo, c_hi;
         walk_chunks(p, wi, c_lo, c_hi);
@@ -988,7 +922,6 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const Step
         }
         walk_step(p, wi, stride);
         stage_issue = stage_issue + 1 == kStages ? 0 : stage_issue + 1;
-        ++in_flight;
     };
     if (lane == 0) {
 #pragma unroll
@@ -1083,7 +1016,6 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const Step
         const unsigned long long tw0 = gtime();
 #endif
         mbar_wait(bars + stage, phase);                  // also when nothing survives: the stage is reused
-        --in_flight;
 #ifdef WRS_TRACE
         const unsigned long long tw1 = gtime();
         WRS_TR_ADD(4, tw1 - tw0);
@@ -1338,7 +1270,7 @@ int launch_step(wrs_decoder* dec, StepParams p, cudaStream_t stream) {
     WRS_CUDA(ctx, cudaGetLastError());
     if (only && only[0] == 's') return WRS_OK;
     const int rows_per_group = MODE == MODE_BEAM ? p.beam : 1;
-    // (programmatic dependent launch was measured and lost 3 us per step: the early tail CTAs only get in the scan's way)
+    // (programmatic dependent launch, measured twice: 2 us slower per step -- tail CTAs placed early only wait)
     decode_tail_kernel<MODE><<<p.n_rows / rows_per_group, rows_per_group * 32, (size_t)kTailHead + (size_t)rows_per_group * kTailBytes, stream>>>(p);
     WRS_CUDA(ctx, cudaGetLastError());
     return WRS_OK;

@@ -1,4 +1,4 @@
-// K2 building blocks: warp-autonomous, register-resident, single-read scan of logits rows.
+// K2 building blocks: warp-autonomous, single-read scan of logits rows.
 //
 // Replaces, per (segment, beam) row, the ATen calls of reference src/decode/filter/*.rs
 // (index_fill_, slice fill_, log_softmax, logsumexp, max) and src/decode/extractor/beam_search.rs:37,62-65
@@ -6,13 +6,14 @@
 //
 // A row is cut into UNITS of 896 elements that start on 16-byte boundaries of the row's memory (57 text units +
 // 2 timestamp units for V = 51865; a unit never straddles ts_begin, the first and last unit of a partition are
-// ragged).  A warp owns a contiguous run of units: the unit being reduced sits in registers (7 x 16 bytes per
-// lane) while the next one is in flight into the warp's shared-memory stage (cp.async); every unit is folded into
-// the run's {max, sum exp(x - ref), top-K}.  Top-K is threshold based: K rounds of redux.max over the lane maxima give
-// a value that at least K elements reach, so only the handful of elements at or above it are gathered
-// (shared memory, per warp) and rank-sorted.  No block-level barrier is used anywhere.
+// ragged).  A warp owns a run of consecutive units of one partition: the unit being reduced sits in registers (7 x 16
+// bytes per lane) while the next one is in flight into the warp's shared-memory stages (cp.async.bulk); every unit is
+// folded into the run's {max, sum exp(x - ref), top-K}.  Top-K is threshold based: K rounds of redux.max over the lane
+// maxima give a value that at least K candidates reach, so only the handful at or above it are gathered (shared
+// memory, per warp) and merged.  The scan launch ranks CELLS (a lane's 28 ids of a unit, decode.cu fold_unit); the
+// per-id form (reduce_unit) is what the tail falls back to when cells tie.  No block-level barrier in the scan.
 //
-// Ordering everywhere is (value desc, token id asc) -- north_star's "ties broken by lowest index".
+// Ordering everywhere is (value desc, id asc) -- north_star's "ties broken by lowest index".
 #pragma once
 
 #include <cuda_runtime.h>
@@ -32,7 +33,8 @@ constexpr int kMaxK = 16;                                // beam + 1 <= 16
 constexpr int kCandCap = 128;                            // gathered candidates per warp before the exact fallback
 constexpr float kLog2e = 1.4426950408889634f;
 
-// what a warp leaves in global memory for one (row, partition) run
+// what a warp leaves in global memory for one run of units; v / id list the run's best CELLS: value = the cell's
+// maximum, id = 32 * unit in row + lane
 struct __align__(16) Partial {
     float m, s;            // max and sum of exp(x - m) over the run's surviving ids (m = -inf, s = 0 if none)
     int n, tie;            // valid entries of v/id; tie != 0: an entry equal to v[n-1] was dropped
