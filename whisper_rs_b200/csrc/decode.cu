@@ -707,136 +707,127 @@ __device__ __forceinline__ void filter_tail(const StepParams& p, int row, const 
     if (lane == 0 && p.no_timestamps >= 0 && p.no_timestamps < V) rp[p.no_timestamps] = -CUDART_INF_F;
 }
 
-// ---- MODE_BEAM tail, k * (k + 1) <= 32 (beam <= 5): one candidate per lane, spread over the CTA's k warps.
-//   phase 1 (every warp, before the first barrier): row merge; the row's results and token prefix go to shared memory
-//   phase 2 (every warp): the candidate's score key; warp w counts how many of row w's candidates precede it
-//   phase 3 (warp 0): ranks, the walk of beam_search.rs:87-104, the selection tables, sums / sources / finished count
-//   phase 4 (warp r): token row r of the next step and finished sequence r are copied out
-constexpr int kFastBeam = 5;                        // k (k + 1) <= 32
+// ---- MODE_BEAM tail, k * (k + 1) <= 32 (beam <= 5): BeamSearchTokenExtractor::update (beam_search.rs:49-146) with one
+//      candidate per lane.  After the barrier behind the row merges EVERY warp of the audio sorts the candidates for
+//      itself (a 32-key bitonic network on shuffles: no tables, no further barrier), walks them, and writes the output row
+//      it stands for: token row r of the next step, finished sequence r, source and sum r.  Warp 0 also keeps the books
+//      (finished count, `completed`).
 struct FastTail {                                   // CTA-level tables (behind the row results in the tail's shared memory)
     long long tok_stage[256];                       // the audio's k token prefixes when k * cur_len <= 256
-    double sel_score[kMaxK], fin_sc[kMaxK];
-    int sel_src[kMaxK], sel_tok[kMaxK], fin_src[kMaxK];
-    int rank_part[kFastBeam][32];
-    int have, n_store, nf, arrived;
+    int have;                                       // finished sequences the audio already holds
 };
-
 static_assert(sizeof(FastTail) <= kTailHead - kTailRows, "fast tail tables do not fit the head of the tail launch's shared memory");
 
-// phase 2: lane c < k K is candidate (beam j = c / K, entry i = c % K).  Returns the lane's candidate and leaves this
-// warp's share of the ranks in fs.rank_part[warp]
-struct FastCand { double score; int tok, j; bool ok; unsigned fl; };
-__device__ __forceinline__ FastCand beam_fast_rank_part(const StepParams& p, FastTail& fs, const RowResult* rr_s, float sum, int warp) {
-    const int k = p.beam, K = p.K, n_c = k * K;
+__device__ __forceinline__ void beam_fast(const StepParams& p, int audio, const FastTail& fs, const RowResult* rr_s, float sum, int warp) {
+    const int k = p.beam, K = p.K, n_c = k * K, L = p.cur_len, L1 = L + 1;
     const int lane = threadIdx.x & 31;
+    const int row0 = audio * k;
     const bool valid = lane < n_c;
-    FastCand c;
-    c.j = valid ? lane / K : 0;
-    const int i = valid ? lane - c.j * K : 0;
-    const RowResult* rr = rr_s + c.j;
+    // ---- lane c < k K is candidate (beam j = c / K, entry i = c % K): score = f64(sum_logprobs[row]) + f64(logprob)   (:70-71)
+    const int j = valid ? lane / K : 0, i = valid ? lane - j * K : 0;
+    const RowResult* rr = rr_s + j;
     const float lp = rr->lp[i];
-    c.tok = rr->tok[i];
-    c.fl = rr->flags;
-    const unsigned same = rr->same;
-    // ---- score = f64(sum_logprobs[row]) + f64(logprob)   (beam_search.rs:70-71)
-    c.score = (double)sum + (double)lp;
+    const int tok = rr->tok[i];
+    const unsigned fl = rr->flags, same = rr->same;
+    const double score = (double)sum + (double)lp;
     // a later beam with the same prefix proposing the same token overwrites this map entry (:74-77)
     bool shadowed = false;
     if (__any_sync(0xffffffffu, valid && same != 0u)) {
         for (int j2 = 1; j2 < k; ++j2)
             for (int i2 = 0; i2 < K; ++i2) {
-                const int t2 = __shfl_sync(0xffffffffu, c.tok, j2 * K + i2);
-                if (j2 > c.j && ((same >> j2) & 1u) && t2 == c.tok) shadowed = true;
+                const int t2 = __shfl_sync(0xffffffffu, tok, j2 * K + i2);
+                if (j2 > j && ((same >> j2) & 1u) && t2 == tok) shadowed = true;
             }
     }
-    const int sh = (!valid || shadowed || c.tok == INT32_MAX) ? 1 : 0;
-    c.ok = valid && !sh;
-    // ---- rank by (score desc, source row asc, token asc) == (score desc, lane asc); shadowed entries go last
-    long long kb = __double_as_longlong(c.score);
-    kb = kb < 0 ? ~kb : (kb | (long long)0x8000000000000000ull);            // order-preserving: unsigned compare
-    const unsigned long long key = (unsigned long long)kb;
-    int part = 0;
+    const bool ok = valid && !shadowed && tok != INT32_MAX;
+    // ---- sort by (score desc, source row asc, token asc) == (score desc, lane asc); entries that are not ok go last.
+    // Order-preserving 64-bit image of the score (0 for "not ok": below the image of every double), the lane rides along
+    long long kb = __double_as_longlong(score);
+    kb = kb < 0 ? ~kb : (kb | (long long)0x8000000000000000ull);
+    unsigned hi = ok ? (unsigned)((unsigned long long)kb >> 32) : 0u, lo = ok ? (unsigned)kb : 0u;
+    int o = lane;
 #pragma unroll
-    for (int t = 0; t < kFastBeam + 1; ++t) {
-        const int d = min(warp * K + t, 31);
-        const unsigned long long kd = __shfl_sync(0xffffffffu, key, d);
-        const int shd = __shfl_sync(0xffffffffu, sh, d);
-        const bool before = shd != sh ? shd < sh : (kd != key ? kd > key : d < lane);
-        part += (t < K && before) ? 1 : 0;
-    }
-    fs.rank_part[warp][lane] = part;
-    return c;
-}
-
-// phase 3 (warp 0 only)
-__device__ __forceinline__ void beam_fast_walk(const StepParams& p, int audio, FastTail& fs, const FastCand& c, int have) {
-    const int k = p.beam;
-    const int lane = threadIdx.x & 31;
-    const int row0 = audio * k;
-    int rank = 0;
+    for (int size = 2; size <= 32; size <<= 1)
 #pragma unroll
-    for (int w = 0; w < kFastBeam; ++w)
-        if (w < k) rank += fs.rank_part[w][lane];
-    const bool nan_seen = __any_sync(0xffffffffu, lane < k * p.K && (c.fl & 128u));
-    // ---- walk (beam_search.rs:87-104): EOT-terminated -> finished, others kept until k are saved.  An entry is
-    //      visited iff fewer than k live entries precede it in sorted order.
-    const bool live = c.ok && c.tok != p.eot, fin = c.ok && c.tok == p.eot;
-    const unsigned below = (1u << rank) - 1u;
-    const unsigned live_sorted = __reduce_or_sync(0xffffffffu, live ? (1u << rank) : 0u);
+        for (int stride = size >> 1; stride > 0; stride >>= 1) {
+            const unsigned phi = __shfl_xor_sync(0xffffffffu, hi, stride), plo = __shfl_xor_sync(0xffffffffu, lo, stride);
+            const int po = __shfl_xor_sync(0xffffffffu, o, stride);
+            const bool mine_first = hi != phi ? hi > phi : (lo != plo ? lo > plo : o < po);
+            const bool want_first = ((lane & stride) == 0) == ((lane & size) == 0 || size == 32);
+            if (mine_first != want_first) { hi = phi; lo = plo; o = po; }
+        }
+    // lane r now holds the r-th entry of the sorted list: candidate o
+    const int s_tok = __shfl_sync(0xffffffffu, tok, o), s_j = __shfl_sync(0xffffffffu, j, o);
+    const bool s_ok = __shfl_sync(0xffffffffu, ok ? 1 : 0, o) != 0;
+    const long long sb = (long long)(((unsigned long long)hi << 32) | lo);
+    const double s_score = __longlong_as_double(sb < 0 ? (sb & 0x7fffffffffffffffll) : ~sb);
+    const bool nan_seen = __any_sync(0xffffffffu, valid && (fl & 128u));
+    // ---- walk (:87-104): EOT-terminated -> finished, others kept until k are saved.  An entry is visited iff fewer than
+    //      k live entries precede it in sorted order.
+    const bool live = s_ok && s_tok != p.eot, fin = s_ok && s_tok == p.eot;
+    const unsigned below = (1u << lane) - 1u;
+    const unsigned live_sorted = __ballot_sync(0xffffffffu, live);
     const int live_before = __popc(live_sorted & below);
     const bool visited = live_before < k;
-    const unsigned fin_sorted = __reduce_or_sync(0xffffffffu, (fin && visited) ? (1u << rank) : 0u);
-    const int fidx = __popc(fin_sorted & below);
+    const unsigned fin_sorted = __ballot_sync(0xffffffffu, fin && visited);
     const int nf = min(__popc(fin_sorted), kMaxBeam), saved = min(__popc(live_sorted), k);
-    if (live && visited) { fs.sel_src[live_before] = c.j; fs.sel_tok[live_before] = c.tok; fs.sel_score[live_before] = c.score; }
-    if (fin && visited && fidx < kMaxBeam) { fs.fin_src[fidx] = c.j; fs.fin_sc[fidx] = c.score; }
-    // fewer than k live candidates cannot happen with >= k+1 finite logits per row; keep the row count anyway
-    if (lane >= saved && lane < k) { fs.sel_src[lane] = 0; fs.sel_tok[lane] = p.eot; fs.sel_score[lane] = -CUDART_INF; }
     // finished store: append in descending score until round(patience*k) entries (:124-138)
-    have = __shfl_sync(0xffffffffu, have, 0);
+    const int have = fs.have;
     const int n_store = min(nf, max(0, p.max_cand - have));
     const int done = (have + n_store >= p.max_cand) ? 1 : 0;           // (:141-146)
-    if (lane == 0) {
-        fs.have = have; fs.n_store = n_store; fs.nf = nf;
+    int arrived = 0;
+    if (warp == 0 && lane == 0) {
         p.fin_n[audio] = have + n_store;
         if (p.dbg_fin_count) p.dbg_fin_count[audio] = nf;
         if (nan_seen) atomicAdd(&p.status->nan_rows, 1);
-        fs.arrived = publish_arrive(p, done);                           // its round trip overlaps the output stores
+        arrived = publish_arrive(p, done);                              // its round trip overlaps the output stores
     }
-    __syncwarp();
-    if (lane < k) {
-        if (p.dbg_fin_source) p.dbg_fin_source[audio * k + lane] = lane < nf ? row0 + fs.fin_src[lane] : -1;
-        if (p.dbg_fin_score) p.dbg_fin_score[audio * k + lane] = lane < nf ? fs.fin_sc[lane] : 0.0;
-        p.source_idx[row0 + lane] = row0 + fs.sel_src[lane];
-        p.sum_out[row0 + lane] = (float)fs.sel_score[lane];   // index_put_(.., score as f32) :91-95
+    if (warp == 0 && (p.dbg_fin_source || p.dbg_fin_score)) {
+        for (int r = 0; r < k; ++r) {
+            const unsigned fm = __ballot_sync(0xffffffffu, fin && visited && __popc(fin_sorted & below) == r);
+            const int fl2 = fm ? __ffs((int)fm) - 1 : 0;
+            const int fj = __shfl_sync(0xffffffffu, s_j, fl2);
+            const double fsr = __shfl_sync(0xffffffffu, s_score, fl2);
+            if (lane == 0) {
+                if (p.dbg_fin_source) p.dbg_fin_source[audio * k + r] = r < nf ? row0 + fj : -1;
+                if (p.dbg_fin_score) p.dbg_fin_score[audio * k + r] = r < nf ? fsr : 0.0;
+            }
+        }
     }
-}
-
-// phase 4 (warp r): next_tokens row r = source prefix + chosen token; finished sequence r = source prefix + EOT
-__device__ __forceinline__ void beam_fast_outputs(const StepParams& p, int audio, const FastTail& fs, int r) {
-    const int k = p.beam, L = p.cur_len, L1 = L + 1;
-    const int lane = threadIdx.x & 31;
-    const int row0 = audio * k;
     const bool staged = k * L <= 256;
+    // ---- output row r = warp: the r-th live entry visited (fewer than k live candidates cannot happen with >= k+1 finite
+    //      logits per row; keep the row anyway: source 0, EOT, -inf)
     {
-        const int src = fs.sel_src[r];
-        const long long tokv = (long long)fs.sel_tok[r];
+        const unsigned sm = __ballot_sync(0xffffffffu, live && visited && live_before == warp);
+        const int sl = sm ? __ffs((int)sm) - 1 : 0;
+        int src = __shfl_sync(0xffffffffu, s_j, sl), tk = __shfl_sync(0xffffffffu, s_tok, sl);
+        double sc = __shfl_sync(0xffffffffu, s_score, sl);
+        if (warp >= saved) { src = 0; tk = p.eot; sc = -CUDART_INF; }
         const int64_t* from = p.tokens + (int64_t)(row0 + src) * p.tok_stride;
-        int64_t* to = p.next_tokens + (int64_t)(row0 + r) * p.next_stride;
-        for (int t = lane; t < L1; t += 32) to[t] = t < L ? (staged ? fs.tok_stage[src * L + t] : from[t]) : tokv;
+        int64_t* to = p.next_tokens + (int64_t)(row0 + warp) * p.next_stride;
+        for (int t = lane; t < L1; t += 32) to[t] = t < L ? (staged ? fs.tok_stage[src * L + t] : from[t]) : (long long)tk;
+        if (lane == 0) {
+            p.source_idx[row0 + warp] = row0 + src;
+            p.sum_out[row0 + warp] = (float)sc;                         // index_put_(.., score as f32) :91-95
+        }
     }
-    if (r < fs.n_store) {
-        const int slot = fs.have + r, src = fs.fin_src[r];
+    // ---- finished sequence r = warp
+    if (warp < n_store) {
+        const unsigned fm = __ballot_sync(0xffffffffu, fin && visited && __popc(fin_sorted & below) == warp);
+        const int fl2 = __ffs((int)fm) - 1;
+        const int src = __shfl_sync(0xffffffffu, s_j, fl2);
+        const double sc = __shfl_sync(0xffffffffu, s_score, fl2);
+        const int slot = have + warp;
         const int64_t* from = p.tokens + (int64_t)(row0 + src) * p.tok_stride;
         int64_t* to = p.fin_tokens + ((int64_t)audio * p.max_cand + slot) * p.max_len;
         for (int t = lane; t < L1; t += 32) to[t] = t < L ? (staged ? fs.tok_stage[src * L + t] : from[t]) : (long long)p.eot;
         if (lane == 0) {
             p.fin_len[audio * p.max_cand + slot] = L1;
-            p.fin_score[audio * p.max_cand + slot] = fs.fin_sc[r];
+            p.fin_score[audio * p.max_cand + slot] = sc;
         }
     }
+    if (warp == 0 && lane == 0) publish_finish(p, arrived, done);
 }
-
 
 // ---- where the units of a warp's runs live.  A run's units are consecutive units of one partition of one row: the
 //      walker steps through them with one addition and recomputes everything else only when the next run begins
@@ -1094,7 +1085,7 @@ __global__ void __launch_bounds__(kMaxBeam * 32) decode_tail_kernel(const StepPa
         if (staged && lane + 32 < p.cur_len) pre_m1 = mine[lane + 32];
         if (fast_tail) {
             if (lane < p.beam * p.K) cand_sum = p.sum_in[rbase + lane / p.K];
-            if (warp == 0 && lane == 0) have = p.fin_n[blockIdx.x];
+            if (warp == 0 && lane == 0) have = p.fin_n[blockIdx.x];   // handed to the other warps through fs.have
         }
     }
     if (lane == 0) wb.n = 0;
@@ -1134,6 +1125,7 @@ __global__ void __launch_bounds__(kMaxBeam * 32) decode_tail_kernel(const StepPa
         if (lane < kMaxK) { res->lp[lane] = r.lp; res->tok[lane] = lane < p.K ? r.tok : INT32_MAX; }
         if (lane == 0) { res->flags = r.flags; res->same = same; }
     }
+    if (fast_tail && warp == 0 && lane == 0) fs.have = have;
     if (staged) {
         if (lane < p.cur_len) fs.tok_stage[warp * p.cur_len + lane] = pre_m;
         if (lane + 32 < p.cur_len) fs.tok_stage[warp * p.cur_len + lane + 32] = pre_m1;
@@ -1145,12 +1137,7 @@ __global__ void __launch_bounds__(kMaxBeam * 32) decode_tail_kernel(const StepPa
         const unsigned long long tt0 = gtime();
 #endif
         WRS_TR(1);
-        const FastCand c = beam_fast_rank_part(p, fs, rr_s, cand_sum, warp);
-        __syncthreads();
-        if (warp == 0) beam_fast_walk(p, (int)blockIdx.x, fs, c, have);
-        __syncthreads();
-        beam_fast_outputs(p, (int)blockIdx.x, fs, warp);
-        if (warp == 0 && lane == 0) publish_finish(p, fs.arrived, (fs.have + fs.n_store >= p.max_cand) ? 1 : 0);
+        beam_fast(p, (int)blockIdx.x, fs, rr_s, cand_sum, warp);
         WRS_TR(3);
         return;
     }
