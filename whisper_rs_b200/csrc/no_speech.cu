@@ -3,9 +3,11 @@
 // i.e. one softmax over the UNFILTERED row per row (the filters run afterwards on the same row), reduced to a single
 // probability.  HBM-bound: a row is read once (4 V bytes), one float per row is written.
 //
-// A CTA takes one eighth of a row into registers (coalesced 4-byte loads: rows are only 4-byte aligned when V is odd),
-// reduces it to {max, sum exp(x - max)} and leaves that pair; the last CTA of the row (self-resetting counter) folds the
-// eight pairs and writes exp(x[no_speech] - max) / sum.  avg_logprob (decode/mod.rs:389-397) is host arithmetic.
+// A CTA takes one eighth of a row into registers as 16-byte chunks that start on 16-byte boundaries of the row's memory
+// (rows are only 4-byte aligned when V is odd: the chunk in front of id 0 and the one around id V - 1 are read id by id),
+// every thread folds its <= 28 values into {max, sum exp(x - max)} on its own, pairs are combined by shuffles and one
+// shared-memory stage (ONE CTA barrier), and the last CTA of the row (self-resetting counter) folds the eight pairs and
+// writes exp(x[no_speech] - max) / sum.  avg_logprob (decode/mod.rs:389-397) is host arithmetic.
 #include <algorithm>
 #include <cmath>
 
@@ -18,67 +20,86 @@ struct wrs_decoder;
 namespace wrs {
 
 constexpr int kNsThreads = 256;
-constexpr int kNsSplit = 8;                              // CTAs per row
-constexpr int kNsPer = 32;                               // elements per thread: covers V <= 8 * 256 * 32 = 65 536
+constexpr int kNsSplit = 8;                              // CTAs per row, at most (the host picks 1..8 so that the grid is one wave if it can)
+constexpr int kNsVec = 8;                                // 16-byte chunks per thread: covers V <= 8 * 256 * 8 * 4 - 3
+constexpr float kNsLog2e = 1.4426950408889634f;
 
-__global__ void __launch_bounds__(kNsThreads) no_speech_kernel(const float* __restrict__ logits, int64_t row_stride, int n_vocab,
-                                                                int no_speech, float2* __restrict__ part, int* __restrict__ arrive,
-                                                                float* __restrict__ out) {
-    __shared__ float red[kNsThreads / 32];
-    __shared__ float bcast;
-    __shared__ int is_last;
-    const int row = blockIdx.x / kNsSplit, piece = blockIdx.x % kNsSplit;
-    const int per = (n_vocab + kNsSplit - 1) / kNsSplit, e0 = piece * per, e1 = min(n_vocab, e0 + per);
+__device__ __forceinline__ float ns_ex2(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+// {m, s} <- {m, s} (+) {m2, s2}: max and sum of exp(x - max) of the union; exp(-inf - -inf) counts as 0
+__device__ __forceinline__ void ns_combine(float& m, float& s, float m2, float s2) {
+    const float M = fmaxf(m, m2);
+    const float a = m == -CUDART_INF_F ? 0.0f : s * ns_ex2((m - M) * kNsLog2e);
+    const float b = m2 == -CUDART_INF_F ? 0.0f : s2 * ns_ex2((m2 - M) * kNsLog2e);
+    m = M; s = a + b;
+}
+
+__global__ void __launch_bounds__(kNsThreads) no_speech_kernel(const float* __restrict__ logits, int64_t row_stride, int n_rows,
+                                                                int n_vocab, int no_speech, int split, float2* __restrict__ part,
+                                                                int* __restrict__ arrive, float* __restrict__ out) {
+    __shared__ float2 red[kNsThreads / 32];
+    const int row = blockIdx.x / split, piece = blockIdx.x - row * split;
     const float* __restrict__ rp = logits + (int64_t)row * row_stride;
+    const int mis = (int)((reinterpret_cast<uintptr_t>(rp) >> 2) & 3);       // ids in front of id 0 in its 16-byte chunk
+    const int n_chunks = (n_vocab + mis + 3) >> 2;                            // chunk c holds ids 4c - mis .. 4c - mis + 3
+    const int per = (n_chunks + split - 1) / split, c0 = piece * per, c1 = min(n_chunks, c0 + per);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    float v[kNsPer];
+    float v[kNsVec][4];
+#pragma unroll
+    for (int k = 0; k < kNsVec; ++k) {
+        const int c = c0 + threadIdx.x + k * kNsThreads, e = 4 * c - mis;
+        if (c < c1 && e >= 0 && e + 3 < n_vocab) {
+            const float4 t = __ldcs(reinterpret_cast<const float4*>(rp + e));
+            v[k][0] = t.x; v[k][1] = t.y; v[k][2] = t.z; v[k][3] = t.w;
+        } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) v[k][i] = (c < c1 && e + i >= 0 && e + i < n_vocab) ? __ldcs(rp + e + i) : -CUDART_INF_F;
+        }
+    }
     float m = -CUDART_INF_F;
 #pragma unroll
-    for (int k = 0; k < kNsPer; ++k) {
-        const int e = e0 + threadIdx.x + k * kNsThreads;
-        v[k] = e < e1 ? __ldcs(rp + e) : -CUDART_INF_F;
-        m = fmaxf(m, v[k]);
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-    if (lane == 0) red[warp] = m;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        float b = red[0];
-        for (int w = 1; w < kNsThreads / 32; ++w) b = fmaxf(b, red[w]);
-        bcast = b;
-    }
-    __syncthreads();
-    const float bm = bcast;
+    for (int k = 0; k < kNsVec; ++k) m = fmaxf(m, fmaxf(fmaxf(v[k][0], v[k][1]), fmaxf(v[k][2], v[k][3])));
     float s = 0.0f;
-    if (bm > -CUDART_INF_F) {
+    if (m > -CUDART_INF_F) {
+        const float nm = -m * kNsLog2e;
+        float s0 = 0.0f, s1 = 0.0f;
 #pragma unroll
-        for (int k = 0; k < kNsPer; ++k) s += __expf(v[k] - bm);            // exp(-inf) = 0 for the padding; NaN stays NaN
+        for (int k = 0; k < kNsVec; ++k) {                                    // exp(-inf) = 0 for the padding; NaN stays NaN
+            s0 += ns_ex2(fmaf(v[k][0], kNsLog2e, nm)) + ns_ex2(fmaf(v[k][1], kNsLog2e, nm));
+            s1 += ns_ex2(fmaf(v[k][2], kNsLog2e, nm)) + ns_ex2(fmaf(v[k][3], kNsLog2e, nm));
+        }
+        s = s0 + s1;
     }
 #pragma unroll
-    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    for (int o = 16; o > 0; o >>= 1) ns_combine(m, s, __shfl_xor_sync(0xffffffffu, m, o), __shfl_xor_sync(0xffffffffu, s, o));
+    if (lane == 0) red[warp] = make_float2(m, s);
     __syncthreads();
-    if (lane == 0) red[warp] = s;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        float t = 0.0f;
-        for (int w = 0; w < kNsThreads / 32; ++w) t += red[w];
-        part[(int64_t)row * kNsSplit + piece] = make_float2(bm, t);
+    if (warp != 0) return;
+    {
+        float2 q = lane < kNsThreads / 32 ? red[lane] : make_float2(-CUDART_INF_F, 0.0f);
+        m = q.x; s = q.y;
+#pragma unroll
+        for (int o = 4; o > 0; o >>= 1) ns_combine(m, s, __shfl_xor_sync(0xffffffffu, m, o), __shfl_xor_sync(0xffffffffu, s, o));
+    }
+    int last = 0;
+    if (lane == 0) {
+        part[(int64_t)row * kNsSplit + piece] = make_float2(m, s);
         __threadfence();
         const int prev = atomicAdd(arrive + row, 1);
-        is_last = prev == kNsSplit - 1;
-        if (is_last) { arrive[row] = 0; __threadfence(); }                   // self-reset for the next launch
+        last = prev == split - 1;
+        if (last) { arrive[row] = 0; __threadfence(); }                      // self-reset for the next launch
     }
-    __syncthreads();
-    if (!is_last || threadIdx.x != 0) return;
-    float M = -CUDART_INF_F;
-    float2 q[kNsSplit];
+    last = __shfl_sync(0xffffffffu, last, 0);
+    if (!last) return;
+    // the row's last CTA: lane i folds pair i
+    float2 q = lane < split ? __ldcg(part + (int64_t)row * kNsSplit + lane) : make_float2(-CUDART_INF_F, 0.0f);
+    float M = q.x, S = q.y;
 #pragma unroll
-    for (int i = 0; i < kNsSplit; ++i) { q[i] = __ldcg(part + (int64_t)row * kNsSplit + i); M = fmaxf(M, q[i].x); }
-    float S = 0.0f;
-#pragma unroll
-    for (int i = 0; i < kNsSplit; ++i) S += q[i].x == -CUDART_INF_F ? 0.0f : q[i].y * expf(q[i].x - M);
-    out[row] = expf(rp[no_speech] - M) / S;
+    for (int o = 4; o > 0; o >>= 1) ns_combine(M, S, __shfl_xor_sync(0xffffffffu, M, o), __shfl_xor_sync(0xffffffffu, S, o));
+    if (lane == 0) out[row] = expf(rp[no_speech] - M) / S;
 }
 
 }  // namespace wrs
@@ -103,10 +124,16 @@ int wrs_no_speech_probs(wrs_decoder* dec, const float* logits, int64_t row_strid
     if (n_rows < 0 || n_rows > max_rows || row_stride < n_vocab)
         return fail(ctx, WRS_ERR_INVALID, "wrs_no_speech_probs: need 0 <= n_rows <= max_rows and row_stride >= n_vocab");
     if (no_speech < 0 || no_speech >= n_vocab) return fail(ctx, WRS_ERR_INVALID, "wrs_no_speech_probs: cfg.no_speech is not a token id");
-    if (n_vocab > kNsSplit * kNsThreads * kNsPer) return fail(ctx, WRS_ERR_UNSUPPORTED, "wrs_no_speech_probs: vocabulary above 65536");
+    if (n_vocab > kNsSplit * kNsThreads * kNsVec * 4 - 64) return fail(ctx, WRS_ERR_UNSUPPORTED, "wrs_no_speech_probs: vocabulary above 65472");
     WRS_CUDA(ctx, cudaSetDevice(ctx->device));
-    no_speech_kernel<<<(unsigned)(n_rows * kNsSplit), kNsThreads, 0, (cudaStream_t)stream>>>(
-        logits, row_stride, n_vocab, no_speech, static_cast<float2*>(pairs), counters, out_probs);
+    // pieces per row: enough for a piece to fit the threads' registers, and the most that still makes the grid one wave
+    // of resident CTAs (8 per SM at 40 registers x 256 threads)
+    const int chunks = (n_vocab + 3 + 3) / 4, min_split = (chunks + kNsThreads * kNsVec - 1) / (kNsThreads * kNsVec);
+    int split = kNsSplit;
+    const int64_t resident = (int64_t)ctx->sm_count * 8;
+    if (n_rows * split > resident && n_rows * min_split <= resident) split = (int)std::max<int64_t>(min_split, resident / n_rows);
+    no_speech_kernel<<<(unsigned)(n_rows * split), kNsThreads, 0, (cudaStream_t)stream>>>(
+        logits, row_stride, (int)n_rows, n_vocab, no_speech, split, static_cast<float2*>(pairs), counters, out_probs);
     WRS_CUDA(ctx, cudaGetLastError());
     return WRS_OK;
 }
