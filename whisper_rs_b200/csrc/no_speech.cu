@@ -20,7 +20,7 @@ struct wrs_decoder;
 namespace wrs {
 
 constexpr int kNsThreads = 256;
-constexpr int kNsSplit = 8;                              // CTAs per row, at most (the host picks 1..8 so that the grid is one wave if it can)
+constexpr int kNsSplit = 8;                              // CTAs per row (4, 16, 32 and a one-wave 7 were measured: slower)
 constexpr int kNsVec = 8;                                // 16-byte chunks per thread: covers V <= 8 * 256 * 8 * 4 - 3
 constexpr float kNsLog2e = 1.4426950408889634f;
 
@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(kNsThreads) no_speech_kernel(const float* __re
     float2 q = lane < split ? __ldcg(part + (int64_t)row * kNsSplit + lane) : make_float2(-CUDART_INF_F, 0.0f);
     float M = q.x, S = q.y;
 #pragma unroll
-    for (int o = 4; o > 0; o >>= 1) ns_combine(M, S, __shfl_xor_sync(0xffffffffu, M, o), __shfl_xor_sync(0xffffffffu, S, o));
+    for (int o = 16; o > 0; o >>= 1) ns_combine(M, S, __shfl_xor_sync(0xffffffffu, M, o), __shfl_xor_sync(0xffffffffu, S, o));
     if (lane == 0) out[row] = expf(rp[no_speech] - M) / S;
 }
 
@@ -126,12 +126,7 @@ int wrs_no_speech_probs(wrs_decoder* dec, const float* logits, int64_t row_strid
     if (no_speech < 0 || no_speech >= n_vocab) return fail(ctx, WRS_ERR_INVALID, "wrs_no_speech_probs: cfg.no_speech is not a token id");
     if (n_vocab > kNsSplit * kNsThreads * kNsVec * 4 - 64) return fail(ctx, WRS_ERR_UNSUPPORTED, "wrs_no_speech_probs: vocabulary above 65472");
     WRS_CUDA(ctx, cudaSetDevice(ctx->device));
-    // pieces per row: enough for a piece to fit the threads' registers, and the most that still makes the grid one wave
-    // of resident CTAs (8 per SM at 40 registers x 256 threads)
-    const int chunks = (n_vocab + 3 + 3) / 4, min_split = (chunks + kNsThreads * kNsVec - 1) / (kNsThreads * kNsVec);
-    int split = kNsSplit;
-    const int64_t resident = (int64_t)ctx->sm_count * 8;
-    if (n_rows * split > resident && n_rows * min_split <= resident) split = (int)std::max<int64_t>(min_split, resident / n_rows);
+    const int split = kNsSplit;
     no_speech_kernel<<<(unsigned)(n_rows * split), kNsThreads, 0, (cudaStream_t)stream>>>(
         logits, row_stride, (int)n_rows, n_vocab, no_speech, split, static_cast<float2*>(pairs), counters, out_probs);
     WRS_CUDA(ctx, cudaGetLastError());
