@@ -253,12 +253,15 @@ def main():
     d_tokens = torch.from_numpy(case["tokens"]).to(dev)
     d_sums = torch.from_numpy(case["sum_logprobs"]).to(dev)
     Lcur = d_tokens.shape[1]
-    d_next = torch.empty(R, Lcur + 1, dtype=torch.int64, device=dev)
+    # what the host reads back every step (next tokens, sums, completed) sits in ONE device block: one D2H copy per step
+    nb_next, nb_sum = R * (Lcur + 1) * 8, R * 4
+    d_outs = torch.zeros(nb_next + nb_sum + 4, dtype=torch.uint8, device=dev)
+    h_outs = torch.zeros(nb_next + nb_sum + 4, dtype=torch.uint8).pin_memory()
+    d_next = d_outs[:nb_next].view(torch.int64).view(R, Lcur + 1)
+    d_sum_out = d_outs[nb_next:nb_next + nb_sum].view(torch.float32)
+    d_done = d_outs[nb_next + nb_sum:].view(torch.int32)
+    h_done = h_outs[nb_next + nb_sum:].view(torch.int32)
     d_src = torch.empty(R, dtype=torch.int32, device=dev)
-    d_sum_out = torch.empty(R, dtype=torch.float32, device=dev)
-    d_done = torch.zeros(1, dtype=torch.int32, device=dev)
-    h_next = torch.empty(R, Lcur + 1, dtype=torch.int64).pin_memory()
-    h_sum = torch.empty(R, dtype=torch.float32).pin_memory()
 
     def decode_call(logits):
         _lib.check(L.wrs_beam_step(dec.handle, logits.data_ptr(), logits.stride(0), R, d_tokens.data_ptr(), d_tokens.stride(0),
@@ -317,9 +320,9 @@ def main():
         if h2d_logits:
             lg.copy_(host_logits, non_blocking=True)
         decode_call(lg)
-        h_next.copy_(d_next, non_blocking=True)
-        h_sum.copy_(d_sum_out, non_blocking=True)
-        return bool(d_done.item())      # the `completed` read is the per-step sync in the reference loop too
+        h_outs.copy_(d_outs, non_blocking=True)
+        torch.cuda.current_stream(dev).synchronize()
+        return bool(h_done[0])          # the `completed` read is the per-step sync in the reference loop too
 
     e2e_dec = {}
     for name, h2d in (("device_logits", False), ("host_logits", True)):
