@@ -1251,8 +1251,13 @@ int launch_step(wrs_decoder* dec, StepParams p, cudaStream_t stream) {
         p.n_runs = (int)n_runs;
         p.rpr_magic = ((1ull << 40) + (uint64_t)p.rpr - 1) / (uint64_t)p.rpr;
     }
-    // investigation aid: WRS_DEBUG_ONLY=scan|tail times one launch alone (results are then meaningless)
+#ifdef WRS_TRACE
+    // investigation aid (trace builds only, tools/debug/split.sh): WRS_DEBUG_ONLY=scan|tail times one launch alone
+    // (results are then meaningless)
     static const char* only = std::getenv("WRS_DEBUG_ONLY");
+#else
+    const char* only = nullptr;
+#endif
     if (!only || only[0] != 't') decode_scan_kernel<<<grid, kStepThreads, smem, stream>>>(p);
     WRS_CUDA(ctx, cudaGetLastError());
     if (only && only[0] == 's') return WRS_OK;
