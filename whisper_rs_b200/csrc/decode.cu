@@ -286,11 +286,12 @@ __device__ __forceinline__ void load_cell(const StepParams& p, const float* __re
     // all loads first, without branches (a piece that is not wanted reads a harmless aligned address): one round trip
     float4 t[kNV]; uint32_t w0[kNV], w1[kNV]; bool need[kNV], inside[kNV];
     const float4* harmless = reinterpret_cast<const float4*>(p.partials);
+    const bool first_row = row == 0, last_row = row == p.n_rows - 1;
 #pragma unroll
     for (int s = 0; s < kNV; ++s) {
         const int e0 = a0 + 4 * (L + 32 * s);
         need[s] = active && e0 < hi && e0 + 3 >= lo;
-        inside[s] = !(row == 0 && e0 < 0) && !(row == p.n_rows - 1 && e0 + 3 >= p.rc.n_vocab);
+        inside[s] = !(first_row && e0 < 0) && !(last_row && e0 + 3 >= p.rc.n_vocab);
         t[s] = __ldcs((need[s] && inside[s]) ? reinterpret_cast<const float4*>(rp + e0) : harmless);
         w0[s] = __ldg(p.bm + min(max(e0, 0) >> 5, p.bm_words - 1));
         w1[s] = __ldg(p.bm + min(max(e0 + 3, 0) >> 5, p.bm_words - 1));
@@ -429,8 +430,10 @@ __device__ __forceinline__ RowOut merge_row(const StepParams& p, int row, const 
     pn = alive ? min(pn, K) : 0;
     bool rescan = __any_sync(0xffffffffu, alive && __float_as_int(h0.w) != 0);
 #pragma unroll
-    for (int e = 0; e < kMaxK; ++e)
-        if (e < K) { lv[32 * e + lane] = ev0[e]; li[32 * e + lane] = ei0[e]; }
+    for (int e = 0; e < kMaxK; ++e) {
+        if (e >= K) break;                               // (warp-uniform: K stores, not kMaxK predicated ones)
+        lv[32 * e + lane] = ev0[e]; li[32 * e + lane] = ei0[e];
+    }
     int taken = 0;
     float hv = pn > 0 ? ev0[0] : -CUDART_INF_F;
     int hi = pn > 0 ? ei0[0] : INT32_MAX;
