@@ -88,3 +88,15 @@ def test_tokenizer_constants_match_package():
         assert getattr(ids, k) == tk[k], k
     assert list(ids.non_speech_tokens) == tk["non_speech_tokens"]
     assert len(ids.non_speech_tokens) == 96 and len(set(ids.non_speech_tokens)) == 84
+
+
+def test_oracle_breaks_exact_ties_by_lowest_id():
+    """Quantised logits (synth quantum): many ids share the best values; the oracle's canonical order must list equal
+    log-probs by ascending id -- the bar the CUDA step is held to (tests/test_gpu_decode.py)."""
+    ids = C.MULTILINGUAL
+    case = synth.decode_case(ids, 1, 5, "mixed", seed=11, quantum=2.0)
+    want = od.decode_step_reference(case, ids)
+    lp, tok = want["cand_logprob"], want["cand_token"]
+    tied = lp[:, :-1] == lp[:, 1:]
+    assert tied.any()
+    assert np.all(tok[:, :-1][tied] < tok[:, 1:][tied])
