@@ -434,21 +434,20 @@ __device__ __forceinline__ RowOut merge_row(const StepParams& p, int row, const 
         if (e >= K) break;                               // (warp-uniform: K stores, not kMaxK predicated ones)
         lv[32 * e + lane] = ev0[e]; li[32 * e + lane] = ei0[e];
     }
-    int taken = 0;
+    // (cells of equal value all come along anyway, so a round needs no tie-break: every head at the round's maximum pops)
+    int taken = 0, got = 0;
     float hv = pn > 0 ? ev0[0] : -CUDART_INF_F;
-    int hi = pn > 0 ? ei0[0] : INT32_MAX;
     float vK = -CUDART_INF_F;                            // value of the K-th best cell (-inf: the row has fewer than K cells)
     for (int rnd = 0; rnd < K; ++rnd) {
         const float m = warp_max(hv);
         if (m == -CUDART_INF_F) break;
-        const int w = __reduce_min_sync(0xffffffffu, hv == m ? hi : INT32_MAX);
-        if (rnd == K - 1) vK = m;
-        if (hv == m && hi == w) {
+        const bool pop = hv == m;
+        got += __popc(__ballot_sync(0xffffffffu, pop));
+        if (pop) {
             ++taken;
-            const bool more = taken < pn;
-            hv = more ? lv[32 * taken + lane] : -CUDART_INF_F;
-            hi = more ? li[32 * taken + lane] : INT32_MAX;
+            hv = taken < pn ? lv[32 * taken + lane] : -CUDART_INF_F;
         }
+        if (got >= K) { vK = m; break; }
     }
     // cells that tie the K-th one come along (a list that dropped such a cell has said so: `tie`)
     while (taken < pn && lv[32 * taken + lane] == vK) ++taken;
