@@ -1239,7 +1239,7 @@ int launch_step(wrs_decoder* dec, StepParams p, cudaStream_t stream) {
             const int a = (nt + q - 1) / q, b2 = ns > 0 ? (ns + q - 1) / q : 0;
             if ((int64_t)(a + b2) * p.n_rows <= Wt && a + b2 <= 32) {     // (the tail merges a row's runs one per lane)
                 rs = b2;
-                rt = (int)std::min<int64_t>(nt, std::max<int64_t>(a, std::min<int64_t>(Wt / p.n_rows, 32) - b2));   // spare warps shorten the text runs
+                rt = a;      // the fewest runs of that length (more, shorter runs were measured: the per-run work costs more)
                 break;
             }
         }
