@@ -32,14 +32,14 @@ N_AUDIO, BEAM, VOCAB = 32, 5, 51865
 LOGMEL_BYTES_PER_SEG = N_SAMPLES * 4 + N_MELS * N_FRAMES * 4          # 2 880 000 B  
 DECODE_BYTES_PER_ROW = VOCAB * 4                                      # 207 460 B
 # dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed ncu --set full captures of this same
-# command (profiles/r1_v4_logmel_ncu.txt, profiles/r1_v7_decode_scan_ncu.txt, profiles/r1_v7_decode_tail_ncu.txt);
+# command (profiles/r1_v4_logmel_ncu.txt, profiles/r1_v8_decode_scan_ncu.txt, profiles/r1_v8_decode_tail_ncu.txt);
 # re-measure when a kernel's traffic changes
 LOGMEL_DRAM_TRAFFIC_PER_LAUNCH = 122.96e6 + 30.77e6                   # 64 segments: PCM read once, output half evicted
-# 160 rows: logits read once by the scan launch (33.24 MB) + the tail launch (1.55 MB under ncu's cold caches: partials and
+# 160 rows: logits read once by the scan launch (33.24 MB) + the tail launch (1.48 MB under ncu's cold caches: partials and
 # the ~6 winning 28-id cells per row it reads again; in a running step most of that is still in L2)
-DECODE_DRAM_TRAFFIC_PER_STEP = 33.24e6 + 1.55e6
+DECODE_DRAM_TRAFFIC_PER_STEP = 33.24e6 + 1.48e6
 TRAFFIC_SOURCE = ("ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch "
-                  "(profiles/r1_v4_logmel_ncu.txt, profiles/r1_v7_decode_*_ncu.txt)")
+                  "(profiles/r1_v4_logmel_ncu.txt, profiles/r1_v8_decode_*_ncu.txt)")
 
 
 def peaks():
