@@ -29,11 +29,14 @@ int main() {
             float v[25];
             for (int m = 0; m < 25; ++m) v[m] = xw[16 * m + t];
             wrs::cf y[13];
-            wrs::rdft25(v, y);
+            // even trials: plain outputs; odd trials: the form the kernel uses (four outputs left conjugated, the
+            // conjugation folded into the twiddle multiplication)
+            if (trial & 1) wrs::rdft25<true>(v, y); else wrs::rdft25(v, y);
             for (int q = 0; q < 13; ++q) {
                 double a = -2 * PI * (double)(t * q) / 400.0;
                 wrs::cf tw{(float)cos(a), (float)sin(a)};
-                yh[t][q] = (t == 0 || q == 0) ? y[q] : wrs::cmul(y[q], tw);
+                if ((trial & 1) && wrs::rdft25_conj_slot(q)) yh[t][q] = wrs::cmul_conj(y[q], tw);
+                else yh[t][q] = (t == 0 || q == 0) ? y[q] : wrs::cmul(y[q], tw);
             }
         }
         // stage B

@@ -52,24 +52,38 @@ void mel_filter_slaney(float* out) {
 }
 
 bool build_mel_bank(const float* dense, MelBank* bank) {
-    int total = 0, total4 = 0;
+    int total = 0, total2 = 0;
     for (int i = 0; i < MelBank::kMaxPadded; ++i) bank->wp[i] = 0.0f;
+    double cost[WRS_N_MELS], cost_sum = 0;
     for (int m = 0; m < WRS_N_MELS; ++m) {
         int lo = -1, hi = -1;
         for (int k = 0; k < WRS_N_BINS; ++k)
             if (dense[m * WRS_N_BINS + k] != 0.0f) { if (lo < 0) lo = k; hi = k; }
         if (lo < 0) { lo = 0; hi = -1; }
-        const int n = hi - lo + 1, n4 = std::max(4, (n + 3) & ~3);   // an empty row keeps four zero weights (K1 always takes a first step)
-        if (total + n > MelBank::kMaxWeights || total4 + n4 > MelBank::kMaxPadded) return false;
+        const int n = hi - lo + 1, n2 = std::max(2, (n + 1) & ~1);   // an empty row keeps two zero weights (K1 always takes a first step)
+        if (total + n > MelBank::kMaxWeights || total2 + n2 > MelBank::kMaxPadded) return false;
         bank->lo[m] = lo; bank->n[m] = n; bank->off[m] = total;
-        bank->n4[m] = n4; bank->off4[m] = total4;
+        bank->n2[m] = n2; bank->off2[m] = total2;
         for (int j = 0; j < n; ++j) {
             bank->w[total + j] = dense[m * WRS_N_BINS + lo + j];
-            bank->wp[total4 + j] = bank->w[total + j];
+            bank->wp[total2 + j] = bank->w[total + j];
         }
-        total += n; total4 += n4;
+        total += n; total2 += n2;
+        cost[m] = 22.0 + 2.5 * n2;                                    // issue slots of one mel row in stage C, roughly
+        cost_sum += cost[m];
     }
     bank->total = total;
+    // contiguous chunks of rows for the eight consumer warps; warps 5-7 did one stage-B item less (about 210 slots)
+    const double kItem = 210.0;
+    const double heavy = std::max(0.0, (cost_sum - 3 * kItem) / 8.0);
+    double edge = 0, run = 0;
+    int m = 0;
+    bank->row_begin[0] = 0;
+    for (int w = 0; w < 8; ++w) {
+        edge += heavy + (w >= 5 ? kItem : 0.0);
+        while (m < WRS_N_MELS && (w == 7 || run + 0.5 * cost[m] <= edge)) run += cost[m++];
+        bank->row_begin[w + 1] = m;
+    }
     return true;
 }
 
@@ -99,16 +113,21 @@ int wrs_ctx_create(int device, wrs_ctx** out) {
     if (device < 0 || device >= n) return wrs::fail(nullptr, WRS_ERR_INVALID, "wrs_ctx_create: bad device index");
     wrs_ctx* ctx = new wrs_ctx();
     ctx->device = device;
-    WRS_CUDA(ctx, cudaSetDevice(device));
-    cudaDeviceProp prop;
-    WRS_CUDA(ctx, cudaGetDeviceProperties(&prop, device));
-    ctx->sm_count = prop.multiProcessorCount;
-    WRS_CUDA(ctx, cudaMalloc(&ctx->d_bank, sizeof(wrs::MelBank)));
-    WRS_CUDA(ctx, cudaMalloc(&ctx->d_status, sizeof(wrs::DevStatus)));
-    WRS_CUDA(ctx, cudaMemset(ctx->d_status, 0, sizeof(wrs::DevStatus)));
-    WRS_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
-    int rc = wrs_logmel_set_filter(ctx, nullptr);
-    if (rc != WRS_OK) { std::string m = ctx->err; wrs_ctx_destroy(ctx); return wrs::fail(nullptr, rc, m); }
+    // any failure from here on: the message goes to the thread-local error (the caller never sees this ctx), and the
+    // half-built context is released
+    auto init = [&]() -> int {
+        WRS_CUDA(ctx, cudaSetDevice(device));
+        cudaDeviceProp prop;
+        WRS_CUDA(ctx, cudaGetDeviceProperties(&prop, device));
+        ctx->sm_count = prop.multiProcessorCount;
+        WRS_CUDA(ctx, cudaMalloc(&ctx->d_bank, sizeof(wrs::MelBank)));
+        WRS_CUDA(ctx, cudaMalloc(&ctx->d_status, sizeof(wrs::DevStatus)));
+        WRS_CUDA(ctx, cudaMemset(ctx->d_status, 0, sizeof(wrs::DevStatus)));
+        WRS_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
+        return wrs_logmel_set_filter(ctx, nullptr);
+    };
+    const int rc = init();
+    if (rc != WRS_OK) { const std::string m = ctx->err; wrs_ctx_destroy(ctx); return wrs::fail(nullptr, rc, m); }
     *out = ctx;
     return WRS_OK;
 }

@@ -1,21 +1,27 @@
 // K1: fused log-mel front-end for batches of audio segments (sm_100a).
 //
 // Replaces the ATen op sequence of reference src/audio.rs:230-259 (hann_window, stft, abs, pow, matmul,
-// clamp_min, log10, max, maximum, add, div) with one persistent kernel.  A CTA (16 warps) takes slices of 64
-// frames; every lane works on TWO frames held side by side in 64-bit register pairs, so the whole FFT runs on
-// Blackwell's packed FP32 instructions (FADD2 / FMUL2 / FFMA2: one issue slot, two frames):
+// clamp_min, log10, max, maximum, add, div) with one persistent, warp-specialised kernel.  A CTA (16 warps, one per
+// SM) takes tiles of 64 frames; every lane works on TWO frames held side by side in 64-bit register pairs, so the
+// FFT and the mel projection run on Blackwell's packed FP32 instructions (FADD2 / FMUL2 / FFMA2).
 //
-//   PCM (HBM) --bulk async copy--> smem tile, row-major [67 rows of 160 samples], pitch 164     (no registers, one
-//            mbarrier; issued by an idle warp as soon as stage A has released the tile, lands behind stages B and C)
-//   stage A  warp (g, tq), lane (f8, tl): frames 8g+f8 and 8g+f8+32, t = 4tq+tl:
-//            real 25-point DFT over the taps 16m+t, times W400^{tq}   -> smem Y[t][q][frame pair]  (float4: re2, im2)
-//            (8 frames x 4 consecutive taps per load = 32 distinct banks at pitch 164)
-//   stage B  warp q, lane = frame pair: complex 16-point DFT, |X|^2   -> smem P[bin][frame pair]   (float2)
-//            warp 14 issues the next slice's PCM copy; warp 15 posts the previous slice and polls the pending one
-//   stage C  warp w, lane = frame pair: 5 mel rows (banded FP32 FMA), log10 -> smem tile[mel][frame]
-//   slice end       : raw log-mel -> HBM, block max -> atomicMax per segment
-//   one slice later : the slice is counted as posted; once all slices of a segment have posted, its max is final
-//                     and floor (max-8), (x+4)/4 are applied in place on the slice's own 20 KB (still in L2)
+//   warps 0-7  "A"  : real 25-point DFTs (FMA-pipe bound).  A tile is two passes of 32 frames (16 frame pairs
+//                     (f, f+16)); pass h reads PCM half-tile buffer h (34 rows of 160 samples, pitch 164, filled by
+//                     bulk async copies that the A warps issue themselves two passes ahead), every lane takes the
+//                     taps 16m + t of its frame pair at compile-time offsets, multiplies by the Hann window
+//                     (src/audio.rs:233), runs the 25-point DFT and the twiddles W400^{tq}, and stores
+//                     Y[t][q][frame pair] (float4: re2, im2).
+//   warps 8-15 "BC" : complex 16-point DFTs over t, |X|^2 -> P[bin][frame pair]; then the banded mel projection
+//                     (src/audio.rs:252), clamp + log10 (:254), raw rows -> HBM, slice maximum (:256); plus the
+//                     deferred floor / scale (:256-258) of an earlier slice of this CTA (LSU / memory bound).
+//
+// The two roles meet only through mbarriers (Y full / Y empty, PCM full / PCM empty per buffer): A of tile k+1 runs
+// while BC works on tile k, so the FMA-bound and the LSU-bound halves of the algorithm share the SM's issue slots
+// instead of alternating behind CTA barriers.  BC warps keep one named barrier between their two stages.
+//
+//   slice end       : raw log-mel -> HBM, the slice's max key -> slice_max[segment][slice] (written once)
+//   one slice later : once all slices of a segment have posted, its max is final and floor (max-8), (x+4)/4 are
+//                     applied in place on the slice's own 20 KB (still in L2)
 #include <algorithm>
 #include <cmath>
 
@@ -26,15 +32,17 @@
 namespace wrs {
 
 constexpr int kThreads = 512;
-constexpr int kWarps = kThreads / 32;
-constexpr int kTW = 64;              // frames per slice (two per lane)
-constexpr int kRows = kTW + 3;       // 160-sample rows f0-2 .. f0+64 needed by 64 frames
+constexpr int kAWarps = 8;           // stage A (producers of Y)
+constexpr int kBWarps = 8;           // stages B and C (consumers)
+constexpr int kBThreads = kBWarps * 32;
+constexpr int kTW = 64;              // frames per tile (two per lane in stages B and C)
+constexpr int kHalf = 32;            // frames per stage-A pass
+constexpr int kHRows = kHalf + 2;    // rows of 160 samples a pass reads: frame i uses rows i .. i+2
 constexpr int kPitch = WRS_HOP_LENGTH + 4;   // words per tile row: 16-byte aligned rows, frame stride == 4 banks
 constexpr float kLog10Of2 = 0.30102999566398120f;
 constexpr int kSlotEmpty = (int)0x80808080;         // memset pattern; as a key it decodes to -3.4e38, never a log10 value
 
-struct TabEntry { int off; float win; };             // tap n of frame 0: word offset in the tile, periodic Hann weight
-__constant__ TabEntry c_tab[WRS_N_FFT];              // src/audio.rs:233
+__constant__ float c_win[WRS_N_FFT];                 // periodic Hann, src/audio.rs:233
 __constant__ float2 c_tw[16 * 13];                   // W400^{tq} = (cos, sin)(-2 pi t q / 400)
 
 struct LogmelParams {
@@ -57,19 +65,18 @@ struct LogmelParams {
 constexpr int kPRows = WRS_N_BINS + 3;               // 201 bins + rows the zero-padded band tails may touch
 
 struct LogmelSmem {
-    float pcm[kRows * kPitch];                       // 43 952 B
-    float4 Y[16 * 13 * 32];                          // 106 496 B
-    float2 P[kPRows * 32];                           // 52 224 B
-    float w[MelBank::kMaxPadded];                    // 3 072 B: in-band filter weights, bands zero-padded to multiples of 4
-    TabEntry tab[WRS_N_FFT];                         // 3 200 B
+    float4 Y[16 * 13 * 32];                          // 106 496 B  [t][q][frame pair]
+    float2 P[kPRows * 32];                           // 52 224 B   [bin][frame pair]
+    float pcm[2][kHRows * kPitch];                   // 44 608 B   half-tile buffers
+    float w[MelBank::kMaxPadded];                    // 3 072 B: in-band filter weights, bands zero-padded to even counts
+    int4 desc[WRS_N_MELS];                           // 1 280 B: {first bin, padded count, weight offset, 0} per mel row
+    float win[WRS_N_FFT];                            // 1 600 B
     float2 tw[16 * 13];                              // 1 664 B
-    int lo[WRS_N_MELS], n4[WRS_N_MELS], off4[WRS_N_MELS];
-    unsigned long long pcm_bar;                      // mbarrier: bytes of the PCM tile in flight
+    unsigned long long pcm_full[2], pcm_empty[2];    // mbarriers: half-tile buffer h filled / read by all A warps
+    unsigned long long y_full, y_empty;              // mbarriers: Y written by both passes / read by all BC warps
+    int row_begin[kBWarps + 1];                      // mel rows [row_begin[w], row_begin[w+1]) of BC warp w
     int red_max;                                     // max key of the slice in progress (reset by the last warp to add to it)
     int warps_done;
-#ifdef WRS_TRACE
-    long long t_arrive[4];                           // barrier-B arrival times of warps 5, 13, 15 (investigation aid)
-#endif
     int fin_ready;                                   // the oldest pending slice's segment is complete: seg_floor is valid
     float seg_floor;
 };
@@ -80,6 +87,19 @@ __device__ __forceinline__ int float_key(float f) {
     return b >= 0 ? b : b ^ 0x7fffffff;
 }
 __device__ __forceinline__ float key_float(int k) { return __int_as_float(k >= 0 ? k : k ^ 0x7fffffff); }
+// max that keeps a NaN (the reference's clamp_min / max / maximum all propagate it)
+__device__ __forceinline__ float fmax_nan(float a, float b) {
+    float r;
+    asm("max.NaN.f32 %0, %1, %2;" : "=f"(r) : "f"(a), "f"(b));
+    return r;
+}
+// log2 of a normal, positive number (the argument has been clamped to >= 1e-10): one MUFU, no denormal fix-up
+__device__ __forceinline__ float log2_pos(float a) {
+    float r;
+    asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
+    return r;
+}
+__device__ __forceinline__ float floor_scale(float x, float fl) { return (fmax_nan(x, fl) + 4.0f) * 0.25f; }
 
 // one sample of the (virtually reflect-padded) segment; i is relative to the segment start
 __device__ __forceinline__ float load_reflect(const float* __restrict__ seg, int i, int n) {
@@ -88,43 +108,40 @@ __device__ __forceinline__ float load_reflect(const float* __restrict__ seg, int
     return (i >= 0 && i < n) ? __ldg(seg + i) : 0.0f;
 }
 
-// The tile of slice (seg, fs) is rows fs-2 .. fs+64 of the segment cut into 160-sample rows.  Rows that lie entirely
-// inside the segment are one contiguous range of the input and move as bulk copies (16-byte aligned PCM); the rows
-// in front of the segment (reflection, first slice) and at or behind its end (last slice) are filled element-wise.
-struct TilePlan { int r_lo, r_hi; };                 // plain rows [r_lo, r_hi)
-__device__ __forceinline__ TilePlan tile_plan(const LogmelParams& p, int fs) {
-    TilePlan t;
-    t.r_lo = max(0, 2 - fs);
-    t.r_hi = p.vec_in != 0 ? max(t.r_lo, min(kRows, p.n_samples / WRS_HOP_LENGTH - fs + 2)) : t.r_lo;
-    return t;
-}
-// Row copies of 640 B, completion counted in bytes on the tile's mbarrier.  Two warps share the issue (part 0 also makes
-// the phase's single arrival and announces the byte count; a copy that completes before that only drives the pending
-// byte count negative for a moment).
-__device__ __forceinline__ void stage_bulk(LogmelSmem& sm, const LogmelParams& p, int seg, int fs, TilePlan t, int lane, int part) {
-    const float* __restrict__ src = p.pcm + (int64_t)seg * p.seg_stride + (int64_t)WRS_HOP_LENGTH * (fs - 2);
-    const int nb = t.r_hi - t.r_lo, half = (nb + 1) >> 1;
-    fence_proxy_async();                             // the tile was last touched by ordinary loads/stores
-    if (part == 0 && lane == 0) mbar_expect_tx(&sm.pcm_bar, (unsigned)(nb * WRS_HOP_LENGTH * sizeof(float)));
-    const int r0 = t.r_lo + part * half, r1 = min(t.r_hi, r0 + half);
-    // warp-uniform loop, one elected lane issues: the addresses stay in uniform registers (a per-lane loop would be
-    // serialised lane by lane through R2UR at about 80 cycles per copy)
-    if (elect_one()) {
-#pragma unroll 4
-        for (int r = r0; r < r1; ++r)
-            bulk_g2s(sm.pcm + r * kPitch, src + r * WRS_HOP_LENGTH, WRS_HOP_LENGTH * (unsigned)sizeof(float), &sm.pcm_bar);
-    }
-}
-// the rows outside [r_lo, r_hi): element-wise with reflection at both ends (src/audio.rs:236 center = true), whole CTA
-__device__ __forceinline__ void stage_general(LogmelSmem& sm, const LogmelParams& p, int seg, int fs, TilePlan t, int tid) {
+__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long* bar, unsigned bytes) { mbar_expect_tx(bar, bytes); }
+__device__ __forceinline__ void bar_bc() { asm volatile("bar.sync 1, %0;" ::"n"(kBThreads) : "memory"); }
+
+// Half-tile buffer `buf` <- rows f0 .. f0+33 of segment `seg` cut into 160-sample rows that start 200 samples before
+// the frame they are named after (row R = samples [160 R - 200, 160 R - 40) of the segment, so that frame f reads rows
+// f, f+1, f+2 and tap n sits at a compile-time offset).  A warp w of the eight takes rows w, w+8, ...: rows that lie
+// entirely inside the segment move as 640-byte bulk copies (16-byte aligned PCM), issued by one elected lane from
+// uniform registers; rows in front of the segment (reflection, src/audio.rs:236 center = true) and at or behind its end
+// are filled element-wise.  Every A warp arrives once on pcm_full[buf], announcing the bytes of its own copies.
+__device__ __forceinline__ void stage_half(LogmelSmem& sm, const LogmelParams& p, int seg, int f0, int buf, int aw, int lane) {
     const float* __restrict__ segp = p.pcm + (int64_t)seg * p.seg_stride;
-    const int base = WRS_HOP_LENGTH * (fs - 2);
-    const int n1 = t.r_lo * WRS_HOP_LENGTH, total = n1 + (kRows - t.r_hi) * WRS_HOP_LENGTH;
-#pragma unroll 4
-    for (int idx = tid; idx < total; idx += kThreads) {
-        const int e = idx < n1 ? idx : idx - n1 + t.r_hi * WRS_HOP_LENGTH;
-        const int r = e / WRS_HOP_LENGTH, c = e - r * WRS_HOP_LENGTH;
-        sm.pcm[r * kPitch + c] = load_reflect(segp, base + e, p.n_samples);
+    float* tile = sm.pcm[buf];
+    const int r_plain_hi = p.vec_in != 0 ? (p.n_samples + 40) / WRS_HOP_LENGTH : 0;      // rows R in [2, r_plain_hi] are plain
+    int nplain = 0;
+    for (int r = aw; r < kHRows; r += kAWarps) {
+        const int R = f0 + r;
+        if (R >= 2 && R <= r_plain_hi) { ++nplain; continue; }
+        const int base = WRS_HOP_LENGTH * R - 200;
+#pragma unroll
+        for (int e = 0; e < WRS_HOP_LENGTH / 32; ++e) tile[r * kPitch + lane + 32 * e] = load_reflect(segp, base + lane + 32 * e, p.n_samples);
+    }
+    __syncwarp();
+    if (elect_one()) {
+        if (nplain != 0) {
+            fence_proxy_async();                     // the buffer was last touched by ordinary loads / stores
+            mbar_arrive_expect_tx(&sm.pcm_full[buf], (unsigned)(nplain * WRS_HOP_LENGTH * sizeof(float)));
+            for (int r = aw; r < kHRows; r += kAWarps) {
+                const int R = f0 + r;
+                if (R >= 2 && R <= r_plain_hi)
+                    bulk_g2s(tile + r * kPitch, segp + (WRS_HOP_LENGTH * R - 200), WRS_HOP_LENGTH * (unsigned)sizeof(float), &sm.pcm_full[buf]);
+            }
+        } else {
+            mbar_arrive(&sm.pcm_full[buf]);
+        }
     }
 }
 
@@ -157,7 +174,7 @@ __device__ __forceinline__ int fold_slots(const LogmelParams& p, int seg, int a,
 template <int NT>
 __device__ __forceinline__ void floor_scale_slice(float* __restrict__ outp, int64_t n_frames, int nf, float fl, int t, bool vec) {
     if (vec) {
-        constexpr int kPer = (WRS_N_MELS * (kTW / 4) + NT - 1) / NT, kBatch = kPer < 7 ? kPer : 7;
+        constexpr int kPer = (WRS_N_MELS * (kTW / 4) + NT - 1) / NT, kBatch = kPer < 5 ? kPer : 5;
         const int nf4 = nf >> 2;
 #pragma unroll 1
         for (int k0 = 0; k0 < kPer; k0 += kBatch) {
@@ -173,8 +190,7 @@ __device__ __forceinline__ void floor_scale_slice(float* __restrict__ outp, int6
                 const int idx = t + (k0 + k) * NT;
                 if (idx < WRS_N_MELS * (kTW / 4) && (idx & 15) < nf4) {
                     float4 x = v[k];
-                    x.x = (fmaxf(x.x, fl) + 4.0f) * 0.25f; x.y = (fmaxf(x.y, fl) + 4.0f) * 0.25f;
-                    x.z = (fmaxf(x.z, fl) + 4.0f) * 0.25f; x.w = (fmaxf(x.w, fl) + 4.0f) * 0.25f;
+                    x.x = floor_scale(x.x, fl); x.y = floor_scale(x.y, fl); x.z = floor_scale(x.z, fl); x.w = floor_scale(x.w, fl);
                     *reinterpret_cast<float4*>(outp + (int64_t)(idx >> 4) * n_frames + 4 * (idx & 15)) = x;
                 }
             }
@@ -184,184 +200,202 @@ __device__ __forceinline__ void floor_scale_slice(float* __restrict__ outp, int6
         for (int idx = t; idx < WRS_N_MELS * nf; idx += NT) {
             const int m = idx / d, c = idx - m * d;
             float* q = outp + (int64_t)m * n_frames + c;
-            *q = (fmaxf(__ldcg(q), fl) + 4.0f) * 0.25f;
+            *q = floor_scale(__ldcg(q), fl);
         }
     }
 }
 
-// Blocking floor + scale of one slice in place: out = (max(raw, segmax - 8) + 4) / 4 (src/audio.rs:256-258).  Only the
-// drain at the end of the kernel (and a full pending queue) comes here; the steady state hides it inside the slice loop.
-__device__ __forceinline__ void finalize_slice_blocking(LogmelSmem& sm, const LogmelParams& p, int seg, int fs, int tid) {
+// Blocking floor + scale of one slice in place, by the eight BC warps (bt = 0..255).  Only the drain at the end of the
+// kernel (and a full pending queue) comes here; the steady state hides it inside the tile loop.
+__device__ __forceinline__ void finalize_slice_blocking(LogmelSmem& sm, const LogmelParams& p, int seg, int fs, int bt) {
     const int nf = min(kTW, p.n_frames - fs);
-    if (tid < 32) {
+    if (bt < 32) {
         // every slice of the segment is owned by a CTA that is running or has finished (persistent grid no larger than
         // what is co-resident; a CTA posts its slice before it ever waits), so this wait ends; the bound is a safety net
         const int* slots = p.slice_max + (int64_t)seg * p.slices_per_seg;
         int spins = 0, key;
         for (;;) {
-            const int a = tid < p.slices_per_seg ? ld_relaxed(slots + tid) : 0;
-            const int b = tid + 32 < p.slices_per_seg ? ld_relaxed(slots + tid + 32) : 0;
+            const int a = bt < p.slices_per_seg ? ld_relaxed(slots + bt) : 0;
+            const int b = bt + 32 < p.slices_per_seg ? ld_relaxed(slots + bt + 32) : 0;
             bool complete;
-            key = fold_slots(p, seg, a, b, tid, complete);
+            key = fold_slots(p, seg, a, b, bt, complete);
             if (complete) break;
             __nanosleep(64);
-            if (++spins > (1 << 22)) { if (tid == 0) atomicExch(&p.status->timeout, 1); break; }
+            if (++spins > (1 << 22)) { if (bt == 0) atomicExch(&p.status->timeout, 1); break; }
         }
-        if (tid == 0) sm.seg_floor = key_float(key) - 8.0f;
+        if (bt == 0) sm.seg_floor = key_float(key) - 8.0f;
     }
-    __syncthreads();
-    floor_scale_slice<kThreads>(p.out + ((int64_t)seg * WRS_N_MELS) * p.n_frames + fs, p.n_frames, nf, sm.seg_floor, tid, p.vec_out != 0);
-    __syncthreads();
+    bar_bc();
+    floor_scale_slice<kBThreads>(p.out + ((int64_t)seg * WRS_N_MELS) * p.n_frames + fs, p.n_frames, nf, sm.seg_floor, bt, p.vec_out != 0);
+    bar_bc();
 }
-
 
 constexpr int kPend = 4;              // slices a CTA may have waiting for their segment's maximum
 
-#ifdef WRS_TRACE
-// investigation aid (tools/debug/logmel_trace.py): per-CTA cycles spent in each phase of the slice loop
-__device__ unsigned long long g_lm_trace[148 * 12];
-#define LM_T(k) do { if (tid == 0) { const long long now_ = clock64(); acc_[k] += now_ - t_; t_ = now_; } } while (0)
-#else
-#define LM_T(k) do {} while (0)
-#endif
+// ---- stage A, one pass: lane (i8, tl) of A warp (g, tq) takes frames i and i+16 of the half-tile (i = 8g + i8) and the
+// taps 16m + t (t = 4tq + tl).  8 frames x 4 consecutive taps per load = 32 distinct banks at pitch 164.
+__device__ __forceinline__ void stage_a_pass(LogmelSmem& sm, const float* __restrict__ tile, float4* __restrict__ ydst,
+                                             const float* __restrict__ winp, const float2* __restrict__ twp,
+                                             unsigned long long* pcm_empty, unsigned long long* y_wait, unsigned y_parity, int lane) {
+    f32x2 v[25];
+#pragma unroll
+    for (int m = 0; m < 25; ++m) {
+        constexpr int kHi = 16 * kPitch;
+        const int off = (m / 10) * kPitch + 16 * (m % 10);           // tap n = 16m + t: row n / 160 = m / 10 (t < 16)
+        const float wv = winp[16 * m];
+        v[m] = mul_(pack2(tile[off], tile[off + kHi]), pack2(wv, wv));
+    }
+    cx<f32x2> y[13];
+    rdft25<true>(v, y);
+    // every tap has been consumed: the buffer may be refilled once all eight A warps say so
+    __syncwarp();
+    if (lane == 0) mbar_arrive(pcm_empty);
+    cx<f32x2> z[13];
+    z[0] = y[0];
+#pragma unroll
+    for (int q = 1; q < 13; ++q) {
+        const float2 w = twp[q];
+        const cx<f32x2> wq{pack2(w.x, w.x), pack2(w.y, w.y)};
+        z[q] = rdft25_conj_slot(q) ? cmul_conj(y[q], wq) : cmul(y[q], wq);
+    }
+    if (y_wait) mbar_wait(y_wait, y_parity);         // BC has read the previous tile's Y
+#pragma unroll
+    for (int q = 0; q < 13; ++q) {
+        float a, b, c, d;
+        unpack2(z[q].re, a, b); unpack2(z[q].im, c, d);
+        ydst[q * 32] = make_float4(a, b, c, d);
+    }
+}
+
+// ---- stage B, one item: q, lane = frame pair.  Complex 16-point DFT over t, |X|^2 -> P.
+__device__ __forceinline__ void stage_b_load(const LogmelSmem& sm, int q, int lane, cx<f32x2> (&z)[16]) {
+#pragma unroll
+    for (int t = 0; t < 16; ++t) {
+        const float4 a = sm.Y[(t * 13 + q) * 32 + lane];
+        z[t].re = pack2(a.x, a.y); z[t].im = pack2(a.z, a.w);
+    }
+    cdft16(z);
+}
+__device__ __forceinline__ void stage_b_store(LogmelSmem& sm, int q, int lane, const cx<f32x2> (&z)[16]) {
+    // bins q + 25 s for s < 8; s >= 8 gives the conjugates of bins 400 - q - 25 s (q = 0: bin 200 at s = 8, nothing beyond)
+    float2* lo = sm.P + q * 32 + lane;
+    float2* hi = sm.P + (400 - q) * 32 + lane;                             // hi[-25 s * 32] = bin 400 - q - 25 s
+#pragma unroll
+    for (int s = 0; s < 16; ++s) {
+        float a, b;
+        unpack2(power(z[s]), a, b);
+        if (s < 8) lo[25 * s * 32] = make_float2(a, b);
+        else if (q != 0) hi[-25 * s * 32] = make_float2(a, b);
+        else if (s == 8) lo[25 * s * 32] = make_float2(a, b);
+    }
+}
 
 template <bool FUSED>
 __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams p) {
-#ifdef WRS_TRACE
-    long long acc_[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0}, t_ = clock64();
-#endif
     extern __shared__ __align__(16) unsigned char smem_raw[];
     LogmelSmem& sm = *reinterpret_cast<LogmelSmem*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     // tables -> smem (once per CTA); the rows of P behind bin 200 stay zero (zero-padded band tails read them)
-    for (int i = tid; i < WRS_N_MELS; i += kThreads) { sm.lo[i] = p.bank->lo[i]; sm.n4[i] = p.bank->n4[i]; sm.off4[i] = p.bank->off4[i]; }
+    for (int i = tid; i < WRS_N_MELS; i += kThreads) sm.desc[i] = make_int4(p.bank->lo[i], p.bank->n2[i], p.bank->off2[i], 0);
     for (int i = tid; i < MelBank::kMaxPadded; i += kThreads) sm.w[i] = p.bank->wp[i];
-    for (int i = tid; i < WRS_N_FFT; i += kThreads) sm.tab[i] = c_tab[i];
+    for (int i = tid; i < WRS_N_FFT; i += kThreads) sm.win[i] = c_win[i];
     for (int i = tid; i < 16 * 13; i += kThreads) sm.tw[i] = c_tw[i];
     for (int i = tid; i < (kPRows - WRS_N_BINS) * 32; i += kThreads) sm.P[WRS_N_BINS * 32 + i] = make_float2(0.0f, 0.0f);
-    if (tid == 0) { mbar_init(&sm.pcm_bar, 1); sm.red_max = float_key(-INFINITY); sm.warps_done = 0; }
-    __syncthreads();
+    if (tid <= kBWarps) sm.row_begin[tid] = p.bank->row_begin[tid];
+    if (tid == 0) {
+        mbar_init(&sm.pcm_full[0], kAWarps); mbar_init(&sm.pcm_full[1], kAWarps);
+        mbar_init(&sm.pcm_empty[0], kAWarps); mbar_init(&sm.pcm_empty[1], kAWarps);
+        mbar_init(&sm.y_full, 2 * kAWarps); mbar_init(&sm.y_empty, kBWarps);
+        sm.red_max = float_key(-INFINITY); sm.warps_done = 0; sm.fin_ready = 0;
+    }
+    __syncthreads();                                     // the only CTA-wide barrier: the roles part here
 
-    // slices are dealt round-robin; (seg, fs) of the current slice advance without divisions
+    // tiles are dealt round-robin; (seg, sl) of the current tile advance without divisions
     const int step_seg = (int)gridDim.x / p.slices_per_seg, step_sl = (int)gridDim.x % p.slices_per_seg;
     int seg = (int)blockIdx.x / p.slices_per_seg, sl = (int)blockIdx.x % p.slices_per_seg;
+
+    if (warp < kAWarps) {
+        // =================================================== A warps
+        const int i = 8 * (warp & 1) + (lane & 7), t = 4 * (warp >> 1) + (lane >> 3);
+        const float* winp = sm.win + t;
+        const float2* twp = sm.tw + t * 13;
+        if ((int)blockIdx.x < p.total_slices) {
+            stage_half(sm, p, seg, sl * kTW, 0, warp, lane);
+            stage_half(sm, p, seg, sl * kTW + kHalf, 1, warp, lane);
+        }
+        unsigned k = 0;
+        for (int slice = blockIdx.x; slice < p.total_slices; slice += gridDim.x, ++k) {
+            int nseg = seg + step_seg, nsl = sl + step_sl;   // the tile after this one
+            if (nsl >= p.slices_per_seg) { nsl -= p.slices_per_seg; ++nseg; }
+            const bool has_next = slice + (int)gridDim.x < p.total_slices;
+#pragma unroll 1
+            for (int h = 0; h < 2; ++h) {
+                mbar_wait(&sm.pcm_full[h], k & 1u);
+                stage_a_pass(sm, sm.pcm[h] + i * kPitch + t, sm.Y + (t * 13) * 32 + 16 * h + i, winp, twp, &sm.pcm_empty[h],
+                             (h == 0 && k > 0) ? &sm.y_empty : nullptr, (k - 1u) & 1u, lane);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sm.y_full);
+                if (has_next) {
+                    mbar_wait(&sm.pcm_empty[h], k & 1u);     // all eight A warps have taken their taps of this pass
+                    stage_half(sm, p, nseg, nsl * kTW + kHalf * h, h, warp, lane);
+                }
+            }
+            seg = nseg; sl = nsl;
+        }
+        return;
+    }
+
+    // ======================================================= BC warps
+    const int bw = warp - kAWarps, bt = tid - kAWarps * 32;
     // slices whose floor/scale is still to be applied, oldest first (fs < 0: empty)
     int pend_seg[kPend], pend_fs[kPend];
 #pragma unroll
     for (int k = 0; k < kPend; ++k) { pend_seg[k] = 0; pend_fs[k] = -1; }
-    unsigned pcm_parity = 0;                             // phase of pcm_bar the next bulk-copied tile completes
-    bool cur_bulk = false;                               // the current slice's tile arrives through pcm_bar
-    const bool ovec = p.vec_out != 0;                    // output rows 16-byte aligned, n_frames % 4 == 0: rows move as bulk copies
-    if ((int)blockIdx.x < p.total_slices) {
-        const TilePlan t = tile_plan(p, sl * kTW);
-        cur_bulk = t.r_hi > t.r_lo;
-        if (cur_bulk && (warp == 13 || warp == 14)) stage_bulk(sm, p, seg, sl * kTW, t, lane, warp - 13);
-        stage_general(sm, p, seg, sl * kTW, t, tid);
-    }
-    __syncthreads();
-
-    for (int slice = blockIdx.x; slice < p.total_slices; slice += gridDim.x) {
-        const int fs = sl * kTW;                         // first frame of the slice
+    const bool ovec = p.vec_out != 0;                    // output rows 16-byte aligned, n_frames % 4 == 0
+    const int m_begin = sm.row_begin[bw], m_end = sm.row_begin[bw + 1];
+    // lane = frame pair: frames fl and fl + 16 of the tile
+    const int fl = 32 * (lane >> 4) + (lane & 15);
+    unsigned k = 0;
+    for (int slice = blockIdx.x; slice < p.total_slices; slice += gridDim.x, ++k) {
+        const int fs = sl * kTW;                         // first frame of the tile
         const int nf = min(kTW, p.n_frames - fs);
-        int nseg = seg + step_seg, nsl = sl + step_sl;   // the slice after this one
+        int nseg = seg + step_seg, nsl = sl + step_sl;
         if (nsl >= p.slices_per_seg) { nsl -= p.slices_per_seg; ++nseg; }
-        const bool has_next = slice + (int)gridDim.x < p.total_slices;
-        const TilePlan nplan = tile_plan(p, nsl * kTW);
-        const bool next_bulk = has_next && nplan.r_hi > nplan.r_lo;
-        const bool next_edge = has_next && nplan.r_hi - nplan.r_lo < kRows;
-        // has the oldest pending slice's segment completed?  The answer is asked for here and looked at in stage B, so
-        // that the round trip to L2 is off every warp's critical path.
+        // has the oldest pending slice's segment completed?  The answer is asked for here and looked at after stage B,
+        // so that the round trip to L2 is off every warp's critical path.
         int poll_a = 0, poll_b = 0;
-        if (FUSED && warp == 15 && pend_fs[0] >= 0) {
+        if (FUSED && bw == kBWarps - 1 && pend_fs[0] >= 0) {
             const int* slots = p.slice_max + (int64_t)pend_seg[0] * p.slices_per_seg;
             if (lane < p.slices_per_seg) poll_a = ld_relaxed(slots + lane);
             if (lane + 32 < p.slices_per_seg) poll_b = ld_relaxed(slots + lane + 32);
         }
-        LM_T(10);
-        if (cur_bulk) { mbar_wait(&sm.pcm_bar, pcm_parity); pcm_parity ^= 1u; }
-        LM_T(7);
+        mbar_wait(&sm.y_full, k & 1u);
 
-        // ---- stage A: 4 frame groups x 4 tap quads.  Lane (f8, tl): frames 8g+f8 and 8g+f8+32, taps 16m + 4tq + tl.
+        // ---- stage B: 13 items (q) over 8 warps: warps 0-4 take q and q + 8, warps 5-7 take one
         {
-            // opaque copy: keeps the compiler from hoisting this thread's 25 tap offsets / window values / twiddles out
-            // of the slice loop, where they would sit in registers (and spill) through stages B and C
-            int wv = warp;
-            asm volatile("" : "+r"(wv));
-            const int g = wv & 3, t = (wv >> 2) * 4 + (lane >> 3), fp = 8 * g + (lane & 7);
-            const float* src = sm.pcm + fp * kPitch;
-            f32x2 v[25];
-#pragma unroll
-            for (int m = 0; m < 25; ++m) {
-                const TabEntry e = sm.tab[16 * m + t];
-                v[m] = mul_(pack2(src[e.off], src[e.off + 32 * kPitch]), pack2(e.win, e.win));
-            }
-            cx<f32x2> y[13];
-            rdft25(v, y);
-            float4* dst = sm.Y + (t * 13) * 32 + fp;
-            {
-                float a, b, c, d;
-                unpack2(y[0].re, a, b); unpack2(y[0].im, c, d);
-                dst[0] = make_float4(a, b, c, d);
-            }
-#pragma unroll
-            for (int q = 1; q < 13; ++q) {
-                const float2 w = sm.tw[t * 13 + q];
-                const f32x2 wr = pack2(w.x, w.x), wi = pack2(w.y, w.y), nwi = pack2(-w.y, -w.y);
-                const f32x2 re = fma_(y[q].im, nwi, mul_(y[q].re, wr));
-                const f32x2 im = fma_(y[q].re, wi, mul_(y[q].im, wr));
-                float a, b, c, d;
-                unpack2(re, a, b); unpack2(im, c, d);
-                dst[q * 32] = make_float4(a, b, c, d);
-            }
-        }
-        __syncthreads();
-        LM_T(0);
-
-        // ---- stage B: warp = q < 13, lane = frame pair (lane, lane + 32).  The tile is free now: warp 14 starts the
-        //      next slice's copy.  One lane of warp 15 counts the previous slice as posted and asks whether the oldest
-        //      pending slice's segment has completed (all its slices have posted their maxima).
-        if (warp < 13) {
-            const int q = warp;
             cx<f32x2> z[16];
-#pragma unroll
-            for (int t = 0; t < 16; ++t) {
-                const float4 a = sm.Y[(t * 13 + q) * 32 + lane];
-                z[t].re = pack2(a.x, a.y); z[t].im = pack2(a.z, a.w);
-            }
-            cdft16(z);
-#pragma unroll
-            for (int s = 0; s < 16; ++s) {
-                if (q != 0 || s < 9) {
-                    float a, b;
-                    unpack2(power(z[s]), a, b);
-                    sm.P[stageb_bin(q, s) * 32 + lane] = make_float2(a, b);
-                }
-            }
-        } else {
-            // the three warps without a bin: 13 and 14 start the next slice's copy (the tile is free now); 15 folds the
-            // per-slice maxima it asked for at the top of the slice: is the oldest pending slice's segment complete?
-            if (warp < 15) {
-                if (next_bulk) stage_bulk(sm, p, nseg, nsl * kTW, nplan, lane, warp - 13);
-            } else if (FUSED) {
-                bool ready = false;
-                int key = 0;
-                if (pend_fs[0] >= 0) key = fold_slots(p, pend_seg[0], poll_a, poll_b, lane, ready);
-                if (lane == 0) {
-                    if (ready) sm.seg_floor = key_float(key) - 8.0f;
-                    sm.fin_ready = ready ? 1 : 0;
-                }
+            stage_b_load(sm, bw, lane, z);
+            if (bw >= 5) { __syncwarp(); if (lane == 0) mbar_arrive(&sm.y_empty); }
+            bar_bc();                                    // every BC warp has finished stage C of the previous tile: P is free
+            stage_b_store(sm, bw, lane, z);
+            if (bw < 5) {
+                stage_b_load(sm, bw + 8, lane, z);
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sm.y_empty);
+                stage_b_store(sm, bw + 8, lane, z);
             }
         }
-#ifdef WRS_TRACE
-        if (lane == 0 && (warp == 5 || warp == 13 || warp == 15)) sm.t_arrive[warp == 5 ? 0 : (warp == 13 ? 1 : 2)] = clock64();
-        const long long tB0_ = t_;
-#endif
-        __syncthreads();
-        LM_T(1);
-#ifdef WRS_TRACE
-        if (tid == 0) { acc_[9] += sm.t_arrive[0] - tB0_; acc_[11] += sm.t_arrive[1] - tB0_; acc_[8] += sm.t_arrive[2] - tB0_; }
-#endif
+        if (FUSED && bw == kBWarps - 1) {
+            bool ready = false;
+            int key = 0;
+            if (pend_fs[0] >= 0) key = fold_slots(p, pend_seg[0], poll_a, poll_b, lane, ready);
+            if (lane == 0) {
+                if (ready) sm.seg_floor = key_float(key) - 8.0f;
+                sm.fin_ready = ready ? 1 : 0;
+            }
+        }
+        bar_bc();                                        // P complete, fin_ready / seg_floor visible
 
         // ---- stage C: banded mel projection (src/audio.rs:252), clamp + log10 (:254), raw rows -> HBM
         const bool fin = FUSED && sm.fin_ready != 0;
@@ -369,130 +403,105 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
         const int fnf = fin ? min(kTW, p.n_frames - ffs) : 0;
         float* __restrict__ foutp = p.out + ((int64_t)fseg * WRS_N_MELS) * p.n_frames + ffs;
         // the pending slice whose floor has just become known: its raw rows come back from L2 behind the mel arithmetic
-        constexpr int kPer = (WRS_N_MELS * (kTW / 4) + kThreads - 1) / kThreads;   // float4 of a [80][64] slice per thread: 3
+        constexpr int kPer = (WRS_N_MELS * (kTW / 4) + kBThreads - 1) / kBThreads;   // float4 of a [80][64] slice per thread: 5
         const int fnf4 = fnf >> 2;
         float4 raw[kPer];
         if (fin && ovec) {
 #pragma unroll
-            for (int k = 0; k < kPer; ++k) {
-                const int idx = tid + k * kThreads;
-                if (idx < WRS_N_MELS * (kTW / 4) && (idx & 15) < fnf4)
-                    raw[k] = __ldcg(reinterpret_cast<const float4*>(foutp + (int64_t)(idx >> 4) * p.n_frames + 4 * (idx & 15)));
+            for (int j = 0; j < kPer; ++j) {
+                const int idx = bt + j * kBThreads;
+                if ((idx & 15) < fnf4)
+                    raw[j] = __ldcg(reinterpret_cast<const float4*>(foutp + (int64_t)(idx >> 4) * p.n_frames + 4 * (idx & 15)));
             }
-        }
-        LM_T(2);
-        if (next_edge) {
-            stage_general(sm, p, nseg, nsl * kTW, nplan, tid);
-
         }
         float lmax = -INFINITY;
-        float* __restrict__ outp = p.out + ((int64_t)seg * WRS_N_MELS) * p.n_frames + fs;
         {
-            const bool ok0 = lane < nf, ok1 = lane + 32 < nf;
-            // software pipeline over the warp's 5 rows: a row's band description and its first four bins are fetched
-            // while the previous row is still in its log / store tail (most bands are 1..8 bins wide, so a row is
-            // mostly latency otherwise)
-            int n4 = sm.n4[warp];
-            const float4* w = reinterpret_cast<const float4*>(sm.w + sm.off4[warp]);
-            const float2* pp = sm.P + sm.lo[warp] * 32 + lane;
-            float4 wa = w[0];
-            float2 p0 = pp[0], p1 = pp[32], p2 = pp[64], p3 = pp[96];
+            const bool ok0 = fl < nf, ok1 = fl + 16 < nf;
+            float* __restrict__ orow = p.out + ((int64_t)seg * WRS_N_MELS + m_begin) * p.n_frames + fs + fl;
+            int4 d = sm.desc[m_begin < WRS_N_MELS ? m_begin : 0];
 #pragma unroll 1
-            for (int i = 0; i < WRS_N_MELS / kWarps; ++i) {
-                const int m = i * kWarps + warp;
-                const int mn = min(m + kWarps, WRS_N_MELS - 1);      // next row (the last iteration re-reads its own)
-                const int n4n = sm.n4[mn];
-                const float4* wn = reinterpret_cast<const float4*>(sm.w + sm.off4[mn]);
-                const float2* ppn = sm.P + sm.lo[mn] * 32 + lane;
-                f32x2 acc0 = mul_(pack2(p0.x, p0.y), pack2(wa.x, wa.x));
-                f32x2 acc1 = mul_(pack2(p1.x, p1.y), pack2(wa.y, wa.y));
-                acc0 = fma_(pack2(p2.x, p2.y), pack2(wa.z, wa.z), acc0);
-                acc1 = fma_(pack2(p3.x, p3.y), pack2(wa.w, wa.w), acc1);
-                for (int j = 4; j < n4; j += 4) {
-                    const float4 wb = w[j >> 2];
-                    const float2 q0 = pp[j * 32], q1 = pp[j * 32 + 32], q2 = pp[j * 32 + 64], q3 = pp[j * 32 + 96];
-                    acc0 = fma_(pack2(q0.x, q0.y), pack2(wb.x, wb.x), acc0);
-                    acc1 = fma_(pack2(q1.x, q1.y), pack2(wb.y, wb.y), acc1);
-                    acc0 = fma_(pack2(q2.x, q2.y), pack2(wb.z, wb.z), acc0);
-                    acc1 = fma_(pack2(q3.x, q3.y), pack2(wb.w, wb.w), acc1);
+            for (int m = m_begin; m < m_end; ++m) {
+                const float2* pp = sm.P + d.x * 32 + lane;
+                const float2* wv = reinterpret_cast<const float2*>(sm.w + d.z);
+                const int n2 = d.y;
+                d = sm.desc[min(m + 1, WRS_N_MELS - 1)];     // the next row's description is fetched behind this row's bins
+                float2 w0 = wv[0];
+                float2 p0 = pp[0], p1 = pp[32];
+                f32x2 acc0 = mul_(pack2(p0.x, p0.y), pack2(w0.x, w0.x));
+                f32x2 acc1 = mul_(pack2(p1.x, p1.y), pack2(w0.y, w0.y));
+#pragma unroll 2
+                for (int j = 2; j < n2; j += 2) {
+                    const float2 wj = wv[j >> 1];
+                    const float2 q0 = pp[j * 32], q1 = pp[j * 32 + 32];
+                    acc0 = fma_(pack2(q0.x, q0.y), pack2(wj.x, wj.x), acc0);
+                    acc1 = fma_(pack2(q1.x, q1.y), pack2(wj.y, wj.y), acc1);
                 }
-                wa = wn[0];
-                p0 = ppn[0]; p1 = ppn[32]; p2 = ppn[64]; p3 = ppn[96];
-                n4 = n4n; w = wn; pp = ppn;
                 float a0, a1;
                 unpack2(add_(acc0, acc1), a0, a1);
-                const float v0 = __log2f(fmaxf(a0, 1e-10f)) * kLog10Of2, v1 = __log2f(fmaxf(a1, 1e-10f)) * kLog10Of2;
-                // raw row -> HBM straight from the registers, 128 contiguous bytes per store (src/audio.rs:254)
-                float* __restrict__ orow = outp + (int64_t)m * p.n_frames + lane;
-                if (ok0) { orow[0] = v0; lmax = fmaxf(lmax, v0); }
-                if (ok1) { orow[32] = v1; lmax = fmaxf(lmax, v1); }
+                const float v0 = log2_pos(fmax_nan(a0, 1e-10f)) * kLog10Of2, v1 = log2_pos(fmax_nan(a1, 1e-10f)) * kLog10Of2;
+                // raw row -> HBM straight from the registers (src/audio.rs:254)
+                if (ok0) { orow[0] = v0; lmax = fmax_nan(lmax, v0); }
+                if (ok1) { orow[16] = v1; lmax = fmax_nan(lmax, v1); }
+                orow += p.n_frames;
             }
         }
-        LM_T(3);
         if (fin) {
-            const float fl = sm.seg_floor;               // out = (max(raw, segmax - 8) + 4) / 4   (src/audio.rs:256-258)
+            const float fl_ = sm.seg_floor;              // out = (max(raw, segmax - 8) + 4) / 4   (src/audio.rs:256-258)
             if (ovec) {
 #pragma unroll
-                for (int k = 0; k < kPer; ++k) {
-                    const int idx = tid + k * kThreads;
-                    if (idx < WRS_N_MELS * (kTW / 4) && (idx & 15) < fnf4) {
-                        float4 v = raw[k];
-                        v.x = (fmaxf(v.x, fl) + 4.0f) * 0.25f; v.y = (fmaxf(v.y, fl) + 4.0f) * 0.25f;
-                        v.z = (fmaxf(v.z, fl) + 4.0f) * 0.25f; v.w = (fmaxf(v.w, fl) + 4.0f) * 0.25f;
+                for (int j = 0; j < kPer; ++j) {
+                    const int idx = bt + j * kBThreads;
+                    if ((idx & 15) < fnf4) {
+                        float4 v = raw[j];
+                        v.x = floor_scale(v.x, fl_); v.y = floor_scale(v.y, fl_); v.z = floor_scale(v.z, fl_); v.w = floor_scale(v.w, fl_);
                         *reinterpret_cast<float4*>(foutp + (int64_t)(idx >> 4) * p.n_frames + 4 * (idx & 15)) = v;
                     }
                 }
             } else {
-                floor_scale_slice<kThreads>(foutp, p.n_frames, fnf, fl, tid, false);   // unaligned output
+                floor_scale_slice<kBThreads>(foutp, p.n_frames, fnf, fl_, bt, false);   // unaligned output
             }
 #pragma unroll
-            for (int k = 0; k + 1 < kPend; ++k) { pend_seg[k] = pend_seg[k + 1]; pend_fs[k] = pend_fs[k + 1]; }
+            for (int j = 0; j + 1 < kPend; ++j) { pend_seg[j] = pend_seg[j + 1]; pend_fs[j] = pend_fs[j + 1]; }
             pend_fs[kPend - 1] = -1;
         }
-        // ---- per-slice max -> per-segment max (src/audio.rs:256 `log_spec.max()`)
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) lmax = fmaxf(lmax, __shfl_xor_sync(0xffffffffu, lmax, o));
-        // No CTA barrier closes stage C: a warp goes straight on to stage A of the next slice (which touches nothing
-        // stage C reads).  The last warp to add its maximum posts the slice: once the maximum is out the slice has
-        // posted (its raw rows are only ever re-read by this CTA).
-        if (lane == 0) {
-            atomicMax(&sm.red_max, float_key(lmax));
-            __threadfence_block();
-            if (atomicAdd(&sm.warps_done, 1) == kWarps - 1) {
+        // ---- per-slice max -> per-segment max (src/audio.rs:256 `log_spec.max()`); a NaN wins (its key is above +inf)
+        {
+            int kmax = float_key(lmax);
+            kmax = __reduce_max_sync(0xffffffffu, kmax);
+            // The last warp to add its maximum posts the slice: once the maximum is out the slice has posted (its raw
+            // rows are only ever re-read by this CTA).
+            if (lane == 0) {
+                atomicMax(&sm.red_max, kmax);
                 __threadfence_block();
-                const int key = atomicExch(&sm.red_max, float_key(-INFINITY));
-                atomicExch(&sm.warps_done, 0);
-                if (FUSED) st_relaxed(p.slice_max + (int64_t)seg * p.slices_per_seg + sl, key);
-                else atomicMax(p.seg_max + seg, key);
+                if (atomicAdd(&sm.warps_done, 1) == kBWarps - 1) {
+                    __threadfence_block();
+                    const int key = atomicExch(&sm.red_max, float_key(-INFINITY));
+                    atomicExch(&sm.warps_done, 0);
+                    if (FUSED) st_relaxed(p.slice_max + (int64_t)seg * p.slices_per_seg + sl, key);
+                    else atomicMax(p.seg_max + seg, key);
+                }
             }
         }
-        LM_T(4);
-        if (next_edge) __syncthreads();                  // the element-wise rows of the next tile came from every warp
-        LM_T(5);
         if (FUSED) {
             if (pend_fs[kPend - 1] >= 0) {               // queue full (a straggling segment): wait for the oldest
-                __syncthreads();
-                finalize_slice_blocking(sm, p, pend_seg[0], pend_fs[0], tid);
+                bar_bc();
+                finalize_slice_blocking(sm, p, pend_seg[0], pend_fs[0], bt);
 #pragma unroll
-                for (int k = 0; k + 1 < kPend; ++k) { pend_seg[k] = pend_seg[k + 1]; pend_fs[k] = pend_fs[k + 1]; }
+                for (int j = 0; j + 1 < kPend; ++j) { pend_seg[j] = pend_seg[j + 1]; pend_fs[j] = pend_fs[j + 1]; }
                 pend_fs[kPend - 1] = -1;
             }
             bool placed = false;
 #pragma unroll
-            for (int k = 0; k < kPend; ++k)
-                if (!placed && pend_fs[k] < 0) { pend_seg[k] = seg; pend_fs[k] = fs; placed = true; }
+            for (int j = 0; j < kPend; ++j)
+                if (!placed && pend_fs[j] < 0) { pend_seg[j] = seg; pend_fs[j] = fs; placed = true; }
         }
-        LM_T(6);
-        seg = nseg; sl = nsl; cur_bulk = next_bulk;
+        seg = nseg; sl = nsl;
     }
-#ifdef WRS_TRACE
-    if (tid == 0) for (int k = 0; k < 12; ++k) g_lm_trace[blockIdx.x * 12 + k] = acc_[k];
-#endif
     if (FUSED) {
-        __syncthreads();
+        bar_bc();
 #pragma unroll
-        for (int k = 0; k < kPend; ++k)
-            if (pend_fs[k] >= 0) finalize_slice_blocking(sm, p, pend_seg[k], pend_fs[k], tid);
+        for (int j = 0; j < kPend; ++j)
+            if (pend_fs[j] >= 0) finalize_slice_blocking(sm, p, pend_seg[j], pend_fs[j], bt);
     }
 }
 
@@ -531,19 +540,15 @@ static bool g_tables_ready[64] = {false};
 static int init_tables(wrs_ctx* ctx) {
     if (ctx->device < 64 && g_tables_ready[ctx->device]) return WRS_OK;
     const double PI = 3.14159265358979323846;
-    static TabEntry tab[WRS_N_FFT];
+    static float win[WRS_N_FFT];
     static float2 tw[16 * 13];
-    for (int n = 0; n < WRS_N_FFT; ++n) {
-        const int u = n + 120;   // frame f, tap n  ->  row f + u/160 of the tile (row 0 = frame row fs-2), column u%160
-        tab[n].off = (u / WRS_HOP_LENGTH) * kPitch + (u % WRS_HOP_LENGTH);
-        tab[n].win = (float)(0.5 - 0.5 * std::cos(2.0 * PI * n / WRS_N_FFT));
-    }
+    for (int n = 0; n < WRS_N_FFT; ++n) win[n] = (float)(0.5 - 0.5 * std::cos(2.0 * PI * n / WRS_N_FFT));
     for (int t = 0; t < 16; ++t)
         for (int q = 0; q < 13; ++q) {
             const double a = -2.0 * PI * (double)(t * q) / 400.0;
             tw[t * 13 + q] = make_float2((float)std::cos(a), (float)std::sin(a));
         }
-    WRS_CUDA(ctx, cudaMemcpyToSymbol(c_tab, tab, sizeof(tab)));
+    WRS_CUDA(ctx, cudaMemcpyToSymbol(c_win, win, sizeof(win)));
     WRS_CUDA(ctx, cudaMemcpyToSymbol(c_tw, tw, sizeof(tw)));
     if (ctx->device < 64) g_tables_ready[ctx->device] = true;
     return WRS_OK;
@@ -553,11 +558,6 @@ static int init_tables(wrs_ctx* ctx) {
 
 extern "C" {
 
-#ifdef WRS_TRACE
-int wrs_debug_logmel_trace_read(unsigned long long* out_host, int n) {
-    return (int)cudaMemcpyFromSymbol(out_host, wrs::g_lm_trace, sizeof(unsigned long long) * n);
-}
-#endif
 
 int wrs_logmel_set_filter(wrs_ctx* ctx, const float* filter_host) {
     if (!ctx) return wrs::fail(nullptr, WRS_ERR_INVALID, "wrs_logmel_set_filter: null ctx");
@@ -569,7 +569,7 @@ int wrs_logmel_set_filter(wrs_ctx* ctx, const float* filter_host) {
     }
     wrs::MelBank bank;
     if (!wrs::build_mel_bank(filter_host, &bank))
-        return wrs::fail(ctx, WRS_ERR_UNSUPPORTED, "wrs_logmel_set_filter: filterbank is not banded (more than 768 in-band weights after padding every band to a multiple of four)");
+        return wrs::fail(ctx, WRS_ERR_UNSUPPORTED, "wrs_logmel_set_filter: filterbank is not banded (more than 768 in-band weights after padding every band to an even count)");
     WRS_CUDA(ctx, cudaSetDevice(ctx->device));
     WRS_CUDA(ctx, cudaMemcpy(ctx->d_bank, &bank, sizeof(bank), cudaMemcpyHostToDevice));
     return WRS_OK;

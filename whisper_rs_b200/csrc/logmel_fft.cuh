@@ -61,6 +61,10 @@ WRS_D f32x2 cfma_(float c, f32x2 a, f32x2 b) { return fma_(a, pack2(c, c), b); }
 template <class T> WRS_HD cx<T> cmul(cx<T> a, cx<T> b) {
     return cx<T>{sub_(mul_(a.re, b.re), mul_(a.im, b.im)), fma_(a.re, b.im, mul_(a.im, b.re))};
 }
+// conj(a) * (b.re + i b.im), both run-time
+template <class T> WRS_HD cx<T> cmul_conj(cx<T> a, cx<T> b) {
+    return cx<T>{fma_(a.im, b.im, mul_(a.re, b.re)), sub_(mul_(a.re, b.im), mul_(a.im, b.re))};
+}
 // a * (wr + i wi) with a compile-time twiddle
 template <class T> WRS_HD cx<T> cmulc(cx<T> a, float wr, float wi) {
     return cx<T>{cfma_(-wi, a.im, cmul_(wr, a.re)), cfma_(wi, a.re, cmul_(wr, a.im))};
@@ -123,7 +127,10 @@ WRS_D void zero_(f32x2& a) { a.v = 0ull; }
 // Real 25-point DFT of v[0..24]; returns Y[0..12] (Y[0] real, its .im = 0).
 // m = 5a + b: first a real 5-point DFT over a for each residue b, then (after W25^{b q0}) a 5-point
 // DFT over b for q0 = 0 (real), 1, 2; q0 = 3, 4 are the conjugates of outputs of q0 = 2, 1.
-template <class T> WRS_HD void rdft25(const T (&v)[25], cx<T> (&y)[13]) {
+// RAW_CONJ: Y[3], Y[4], Y[8], Y[9] are left conjugated (rdft25_conj_slot(q) tells which); the caller folds the
+// conjugation into the twiddle multiplication that follows (cmul_conj), which saves the four negations.
+WRS_HD bool rdft25_conj_slot(int q) { return q == 3 || q == 4 || q == 8 || q == 9; }
+template <bool RAW_CONJ = false, class T> WRS_HD void rdft25(const T (&v)[25], cx<T> (&y)[13]) {
     T u0[5];
     cx<T> u1[5], u2[5];
 #pragma unroll
@@ -139,14 +146,16 @@ template <class T> WRS_HD void rdft25(const T (&v)[25], cx<T> (&y)[13]) {
         cx<T> o0, o1, o2, o3, o4;
         cdft5(u1[0], cmulc(u1[1], WRS_W25_1R, WRS_W25_1I), cmulc(u1[2], WRS_W25_2R, WRS_W25_2I),
               cmulc(u1[3], WRS_W25_3R, WRS_W25_3I), cmulc(u1[4], WRS_W25_4R, WRS_W25_4I), o0, o1, o2, o3, o4);
-        y[1] = o0; y[6] = o1; y[11] = o2; y[9] = cx<T>{o3.re, neg_(o3.im)}; y[4] = cx<T>{o4.re, neg_(o4.im)};
+        y[1] = o0; y[6] = o1; y[11] = o2;
+        if (RAW_CONJ) { y[9] = o3; y[4] = o4; } else { y[9] = cx<T>{o3.re, neg_(o3.im)}; y[4] = cx<T>{o4.re, neg_(o4.im)}; }
     }
     // q0 = 2 : outputs Y[2], Y[7], Y[12], Y[17] = conj Y[8], Y[22] = conj Y[3]
     {
         cx<T> o0, o1, o2, o3, o4;
         cdft5(u2[0], cmulc(u2[1], WRS_W25_2R, WRS_W25_2I), cmulc(u2[2], WRS_W25_4R, WRS_W25_4I),
               cmulc(u2[3], WRS_W25_6R, WRS_W25_6I), cmulc(u2[4], WRS_W25_8R, WRS_W25_8I), o0, o1, o2, o3, o4);
-        y[2] = o0; y[7] = o1; y[12] = o2; y[8] = cx<T>{o3.re, neg_(o3.im)}; y[3] = cx<T>{o4.re, neg_(o4.im)};
+        y[2] = o0; y[7] = o1; y[12] = o2;
+        if (RAW_CONJ) { y[8] = o3; y[3] = o4; } else { y[8] = cx<T>{o3.re, neg_(o3.im)}; y[3] = cx<T>{o4.re, neg_(o4.im)}; }
     }
 }
 

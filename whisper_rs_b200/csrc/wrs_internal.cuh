@@ -18,11 +18,14 @@ struct MelBank {
     int off[WRS_N_MELS];
     static constexpr int kMaxPadded = 768;
     float w[kMaxWeights];
-    // the same bands padded with zero weights to multiples of four (the mel loop takes four bins per step, a weight is
-    // the scalar operand of a packed two-frame FMA).  Row m: n4[m] weights from off4[m] (both multiples of 4).
-    int n4[WRS_N_MELS];
-    int off4[WRS_N_MELS];
+    // the same bands padded with zero weights to even counts (the mel loop takes two bins per step, a weight is the
+    // scalar operand of a packed two-frame FMA).  Row m: n2[m] >= 2 weights from off2[m] (both even).
+    int n2[WRS_N_MELS];
+    int off2[WRS_N_MELS];
     float wp[kMaxPadded];
+    // K1 stage C: mel rows [row_begin[w], row_begin[w+1]) belong to consumer warp w of 8, cut so that a warp's mel work
+    // plus its share of stage B (warps 0-4 take two 16-point DFT items, warps 5-7 one) comes out even
+    int row_begin[9];
     int total;
 };
 
