@@ -72,6 +72,17 @@ int wrs_logmel_set_filter(wrs_ctx* ctx, const float* filter_80x201_host);
 int wrs_logmel_batch(wrs_ctx* ctx, const float* pcm, int64_t n_segments, int64_t n_samples, int64_t seg_stride,
                      float* out, wrs_stream_t stream);
 
+/* wrs_logmel_batch for callers that cannot allocate device memory (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same arguments, same kernels, same results; the per-slice max words (the kernel's only scratch) live in
+ * a fixed 256 KB (65 536 words) static device array instead of the context's growable buffer, so the call makes no
+ * cudaMalloc / cudaFree / allocating library call.  A batch needs one word per 64-frame slice (47 per 30 s segment:
+ * up to 1394 segments), or one word per segment for clips longer than one round of the grid; more than that is
+ * rejected with WRS_ERR_UNSUPPORTED.  Every call on a device shares the array (it keeps the last call's words; a
+ * call clears what it uses, on `stream`): calls that overlap on the GPU race -- serialise them on one stream. */
+int wrs_logmel_batch_noalloc(wrs_ctx* ctx, const float* pcm, int64_t n_segments, int64_t n_samples,
+                             int64_t seg_stride, float* out, wrs_stream_t stream);
+
 /* Same call for a CPU-resident caller (the reference runs on Device::Cpu, examples/transcribe.rs:19):
  * HOST buffers; H2D, kernel, D2H and a stream synchronise happen inside. */
 int wrs_logmel_batch_host(wrs_ctx* ctx, const float* pcm_host, int64_t n_segments, int64_t n_samples,

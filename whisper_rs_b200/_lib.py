@@ -47,6 +47,7 @@ SIGNATURES = {
     "wrs_mel_filter_host": (C.c_int, [_P]),
     "wrs_logmel_set_filter": (C.c_int, [_P, _P]),
     "wrs_logmel_batch": (C.c_int, [_P, _P, _I64, _I64, _I64, _P, _P]),
+    "wrs_logmel_batch_noalloc": (C.c_int, [_P, _P, _I64, _I64, _I64, _P, _P]),
     "wrs_logmel_batch_host": (C.c_int, [_P, _P, _I64, _I64, _I64, _P]),
     "wrs_pad_or_trim": (C.c_int, [_P, _P, _I64, _I64, _I64, _P, _I64, _P]),
     "wrs_ctx_set_option": (C.c_int, [_P, C.c_char_p, _I64]),

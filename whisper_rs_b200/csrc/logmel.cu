@@ -575,16 +575,59 @@ int wrs_logmel_set_filter(wrs_ctx* ctx, const float* filter_host) {
     return WRS_OK;
 }
 
+}  // extern "C"
+
+namespace wrs {
+
+// ---- scratch of wrs_logmel_batch_noalloc: the per-slice (or per-segment) max words of ONE call, resident in every
+// GPU that loads the library until exit.  64 Ki words = 256 KB: up to 1394 segments of 30 s (47 slices each).
+constexpr int64_t kNoAllocWords = 65536;
+static __device__ __align__(256) int g_noalloc_seg_state[kNoAllocWords];
+static int* g_noalloc_ptr[64] = {nullptr};            // device address of the array, per device (host code must not use the symbol itself)
+
+// `scratch` == nullptr: the context's own buffer, grown with cudaMalloc when a call needs more (wrs_logmel_batch);
+// otherwise the caller-independent words [0, scratch_cap) and no allocation of any kind (wrs_logmel_batch_noalloc).
+static int logmel_batch_impl(wrs_ctx* ctx, const char* who, const float* pcm, int64_t n_segments, int64_t n_samples,
+                             int64_t seg_stride, float* out, wrs_stream_t stream_, int* scratch, int64_t scratch_cap);
+
+}  // namespace wrs
+
+extern "C" {
+
 int wrs_logmel_batch(wrs_ctx* ctx, const float* pcm, int64_t n_segments, int64_t n_samples, int64_t seg_stride,
                      float* out, wrs_stream_t stream_) {
+    return wrs::logmel_batch_impl(ctx, "wrs_logmel_batch", pcm, n_segments, n_samples, seg_stride, out, stream_, nullptr, 0);
+}
+
+int wrs_logmel_batch_noalloc(wrs_ctx* ctx, const float* pcm, int64_t n_segments, int64_t n_samples, int64_t seg_stride,
+                             float* out, wrs_stream_t stream_) {
     using namespace wrs;
-    if (!ctx) return fail(nullptr, WRS_ERR_INVALID, "wrs_logmel_batch: null ctx");
+    if (!ctx) return fail(nullptr, WRS_ERR_INVALID, "wrs_logmel_batch_noalloc: null ctx");
+    if (ctx->device < 0 || ctx->device >= 64) return fail(ctx, WRS_ERR_UNSUPPORTED, "wrs_logmel_batch_noalloc: device index beyond 63");
+    WRS_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (!g_noalloc_ptr[ctx->device]) {                // once per device, with that device current
+        int* ptr = nullptr;
+        WRS_CUDA(ctx, cudaGetSymbolAddress((void**)&ptr, g_noalloc_seg_state));
+        g_noalloc_ptr[ctx->device] = ptr;
+    }
+    return logmel_batch_impl(ctx, "wrs_logmel_batch_noalloc", pcm, n_segments, n_samples, seg_stride, out, stream_,
+                             g_noalloc_ptr[ctx->device], kNoAllocWords);
+}
+
+}  // extern "C"
+
+namespace wrs {
+
+static int logmel_batch_impl(wrs_ctx* ctx, const char* who_, const float* pcm, int64_t n_segments, int64_t n_samples,
+                             int64_t seg_stride, float* out, wrs_stream_t stream_, int* scratch, int64_t scratch_cap) {
+    const std::string who(who_);
+    if (!ctx) return fail(nullptr, WRS_ERR_INVALID, who + ": null ctx");
     if (n_segments == 0) return WRS_OK;
-    if (!pcm || !out) return fail(ctx, WRS_ERR_INVALID, "wrs_logmel_batch: null buffer");
+    if (!pcm || !out) return fail(ctx, WRS_ERR_INVALID, who + ": null buffer");
     if (n_segments < 0 || n_samples < WRS_N_FFT || seg_stride < n_samples)
-        return fail(ctx, WRS_ERR_INVALID, "wrs_logmel_batch: need n_segments >= 0, n_samples >= 400 (reflect padding needs > 200), seg_stride >= n_samples");
+        return fail(ctx, WRS_ERR_INVALID, who + ": need n_segments >= 0, n_samples >= 400 (reflect padding needs > 200), seg_stride >= n_samples");
     if (n_samples > (int64_t)1 << 30 || n_segments > (int64_t)1 << 24)
-        return fail(ctx, WRS_ERR_UNSUPPORTED, "wrs_logmel_batch: segment longer than 2^30 samples or more than 2^24 segments");
+        return fail(ctx, WRS_ERR_UNSUPPORTED, who + ": segment longer than 2^30 samples or more than 2^24 segments");
     cudaStream_t stream = (cudaStream_t)stream_;
     WRS_CUDA(ctx, cudaSetDevice(ctx->device));
     int rc = init_tables(ctx);
@@ -596,7 +639,7 @@ int wrs_logmel_batch(wrs_ctx* ctx, const float* pcm, int64_t n_segments, int64_t
     p.n_segments = (int)n_segments; p.n_samples = (int)n_samples; p.n_frames = (int)(n_samples / WRS_HOP_LENGTH);
     p.slices_per_seg = (p.n_frames + TW - 1) / TW;
     const int64_t total = (int64_t)p.slices_per_seg * n_segments;
-    if (total > INT32_MAX) return fail(ctx, WRS_ERR_UNSUPPORTED, "wrs_logmel_batch: too many slices");
+    if (total > INT32_MAX) return fail(ctx, WRS_ERR_UNSUPPORTED, who + ": too many slices");
     p.total_slices = (int)total;
     p.vec_in = ((reinterpret_cast<uintptr_t>(pcm) & 15) == 0 && (seg_stride & 3) == 0) ? 1 : 0;
     p.vec_out = ((reinterpret_cast<uintptr_t>(out) & 15) == 0 && (p.n_frames & 3) == 0) ? 1 : 0;
@@ -619,18 +662,27 @@ int wrs_logmel_batch(wrs_ctx* ctx, const float* pcm, int64_t n_segments, int64_t
     // "segment": src/transcribe.rs:112 takes the maximum over the clip) take the two-launch form.
     const bool fused = ctx->opt_logmel_fused != 0 && p.slices_per_seg <= grid;
     const int64_t need = fused ? total : n_segments;     // fused: one word per slice; two launches: one per segment
-    if (need > ctx->seg_cap) {
-        WRS_CUDA(ctx, cudaStreamSynchronize(stream));
-        cudaFree(ctx->d_seg_state);
-        ctx->d_seg_state = nullptr;
-        const int64_t cap = std::max<int64_t>(need, 4096);
-        WRS_CUDA(ctx, cudaMalloc(&ctx->d_seg_state, sizeof(int) * cap));
-        ctx->seg_cap = cap;
+    int* seg_state = scratch;
+    if (scratch) {
+        if (need > scratch_cap)
+            return fail(ctx, WRS_ERR_UNSUPPORTED, who + ": the call needs " + std::to_string(need) + " scratch words (one per 64-frame slice, or one per segment for a clip longer than one round of the grid); the fixed scratch holds " +
+                                                      std::to_string(scratch_cap) + " -- use wrs_logmel_batch or split the batch");
+    } else {
+        if (need > ctx->seg_cap) {
+            WRS_CUDA(ctx, cudaStreamSynchronize(stream));
+            cudaFree(ctx->d_seg_state);
+            ctx->d_seg_state = nullptr;
+            const int64_t cap = std::max<int64_t>(need, 4096);
+            WRS_CUDA(ctx, cudaMalloc(&ctx->d_seg_state, sizeof(int) * cap));
+            ctx->seg_cap = cap;
+        }
+        seg_state = ctx->d_seg_state;
     }
-    p.seg_max = ctx->d_seg_state;
-    p.slice_max = ctx->d_seg_state;
+    p.seg_max = seg_state;
+    p.slice_max = seg_state;
     // 0x80808080: kSlotEmpty for the per-slice words, and (decoding to about -3.4e38) "minus infinity" for atomicMax
-    WRS_CUDA(ctx, cudaMemsetAsync(ctx->d_seg_state, 0x80, sizeof(int) * need, stream));
+    // (the shared scratch keeps the last call's words: every call clears what it is going to use)
+    WRS_CUDA(ctx, cudaMemsetAsync(seg_state, 0x80, sizeof(int) * need, stream));
 
     // fused: the floor/scale of a slice is applied one slice later by the CTA that produced it, once the segment's
     // other slices (all owned by co-resident CTAs: cooperative launch) have posted their maxima
@@ -650,6 +702,10 @@ int wrs_logmel_batch(wrs_ctx* ctx, const float* pcm, int64_t n_segments, int64_t
     }
     return WRS_OK;
 }
+
+}  // namespace wrs
+
+extern "C" {
 
 int wrs_logmel_batch_host(wrs_ctx* ctx, const float* pcm_host, int64_t n_segments, int64_t n_samples,
                           int64_t seg_stride, float* out_host) {
