@@ -104,6 +104,26 @@ def test_reference_signature_whole_clip_and_custom_filter():
     assert (got.cpu() - want).abs().max().item() <= TOL
 
 
+def test_custom_filterbanks_of_every_band_class():
+    """K1 projects a mel row over 4, 8 or 16 bins (band zero-padded) or, wider than that, over its own length: banded
+    filterbanks that put rows into every class, including bands that end at bin 200."""
+    pcm = synth.audio_batch(4, seed=77, n_samples=160 * 700)
+    rng = np.random.default_rng(5)
+    for widths in ([6] * 80, [3, 8, 16, 20, 1, 12] * 13 + [2, 9]):
+        dense = np.zeros((80, 201), dtype=np.float32)
+        for m, wd in enumerate(widths):
+            lo = min(2 * m + (m % 3), 201 - wd)
+            dense[m, lo:lo + wd] = rng.uniform(0.002, 0.02, size=wd).astype(np.float32)
+        filt = torch.from_numpy(dense)
+        for s_ in (1, 3):
+            x = torch.from_numpy(pcm[s_])
+            got = audio.log_mel_spectrogram(x.cuda(), filt)
+            assert (got.cpu() - oa.log_mel_spectrogram(x, filt)).abs().max().item() <= TOL
+    x = torch.from_numpy(pcm[0])
+    got = audio.log_mel_spectrogram(x.cuda(), audio.mel_filter())          # back to the built-in filterbank
+    assert (got.cpu() - oa.log_mel_spectrogram(x, oa.mel_filter())).abs().max().item() <= TOL
+
+
 def test_long_clip_takes_the_two_launch_form():
     """a whole clip as one segment (src/transcribe.rs:112, maximum over the clip).  More slices than
     the grid holds in one round cannot use the in-kernel hand-over (waits could become circular): two launches."""

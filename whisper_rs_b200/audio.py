@@ -16,7 +16,7 @@ import torch
 from . import _lib
 from .constants import HOP_LENGTH, N_BINS, N_FFT, N_MELS, N_SAMPLES, N_FRAMES, SAMPLE_RATE, CHUNK_LENGTH  # noqa: F401
 
-_filter_cache = {}   # device -> key of the filter currently loaded in that device's context
+_filter_cache = {}   # device -> "builtin" or (the caller's filter tensor, its version) currently loaded in that device's context
 
 
 def mel_filter() -> torch.Tensor:
@@ -39,12 +39,13 @@ def _ensure_filter(ctx: _lib.Context, filt: torch.Tensor | None):
         return
     if tuple(filt.shape) != (N_MELS, N_BINS):
         raise ValueError(f"mel_filter must be [{N_MELS}, {N_BINS}], got {tuple(filt.shape)}")
-    key = (filt.data_ptr(), filt._version, str(filt.device), filt.dtype)
-    if _filter_cache.get(ctx.device) == key:
+    # the entry holds the tensor itself: its address cannot be reused by another filter while it is cached
+    cur = _filter_cache.get(ctx.device)
+    if isinstance(cur, tuple) and cur[0] is filt and cur[1] == filt._version:
         return
     host = filt.detach().to("cpu", torch.float32).contiguous().numpy()
     _lib.check(_lib.lib().wrs_logmel_set_filter(ctx.handle, host.ctypes.data_as(C.c_void_p)), ctx.handle)
-    _filter_cache[ctx.device] = key
+    _filter_cache[ctx.device] = (filt, filt._version)
 
 
 def pad_or_trim(audio: torch.Tensor, length: int) -> torch.Tensor:

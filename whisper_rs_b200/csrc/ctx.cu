@@ -52,38 +52,58 @@ void mel_filter_slaney(float* out) {
 }
 
 bool build_mel_bank(const float* dense, MelBank* bank) {
-    int total = 0, total2 = 0;
-    for (int i = 0; i < MelBank::kMaxPadded; ++i) bank->wp[i] = 0.0f;
-    double cost[WRS_N_MELS], cost_sum = 0;
+    constexpr int kPRows = WRS_N_BINS + 3;                  // rows of K1's power tile: 201 bins + zero rows behind them
+    int total = 0;
     for (int m = 0; m < WRS_N_MELS; ++m) {
         int lo = -1, hi = -1;
         for (int k = 0; k < WRS_N_BINS; ++k)
             if (dense[m * WRS_N_BINS + k] != 0.0f) { if (lo < 0) lo = k; hi = k; }
         if (lo < 0) { lo = 0; hi = -1; }
-        const int n = hi - lo + 1, n2 = std::max(2, (n + 1) & ~1);   // an empty row keeps two zero weights (K1 always takes a first step)
-        if (total + n > MelBank::kMaxWeights || total2 + n2 > MelBank::kMaxPadded) return false;
+        const int n = hi - lo + 1;
+        if (total + n > MelBank::kMaxWeights) return false;
         bank->lo[m] = lo; bank->n[m] = n; bank->off[m] = total;
-        bank->n2[m] = n2; bank->off2[m] = total2;
-        for (int j = 0; j < n; ++j) {
-            bank->w[total + j] = dense[m * WRS_N_BINS + lo + j];
-            bank->wp[total2 + j] = bank->w[total + j];
-        }
-        total += n; total2 += n2;
-        cost[m] = 22.0 + 2.5 * n2;                                    // issue slots of one mel row in stage C, roughly
-        cost_sum += cost[m];
+        for (int j = 0; j < n; ++j) bank->w[total + j] = dense[m * WRS_N_BINS + lo + j];
+        total += n;
     }
     bank->total = total;
-    // contiguous chunks of rows for the eight consumer warps; warps 5-7 did one stage-B item less (about 210 slots)
-    const double kItem = 210.0;
-    const double heavy = std::max(0.0, (cost_sum - 3 * kItem) / 8.0);
-    double edge = 0, run = 0;
-    int m = 0;
-    bank->row_begin[0] = 0;
-    for (int w = 0; w < 8; ++w) {
-        edge += heavy + (w >= 5 ? kItem : 0.0);
-        while (m < WRS_N_MELS && (w == 7 || run + 0.5 * cost[m] <= edge)) run += cost[m++];
-        bank->row_begin[w + 1] = m;
+    // classes, padded weights, and the deal: rows in descending cost, each to the warp with the least so far
+    int cls[WRS_N_MELS], len[WRS_N_MELS], order[WRS_N_MELS];
+    double cost[WRS_N_MELS];
+    for (int m = 0; m < WRS_N_MELS; ++m) {
+        const int n = bank->n[m];
+        static const int kLen[MelBank::kClasses - 1] = {2, 4, 6, 8, 12, 16};
+        cls[m] = MelBank::kClasses - 1; len[m] = (n + 1) & ~1;
+        for (int c = 0; c < MelBank::kClasses - 1; ++c)
+            if (n <= kLen[c]) { cls[m] = c; len[m] = kLen[c]; break; }
+        cost[m] = 22.0 + 2.25 * len[m];                     // issue slots of one mel row, roughly
+        order[m] = m;
     }
+    std::stable_sort(order, order + WRS_N_MELS, [&](int a, int b2) { return cost[a] > cost[b2]; });
+    double load[MelBank::kCWarps] = {0};
+    int owner[WRS_N_MELS];
+    for (int i = 0; i < WRS_N_MELS; ++i) {
+        int best = 0;
+        for (int w = 1; w < MelBank::kCWarps; ++w) if (load[w] < load[best]) best = w;
+        owner[order[i]] = best; load[best] += cost[order[i]];
+    }
+    for (int i = 0; i < MelBank::kMaxPadded; ++i) bank->wp[i] = 0.0f;
+    int nr = 0, nw = 0;
+    for (int w = 0; w < MelBank::kCWarps; ++w) {
+        for (int c = 0; c < MelBank::kClasses; ++c) {
+            bank->cls_begin[w][c] = nr;
+            for (int m = 0; m < WRS_N_MELS; ++m) {
+                if (owner[m] != w || cls[m] != c) continue;
+                const int L = len[m];
+                if (nw + L > MelBank::kMaxPadded || L > kPRows) return false;
+                const int first = std::max(0, std::min(bank->lo[m], kPRows - L));   // the window of L bins stays inside the power tile
+                for (int j = 0; j < bank->n[m]; ++j) bank->wp[nw + bank->lo[m] - first + j] = bank->w[bank->off[m] + j];
+                bank->rows[nr++] = make_int4(first * 32 * (int)sizeof(float2), nw * (int)sizeof(float), m, L);
+                nw += (L + 3) & ~3;
+            }
+        }
+        bank->cls_begin[w][MelBank::kClasses] = nr;
+    }
+    bank->rows[WRS_N_MELS] = bank->rows[WRS_N_MELS + 1] = bank->rows[0];   // (looked at, never used)
     return true;
 }
 

@@ -3,25 +3,25 @@
 // Replaces the ATen op sequence of reference src/audio.rs:230-259 (hann_window, stft, abs, pow, matmul,
 // clamp_min, log10, max, maximum, add, div) with one persistent, warp-specialised kernel.  A CTA (16 warps, one per
 // SM) takes tiles of 64 frames; every lane works on TWO frames held side by side in 64-bit register pairs, so the
-// FFT and the mel projection run on Blackwell's packed FP32 instructions (FADD2 / FMUL2 / FFMA2).
+// FFT and the mel projection run on Blackwell's packed FP32 instructions (FADD2 / FMUL2 / FFMA2): the FMA pipe runs
+// no faster for them (measured: 127 FMA/clk/SM either way), but they halve the issue slots, which is what bounds
+// this kernel.
 //
-//   warps 0-7  "A"  : real 25-point DFTs (FMA-pipe bound).  A tile is two passes of 32 frames (16 frame pairs
-//                     (f, f+16)); pass h reads PCM half-tile buffer h (34 rows of 160 samples, pitch 164, filled by
-//                     bulk async copies that the A warps issue themselves two passes ahead), every lane takes the
-//                     taps 16m + t of its frame pair at compile-time offsets, multiplies by the Hann window
-//                     (src/audio.rs:233), runs the 25-point DFT and the twiddles W400^{tq}, and stores
-//                     Y[t][q][frame pair] (float4: re2, im2).
-//   warps 8-15 "BC" : complex 16-point DFTs over t, |X|^2 -> P[bin][frame pair]; then the banded mel projection
-//                     (src/audio.rs:252), clamp + log10 (:254), raw rows -> HBM, slice maximum (:256); plus the
-//                     deferred floor / scale (:256-258) of an earlier slice of this CTA (LSU / memory bound).
+//   warps 0-7   "A"  : real 25-point DFTs.  A tile is two passes of 32 frames (16 frame pairs (f, f+16)); pass h reads
+//                      PCM half-tile buffer h (34 rows of 160 samples, pitch 164, filled by bulk async copies that the
+//                      A warps issue themselves one tile ahead), every lane takes the taps 16m + t of its frame pair at
+//                      compile-time offsets, multiplies by the Hann window (src/audio.rs:233), runs the 25-point DFT
+//                      and the twiddles W400^{tq}, and stores Y[t][q][frame pair] (float4: re2, im2), half h.
+//   warps 8-14  "BC" : per half, complex 16-point DFTs over t (lane = (q, frame pair), two q per warp), |X|^2 ->
+//                      P[bin][frame pair]; then the banded mel projection (src/audio.rs:252), clamp + log10 (:254), raw
+//                      rows -> HBM, slice maximum (:256) -> slice_max[segment][slice] (one word, written once).
+//   warp 15     "F"  : the finalizer.  For each slice of this CTA, oldest first: waits until every slice of the
+//                      slice's segment has posted its maximum, then applies floor (max-8) and (x+4)/4 (:256-258) in
+//                      place on the slice's own 20 KB of raw rows (still in L2).  Nothing waits for it.
 //
-// The two roles meet only through mbarriers (Y full / Y empty, PCM full / PCM empty per buffer): A of tile k+1 runs
-// while BC works on tile k, so the FMA-bound and the LSU-bound halves of the algorithm share the SM's issue slots
-// instead of alternating behind CTA barriers.  BC warps keep one named barrier between their two stages.
-//
-//   slice end       : raw log-mel -> HBM, the slice's max key -> slice_max[segment][slice] (written once)
-//   one slice later : once all slices of a segment have posted, its max is final and floor (max-8), (x+4)/4 are
-//                     applied in place on the slice's own 20 KB (still in L2)
+// The roles meet only through mbarriers (Y half full / empty, PCM buffer full / empty) and global memory (F): the
+// FMA-bound and the LSU-bound parts of the algorithm share the SM's issue slots instead of alternating behind CTA
+// barriers.  The seven BC warps keep one named barrier between their two stages.
 #include <algorithm>
 #include <cmath>
 
@@ -33,17 +33,19 @@ namespace wrs {
 
 constexpr int kThreads = 512;
 constexpr int kAWarps = 8;           // stage A (producers of Y)
-constexpr int kBWarps = 8;           // stages B and C (consumers)
+constexpr int kBWarps = 7;           // stages B and C (consumers); the sixteenth warp is the finalizer
 constexpr int kBThreads = kBWarps * 32;
-constexpr int kTW = 64;              // frames per tile (two per lane in stages B and C)
-constexpr int kHalf = 32;            // frames per stage-A pass
+constexpr int kTW = 64;              // frames per tile (two per lane)
+constexpr int kHalf = 32;            // frames per stage-A pass / per half of Y
 constexpr int kHRows = kHalf + 2;    // rows of 160 samples a pass reads: frame i uses rows i .. i+2
 constexpr int kPitch = WRS_HOP_LENGTH + 4;   // words per tile row: 16-byte aligned rows, frame stride == 4 banks
+constexpr int kWinPitch = 28;        // window table [t][m], 25 values padded to 7 x 16 bytes
+constexpr int kTwPitch = 24;         // twiddle table [t][(q-1)]{cos, sin}, q = 1..12
 constexpr float kLog10Of2 = 0.30102999566398120f;
 constexpr int kSlotEmpty = (int)0x80808080;         // memset pattern; as a key it decodes to -3.4e38, never a log10 value
 
-__constant__ float c_win[WRS_N_FFT];                 // periodic Hann, src/audio.rs:233
-__constant__ float2 c_tw[16 * 13];                   // W400^{tq} = (cos, sin)(-2 pi t q / 400)
+__constant__ float c_win[16 * kWinPitch];            // periodic Hann (src/audio.rs:233), c_win[t][m] = w[16m + t]
+__constant__ float c_tw[16 * kTwPitch];              // W400^{tq} = (cos, sin)(-2 pi t q / 400)
 
 struct LogmelParams {
     const float* pcm;
@@ -65,20 +67,18 @@ struct LogmelParams {
 constexpr int kPRows = WRS_N_BINS + 3;               // 201 bins + rows the zero-padded band tails may touch
 
 struct LogmelSmem {
-    float4 Y[16 * 13 * 32];                          // 106 496 B  [t][q][frame pair]
+    float4 Y[16 * 13 * 32];                          // 106 496 B  [t][q][frame pair], halves = frame pairs 0-15 / 16-31
     float2 P[kPRows * 32];                           // 52 224 B   [bin][frame pair]
     float pcm[2][kHRows * kPitch];                   // 44 608 B   half-tile buffers
-    float w[MelBank::kMaxPadded];                    // 3 072 B: in-band filter weights, bands zero-padded to even counts
-    int4 desc[WRS_N_MELS];                           // 1 280 B: {first bin, padded count, weight offset, 0} per mel row
-    float win[WRS_N_FFT];                            // 1 600 B
-    float2 tw[16 * 13];                              // 1 664 B
+    float w[MelBank::kMaxPadded];                    // 6 144 B: filter weights, bands zero-padded to their class length (MelBank)
+    int4 rows[WRS_N_MELS + 2];                       // 1 312 B: MelBank::rows
+    float win[16 * kWinPitch];                       // 1 792 B
+    float tw[16 * kTwPitch];                         // 1 536 B
     unsigned long long pcm_full[2], pcm_empty[2];    // mbarriers: half-tile buffer h filled / read by all A warps
-    unsigned long long y_full, y_empty;              // mbarriers: Y written by both passes / read by all BC warps
-    int row_begin[kBWarps + 1];                      // mel rows [row_begin[w], row_begin[w+1]) of BC warp w
+    unsigned long long y_full[2], y_empty[2];        // mbarriers: half h of Y written by all A warps / read by all BC warps
+    int cls_begin[kBWarps][MelBank::kClasses + 1];   // MelBank::cls_begin
     int red_max;                                     // max key of the slice in progress (reset by the last warp to add to it)
     int warps_done;
-    int fin_ready;                                   // the oldest pending slice's segment is complete: seg_floor is valid
-    float seg_floor;
 };
 static_assert(sizeof(LogmelSmem) <= 227 * 1024, "log-mel working set exceeds the 227 KB a CTA can own");
 
@@ -99,7 +99,7 @@ __device__ __forceinline__ float log2_pos(float a) {
     asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
     return r;
 }
-__device__ __forceinline__ float floor_scale(float x, float fl) { return (fmax_nan(x, fl) + 4.0f) * 0.25f; }
+__device__ __forceinline__ float scale4(float x) { return (x + 4.0f) * 0.25f; }     // src/audio.rs:258
 
 // one sample of the (virtually reflect-padded) segment; i is relative to the segment start
 __device__ __forceinline__ float load_reflect(const float* __restrict__ seg, int i, int n) {
@@ -108,8 +108,19 @@ __device__ __forceinline__ float load_reflect(const float* __restrict__ seg, int
     return (i >= 0 && i < n) ? __ldg(seg + i) : 0.0f;
 }
 
-__device__ __forceinline__ void mbar_arrive_expect_tx(unsigned long long* bar, unsigned bytes) { mbar_expect_tx(bar, bytes); }
 __device__ __forceinline__ void bar_bc() { asm volatile("bar.sync 1, %0;" ::"n"(kBThreads) : "memory"); }
+// mbarrier wait that lets the hardware park the warp (suspend-time hint) instead of spinning through issue slots
+__device__ __forceinline__ void mbar_wait_park(unsigned long long* bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_addr(bar)), "r"(parity), "r"(0x989680u) : "memory");
+}
 
 // Half-tile buffer `buf` <- rows f0 .. f0+33 of segment `seg` cut into 160-sample rows that start 200 samples before
 // the frame they are named after (row R = samples [160 R - 200, 160 R - 40) of the segment, so that frame f reads rows
@@ -121,6 +132,20 @@ __device__ __forceinline__ void stage_half(LogmelSmem& sm, const LogmelParams& p
     const float* __restrict__ segp = p.pcm + (int64_t)seg * p.seg_stride;
     float* tile = sm.pcm[buf];
     const int r_plain_hi = p.vec_in != 0 ? (p.n_samples + 40) / WRS_HOP_LENGTH : 0;      // rows R in [2, r_plain_hi] are plain
+    if (f0 >= 2 && f0 + kHRows - 1 <= r_plain_hi) {
+        // the usual half-tile: every row is plain.  Rows aw, aw + 8, ...: five of them for aw < 2, four otherwise.
+        if (elect_one()) {
+            const int n = aw < kHRows - 4 * kAWarps ? 5 : 4;
+            fence_proxy_async();                     // the buffer was last touched by ordinary loads
+            mbar_expect_tx(&sm.pcm_full[buf], (unsigned)(n * WRS_HOP_LENGTH * sizeof(float)));
+            const float* src = segp + (WRS_HOP_LENGTH * (f0 + aw) - 200);
+            float* dst = tile + aw * kPitch;
+#pragma unroll
+            for (int j = 0; j < 5; ++j)
+                if (j < n) bulk_g2s(dst + j * kAWarps * kPitch, src + j * kAWarps * WRS_HOP_LENGTH, WRS_HOP_LENGTH * (unsigned)sizeof(float), &sm.pcm_full[buf]);
+        }
+        return;
+    }
     int nplain = 0;
     for (int r = aw; r < kHRows; r += kAWarps) {
         const int R = f0 + r;
@@ -133,7 +158,7 @@ __device__ __forceinline__ void stage_half(LogmelSmem& sm, const LogmelParams& p
     if (elect_one()) {
         if (nplain != 0) {
             fence_proxy_async();                     // the buffer was last touched by ordinary loads / stores
-            mbar_arrive_expect_tx(&sm.pcm_full[buf], (unsigned)(nplain * WRS_HOP_LENGTH * sizeof(float)));
+            mbar_expect_tx(&sm.pcm_full[buf], (unsigned)(nplain * WRS_HOP_LENGTH * sizeof(float)));
             for (int r = aw; r < kHRows; r += kAWarps) {
                 const int R = f0 + r;
                 if (R >= 2 && R <= r_plain_hi)
@@ -154,13 +179,12 @@ __device__ __forceinline__ int ld_relaxed(const int* p) {
 }
 __device__ __forceinline__ void st_relaxed(int* p, int v) { asm volatile("st.relaxed.gpu.global.s32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
 
-// One warp: have all slices of `seg` posted?  Folds the slots this lane owns beyond the two it may already hold
-// (a = slot lane, b = slot lane + 32, fetched earlier); returns the segment's max key on every lane, `complete` likewise.
-__device__ __forceinline__ int fold_slots(const LogmelParams& p, int seg, int a, int b, int lane, bool& complete) {
+// One warp: have all slices of `seg` posted?  Returns the segment's max key on every lane, `complete` likewise.
+__device__ __forceinline__ int fold_slots(const LogmelParams& p, int seg, int lane, bool& complete) {
     const int* slots = p.slice_max + (int64_t)seg * p.slices_per_seg;
-    bool miss = (lane < p.slices_per_seg && a == kSlotEmpty) || (lane + 32 < p.slices_per_seg && b == kSlotEmpty);
-    int mx = max(lane < p.slices_per_seg ? a : INT32_MIN, lane + 32 < p.slices_per_seg ? b : INT32_MIN);
-    for (int i = lane + 64; i < p.slices_per_seg; i += 32) {
+    bool miss = false;
+    int mx = INT32_MIN;
+    for (int i = lane; i < p.slices_per_seg; i += 32) {
         const int v = ld_relaxed(slots + i);
         miss = miss || v == kSlotEmpty;
         mx = max(mx, v);
@@ -169,84 +193,89 @@ __device__ __forceinline__ int fold_slots(const LogmelParams& p, int seg, int a,
     return __reduce_max_sync(0xffffffffu, mx);
 }
 
-// out = (max(raw, segmax - 8) + 4) / 4 (src/audio.rs:256-258) in place on one [80][nf] slice, by NT threads (t = 0..NT-1).
-// Aligned rows: all of a thread's 16-byte loads go out before the first store.
-template <int NT>
-__device__ __forceinline__ void floor_scale_slice(float* __restrict__ outp, int64_t n_frames, int nf, float fl, int t, bool vec) {
+// The floor of src/audio.rs:256 on one [80][nf] slice of already scaled values, in place, by one warp:
+// out = max(out, fl) with fl = ((segmax - 8) + 4) / 4.  Aligned rows: ten 16-byte loads (L2) are in flight per lane
+// before the first store; a warp instruction covers two rows of the slice (16 lanes x 16 bytes each).  (Bulk reductions
+// by the TMA engine -- cp.reduce.async.bulk .max.s32 / .min.u32 on the bit patterns -- were measured: correct, but the
+// L2 takes them element by element: 131 us per batch against 109.)
+__device__ __forceinline__ void floor_slice(float* __restrict__ outp, int64_t n_frames, int nf, float fl, int lane, bool vec) {
     if (vec) {
-        constexpr int kPer = (WRS_N_MELS * (kTW / 4) + NT - 1) / NT, kBatch = kPer < 5 ? kPer : 5;
+        constexpr int kPer = WRS_N_MELS * (kTW / 4) / 32, kBatch = 10;      // 40 float4 per lane
+        static_assert(kPer % kBatch == 0, "batches must tile the slice");
         const int nf4 = nf >> 2;
+        const bool mine = (lane & 15) < nf4;
+        float* base = outp + (int64_t)(lane >> 4) * n_frames + 4 * (lane & 15);
+        const int64_t step = 2 * n_frames;                                  // two rows per warp instruction
 #pragma unroll 1
         for (int k0 = 0; k0 < kPer; k0 += kBatch) {
             float4 v[kBatch];
 #pragma unroll
-            for (int k = 0; k < kBatch; ++k) {
-                const int idx = t + (k0 + k) * NT;
-                if (idx < WRS_N_MELS * (kTW / 4) && (idx & 15) < nf4)
-                    v[k] = __ldcg(reinterpret_cast<const float4*>(outp + (int64_t)(idx >> 4) * n_frames + 4 * (idx & 15)));
-            }
+            for (int k = 0; k < kBatch; ++k)
+                if (mine) v[k] = __ldcg(reinterpret_cast<const float4*>(base + (k0 + k) * step));
 #pragma unroll
-            for (int k = 0; k < kBatch; ++k) {
-                const int idx = t + (k0 + k) * NT;
-                if (idx < WRS_N_MELS * (kTW / 4) && (idx & 15) < nf4) {
+            for (int k = 0; k < kBatch; ++k)
+                if (mine) {
                     float4 x = v[k];
-                    x.x = floor_scale(x.x, fl); x.y = floor_scale(x.y, fl); x.z = floor_scale(x.z, fl); x.w = floor_scale(x.w, fl);
-                    *reinterpret_cast<float4*>(outp + (int64_t)(idx >> 4) * n_frames + 4 * (idx & 15)) = x;
+                    x.x = fmax_nan(x.x, fl); x.y = fmax_nan(x.y, fl); x.z = fmax_nan(x.z, fl); x.w = fmax_nan(x.w, fl);
+                    *reinterpret_cast<float4*>(base + (k0 + k) * step) = x;
                 }
-            }
         }
     } else {
         const int d = max(nf, 1);
-        for (int idx = t; idx < WRS_N_MELS * nf; idx += NT) {
+        for (int idx = lane; idx < WRS_N_MELS * nf; idx += 32) {
             const int m = idx / d, c = idx - m * d;
             float* q = outp + (int64_t)m * n_frames + c;
-            *q = floor_scale(__ldcg(q), fl);
+            *q = fmax_nan(__ldcg(q), fl);
         }
     }
 }
 
-// Blocking floor + scale of one slice in place, by the eight BC warps (bt = 0..255).  Only the drain at the end of the
-// kernel (and a full pending queue) comes here; the steady state hides it inside the tile loop.
-__device__ __forceinline__ void finalize_slice_blocking(LogmelSmem& sm, const LogmelParams& p, int seg, int fs, int bt) {
-    const int nf = min(kTW, p.n_frames - fs);
-    if (bt < 32) {
-        // every slice of the segment is owned by a CTA that is running or has finished (persistent grid no larger than
-        // what is co-resident; a CTA posts its slice before it ever waits), so this wait ends; the bound is a safety net
-        const int* slots = p.slice_max + (int64_t)seg * p.slices_per_seg;
+// The finalizer warp of a CTA: the floor of the CTA's own slices, oldest first, each as soon as its segment's maximum
+// is known.  Every slice of a segment is owned by a CTA that is running or has finished (persistent grid no larger
+// than what is co-resident: cooperative launch), and the warps that produce slices never wait for a finalizer, so the
+// wait ends; the bound is a safety net (WRS_ERR_TIMEOUT through wrs_ctx_check).
+__device__ __forceinline__ void finalizer_warp(const LogmelParams& p, int lane) {
+    const int step_seg = (int)gridDim.x / p.slices_per_seg, step_sl = (int)gridDim.x % p.slices_per_seg;
+    int seg = (int)blockIdx.x / p.slices_per_seg, sl = (int)blockIdx.x % p.slices_per_seg;
+    const bool ovec = p.vec_out != 0;
+    for (int slice = blockIdx.x; slice < p.total_slices; slice += gridDim.x) {
         int spins = 0, key;
         for (;;) {
-            const int a = bt < p.slices_per_seg ? ld_relaxed(slots + bt) : 0;
-            const int b = bt + 32 < p.slices_per_seg ? ld_relaxed(slots + bt + 32) : 0;
             bool complete;
-            key = fold_slots(p, seg, a, b, bt, complete);
+            key = fold_slots(p, seg, lane, complete);
             if (complete) break;
-            __nanosleep(64);
-            if (++spins > (1 << 22)) { if (bt == 0) atomicExch(&p.status->timeout, 1); break; }
+            __nanosleep(spins < 8 ? 256 : 1024);
+            if (++spins > (1 << 21)) { if (lane == 0) atomicExch(&p.status->timeout, 1); break; }
         }
-        if (bt == 0) sm.seg_floor = key_float(key) - 8.0f;
+        // the slice's rows were stored by this CTA's BC warps before they posted its word: acquire at CTA scope
+        __threadfence_block();
+        const int fs = sl * kTW, nf = min(kTW, p.n_frames - fs);
+        floor_slice(p.out + ((int64_t)seg * WRS_N_MELS) * p.n_frames + fs, p.n_frames, nf, scale4(key_float(key) - 8.0f), lane, ovec);
+        seg += step_seg; sl += step_sl;
+        if (sl >= p.slices_per_seg) { sl -= p.slices_per_seg; ++seg; }
     }
-    bar_bc();
-    floor_scale_slice<kBThreads>(p.out + ((int64_t)seg * WRS_N_MELS) * p.n_frames + fs, p.n_frames, nf, sm.seg_floor, bt, p.vec_out != 0);
-    bar_bc();
 }
 
-constexpr int kPend = 4;              // slices a CTA may have waiting for their segment's maximum
-
 // ---- stage A, one pass: lane (i8, tl) of A warp (g, tq) takes frames i and i+16 of the half-tile (i = 8g + i8) and the
-// taps 16m + t (t = 4tq + tl).  8 frames x 4 consecutive taps per load = 32 distinct banks at pitch 164.
-__device__ __forceinline__ void stage_a_pass(LogmelSmem& sm, const float* __restrict__ tile, float4* __restrict__ ydst,
-                                             const float* __restrict__ winp, const float2* __restrict__ twp,
+// taps 16m + t (t = 4tq + tl).  8 frames x 4 consecutive taps per load = 32 distinct banks at pitch 164.  Window and
+// twiddles come as 16-byte loads from per-t tables (four distinct addresses per warp, broadcast within a tap).
+__device__ __forceinline__ void stage_a_pass(const float* __restrict__ tile, float4* __restrict__ ydst,
+                                             const float (&win)[25], const float (&tw)[24],
                                              unsigned long long* pcm_empty, unsigned long long* y_wait, unsigned y_parity, int lane) {
     f32x2 v[25];
 #pragma unroll
     for (int m = 0; m < 25; ++m) {
         constexpr int kHi = 16 * kPitch;
-        const int off = (m / 10) * kPitch + 16 * (m % 10);           // tap n = 16m + t: row n / 160 = m / 10 (t < 16)
-        const float wv = winp[16 * m];
-        v[m] = mul_(pack2(tile[off], tile[off + kHi]), pack2(wv, wv));
+        const int off = (m / 10) * kPitch + 16 * (m % 10);               // tap n = 16m + t: row n / 160 = m / 10 (t < 16)
+        v[m] = mul_(pack2(tile[off], tile[off + kHi]), pack2(win[m], win[m]));
     }
     cx<f32x2> y[13];
+#ifdef WRS_EXP_NO_AMATH
+#pragma unroll
+    for (int q = 0; q < 13; ++q) { y[q].re = v[q]; y[q].im = v[q + 12]; }
+#else
     rdft25<true>(v, y);
+#endif
     // every tap has been consumed: the buffer may be refilled once all eight A warps say so
     __syncwarp();
     if (lane == 0) mbar_arrive(pcm_empty);
@@ -254,11 +283,10 @@ __device__ __forceinline__ void stage_a_pass(LogmelSmem& sm, const float* __rest
     z[0] = y[0];
 #pragma unroll
     for (int q = 1; q < 13; ++q) {
-        const float2 w = twp[q];
-        const cx<f32x2> wq{pack2(w.x, w.x), pack2(w.y, w.y)};
+        const cx<f32x2> wq{pack2(tw[2 * q - 2], tw[2 * q - 2]), pack2(tw[2 * q - 1], tw[2 * q - 1])};
         z[q] = rdft25_conj_slot(q) ? cmul_conj(y[q], wq) : cmul(y[q], wq);
     }
-    if (y_wait) mbar_wait(y_wait, y_parity);         // BC has read the previous tile's Y
+    if (y_wait) mbar_wait_park(y_wait, y_parity);    // BC has read this half of the previous tile's Y
 #pragma unroll
     for (int q = 0; q < 13; ++q) {
         float a, b, c, d;
@@ -267,26 +295,108 @@ __device__ __forceinline__ void stage_a_pass(LogmelSmem& sm, const float* __rest
     }
 }
 
-// ---- stage B, one item: q, lane = frame pair.  Complex 16-point DFT over t, |X|^2 -> P.
-__device__ __forceinline__ void stage_b_load(const LogmelSmem& sm, int q, int lane, cx<f32x2> (&z)[16]) {
+// ---- stage B, one half of Y: lane (q2, f16) of BC warp w takes q = 2w + q2 and frame pair fp = 16h + f16.  Complex
+// 16-point DFT over t, |X|^2 -> P[bin][fp].  (q = 13 does not exist: that half warp repeats q = 12 and stores nothing.)
+__device__ __forceinline__ void stage_b_load(const LogmelSmem& sm, int q, int fp, cx<f32x2> (&z)[16]) {
+    const float4* src = sm.Y + q * 32 + fp;
 #pragma unroll
     for (int t = 0; t < 16; ++t) {
-        const float4 a = sm.Y[(t * 13 + q) * 32 + lane];
+        const float4 a = src[t * 13 * 32];
         z[t].re = pack2(a.x, a.y); z[t].im = pack2(a.z, a.w);
     }
-    cdft16(z);
 }
-__device__ __forceinline__ void stage_b_store(LogmelSmem& sm, int q, int lane, const cx<f32x2> (&z)[16]) {
+__device__ __forceinline__ void stage_b_store(LogmelSmem& sm, int q, int fp, bool active, const cx<f32x2> (&z)[16]) {
     // bins q + 25 s for s < 8; s >= 8 gives the conjugates of bins 400 - q - 25 s (q = 0: bin 200 at s = 8, nothing beyond)
-    float2* lo = sm.P + q * 32 + lane;
-    float2* hi = sm.P + (400 - q) * 32 + lane;                             // hi[-25 s * 32] = bin 400 - q - 25 s
+    float2* lo = sm.P + q * 32 + fp;
+    float2* hi = sm.P + (400 - q) * 32 + fp;                               // hi[-25 s * 32] = bin 400 - q - 25 s
+    const bool upper = active && q != 0;
 #pragma unroll
     for (int s = 0; s < 16; ++s) {
         float a, b;
         unpack2(power(z[s]), a, b);
-        if (s < 8) lo[25 * s * 32] = make_float2(a, b);
-        else if (q != 0) hi[-25 * s * 32] = make_float2(a, b);
-        else if (s == 8) lo[25 * s * 32] = make_float2(a, b);
+        if (s < 8) { if (active) lo[25 * s * 32] = make_float2(a, b); }
+        else {
+            if (upper) hi[-25 * s * 32] = make_float2(a, b);
+            if (s == 8 && active && q == 0) lo[25 * s * 32] = make_float2(a, b);
+        }
+    }
+}
+
+// ---- stage C: rows [b, e) of the row list, all of one class: N bins each (N = 0: the row's own even count), lane = frame
+// pair.  Banded mel projection (src/audio.rs:252), clamp + log10 (:254), raw row -> HBM straight from the registers.  A
+// row's loads all go out before its arithmetic; the next row's description is fetched behind them.
+struct MelRowCtx {
+    const int4* rows; const char* pbase; const char* wbase; float* obase; int n_frames; bool ok0, ok1;
+};
+__device__ __forceinline__ void mel_flush(const MelRowCtx& mc, f32x2 acc, int m, float& lmax) {
+    float a0, a1;
+    unpack2(acc, a0, a1);
+#ifdef WRS_EXP_NO_LOG
+    const float v0 = a0, v1 = a1;
+#else
+    const float v0 = log2_pos(fmax_nan(a0, 1e-10f)) * kLog10Of2, v1 = log2_pos(fmax_nan(a1, 1e-10f)) * kLog10Of2;
+#endif
+    float* __restrict__ orow = mc.obase + (int64_t)m * mc.n_frames;
+    // what goes to HBM is already scaled: (x + 4) / 4 is monotonic, so the floor of src/audio.rs:256 commutes with it
+    // exactly -- max((x + 4) / 4, (floor + 4) / 4) == (max(x, floor) + 4) / 4 -- and the finalizer only takes a maximum
+#ifdef WRS_EXP_NO_CSTORE
+    if (mc.ok0) lmax = fmax_nan(lmax, scale4(v0));
+    if (mc.ok1) lmax = fmax_nan(lmax, scale4(v1));
+#else
+    if (mc.ok0) { orow[0] = scale4(v0); lmax = fmax_nan(lmax, v0); }
+    if (mc.ok1) { orow[16] = scale4(v1); lmax = fmax_nan(lmax, v1); }
+#endif
+}
+// one row of a fixed-length class in flight: its description, N power values and N weights
+template <int N> struct MelRowRegs { int m; float2 q[N]; float2 w2[N / 2]; };
+template <int N>
+__device__ __forceinline__ void mel_row_load(const MelRowCtx& mc, int idx, MelRowRegs<N>& r) {
+    const int4 c = mc.rows[idx];
+    const float2* pp = reinterpret_cast<const float2*>(mc.pbase + c.x);
+    const float2* wv = reinterpret_cast<const float2*>(mc.wbase + c.y);
+    r.m = c.z;
+#pragma unroll
+    for (int j = 0; j < N / 2; ++j) r.w2[j] = wv[j];
+#pragma unroll
+    for (int j = 0; j < N; ++j) r.q[j] = pp[j * 32];
+}
+template <int N>
+__device__ __forceinline__ void mel_row_finish(const MelRowCtx& mc, const MelRowRegs<N>& r, float& lmax) {
+    f32x2 acc0 = mul_(pack2(r.q[0].x, r.q[0].y), pack2(r.w2[0].x, r.w2[0].x));
+    f32x2 acc1 = mul_(pack2(r.q[1].x, r.q[1].y), pack2(r.w2[0].y, r.w2[0].y));
+#pragma unroll
+    for (int j = 1; j < N / 2; ++j) {
+        acc0 = fma_(pack2(r.q[2 * j].x, r.q[2 * j].y), pack2(r.w2[j].x, r.w2[j].x), acc0);
+        acc1 = fma_(pack2(r.q[2 * j + 1].x, r.q[2 * j + 1].y), pack2(r.w2[j].y, r.w2[j].y), acc1);
+    }
+    mel_flush(mc, add_(acc0, acc1), r.m, lmax);
+}
+// rows [b, e) of class N (N bins each): a row's loads all go out before its arithmetic
+template <int N>
+__device__ __forceinline__ void mel_rows(const MelRowCtx& mc, int b, int e, float& lmax) {
+#pragma unroll 1
+    for (int i = b; i < e; ++i) {
+        MelRowRegs<N> r;
+        mel_row_load<N>(mc, i, r);
+        mel_row_finish<N>(mc, r, lmax);
+    }
+}
+// rows wider than the largest class: their own (even) number of bins
+__device__ __forceinline__ void mel_rows_wide(const MelRowCtx& mc, int b, int e, float& lmax) {
+#pragma unroll 1
+    for (int i = b; i < e; ++i) {
+        const int4 c = mc.rows[i];
+        const float2* pp = reinterpret_cast<const float2*>(mc.pbase + c.x);
+        const float2* wv = reinterpret_cast<const float2*>(mc.wbase + c.y);
+        f32x2 acc0 = pack2(0.0f, 0.0f), acc1 = acc0;
+#pragma unroll 2
+        for (int j = 0; j < c.w; j += 2) {
+            const float2 wj = wv[j >> 1];
+            const float2 q0 = pp[j * 32], q1 = pp[j * 32 + 32];
+            acc0 = fma_(pack2(q0.x, q0.y), pack2(wj.x, wj.x), acc0);
+            acc1 = fma_(pack2(q1.x, q1.y), pack2(wj.y, wj.y), acc1);
+        }
+        mel_flush(mc, add_(acc0, acc1), c.z, lmax);
     }
 }
 
@@ -296,30 +406,43 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
     LogmelSmem& sm = *reinterpret_cast<LogmelSmem*>(smem_raw);
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-    // tables -> smem (once per CTA); the rows of P behind bin 200 stay zero (zero-padded band tails read them)
-    for (int i = tid; i < WRS_N_MELS; i += kThreads) sm.desc[i] = make_int4(p.bank->lo[i], p.bank->n2[i], p.bank->off2[i], 0);
-    for (int i = tid; i < MelBank::kMaxPadded; i += kThreads) sm.w[i] = p.bank->wp[i];
-    for (int i = tid; i < WRS_N_FFT; i += kThreads) sm.win[i] = c_win[i];
-    for (int i = tid; i < 16 * 13; i += kThreads) sm.tw[i] = c_tw[i];
-    for (int i = tid; i < (kPRows - WRS_N_BINS) * 32; i += kThreads) sm.P[WRS_N_BINS * 32 + i] = make_float2(0.0f, 0.0f);
-    if (tid <= kBWarps) sm.row_begin[tid] = p.bank->row_begin[tid];
-    if (tid == 0) {
-        mbar_init(&sm.pcm_full[0], kAWarps); mbar_init(&sm.pcm_full[1], kAWarps);
-        mbar_init(&sm.pcm_empty[0], kAWarps); mbar_init(&sm.pcm_empty[1], kAWarps);
-        mbar_init(&sm.y_full, 2 * kAWarps); mbar_init(&sm.y_empty, kBWarps);
-        sm.red_max = float_key(-INFINITY); sm.warps_done = 0; sm.fin_ready = 0;
+    if (warp == kAWarps + kBWarps) {                     // the finalizer touches no shared memory: it starts at once
+#ifndef WRS_EXP_NO_F
+        if (FUSED) finalizer_warp(p, lane);
+#endif
+        return;
     }
-    __syncthreads();                                     // the only CTA-wide barrier: the roles part here
+    // tables -> smem (once per CTA); the rows of P behind bin 200 stay zero (zero-padded band tails read them)
+    constexpr int kSetup = (kAWarps + kBWarps) * 32;
+    for (int i = tid; i < WRS_N_MELS + 2; i += kSetup) sm.rows[i] = p.bank->rows[i];
+    for (int i = tid; i < MelBank::kMaxPadded; i += kSetup) sm.w[i] = p.bank->wp[i];
+    for (int i = tid; i < 16 * kWinPitch; i += kSetup) sm.win[i] = c_win[i];
+    for (int i = tid; i < 16 * kTwPitch; i += kSetup) sm.tw[i] = c_tw[i];
+    for (int i = tid; i < (kPRows - WRS_N_BINS) * 32; i += kSetup) sm.P[WRS_N_BINS * 32 + i] = make_float2(0.0f, 0.0f);
+    if (tid < kBWarps * (MelBank::kClasses + 1)) (&sm.cls_begin[0][0])[tid] = (&p.bank->cls_begin[0][0])[tid];
+    if (tid == 0) {
+        for (int h = 0; h < 2; ++h) {
+            mbar_init(&sm.pcm_full[h], kAWarps); mbar_init(&sm.pcm_empty[h], kAWarps);
+            mbar_init(&sm.y_full[h], kAWarps); mbar_init(&sm.y_empty[h], kBWarps);
+        }
+        sm.red_max = float_key(-INFINITY); sm.warps_done = 0;
+    }
+    asm volatile("bar.sync 2, %0;" ::"n"(kSetup) : "memory");   // the only barrier A and BC warps share: the roles part here
 
     // tiles are dealt round-robin; (seg, sl) of the current tile advance without divisions
-    const int step_seg = (int)gridDim.x / p.slices_per_seg, step_sl = (int)gridDim.x % p.slices_per_seg;
-    int seg = (int)blockIdx.x / p.slices_per_seg, sl = (int)blockIdx.x % p.slices_per_seg;
-
+    int gx = (int)gridDim.x, bx = (int)blockIdx.x, sps = p.slices_per_seg;
     if (warp < kAWarps) {
         // =================================================== A warps
+        asm volatile("" : "+r"(gx), "+r"(bx), "+r"(sps));
+        const int step_seg = gx / sps, step_sl = gx % sps;
+        int seg = bx / sps, sl = bx % sps;
         const int i = 8 * (warp & 1) + (lane & 7), t = 4 * (warp >> 1) + (lane >> 3);
-        const float* winp = sm.win + t;
-        const float2* twp = sm.tw + t * 13;
+        // the lane's t never changes: its 25 window values and 12 twiddles stay in registers for the whole kernel
+        float win[25], tw[24];
+#pragma unroll
+        for (int m = 0; m < 25; ++m) win[m] = sm.win[t * kWinPitch + m];
+#pragma unroll
+        for (int j = 0; j < 24; ++j) tw[j] = sm.tw[t * kTwPitch + j];
         if ((int)blockIdx.x < p.total_slices) {
             stage_half(sm, p, seg, sl * kTW, 0, warp, lane);
             stage_half(sm, p, seg, sl * kTW + kHalf, 1, warp, lane);
@@ -331,13 +454,13 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
             const bool has_next = slice + (int)gridDim.x < p.total_slices;
 #pragma unroll 1
             for (int h = 0; h < 2; ++h) {
-                mbar_wait(&sm.pcm_full[h], k & 1u);
-                stage_a_pass(sm, sm.pcm[h] + i * kPitch + t, sm.Y + (t * 13) * 32 + 16 * h + i, winp, twp, &sm.pcm_empty[h],
-                             (h == 0 && k > 0) ? &sm.y_empty : nullptr, (k - 1u) & 1u, lane);
+                mbar_wait_park(&sm.pcm_full[h], k & 1u);
+                stage_a_pass(sm.pcm[h] + i * kPitch + t, sm.Y + (t * 13) * 32 + 16 * h + i, win, tw, &sm.pcm_empty[h],
+                             k > 0 ? &sm.y_empty[h] : nullptr, (k - 1u) & 1u, lane);
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&sm.y_full);
+                if (lane == 0) mbar_arrive(&sm.y_full[h]);
                 if (has_next) {
-                    mbar_wait(&sm.pcm_empty[h], k & 1u);     // all eight A warps have taken their taps of this pass
+                    mbar_wait_park(&sm.pcm_empty[h], k & 1u);    // all eight A warps have taken their taps of this pass
                     stage_half(sm, p, nseg, nsl * kTW + kHalf * h, h, warp, lane);
                 }
             }
@@ -347,129 +470,64 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
     }
 
     // ======================================================= BC warps
-    const int bw = warp - kAWarps, bt = tid - kAWarps * 32;
-    // slices whose floor/scale is still to be applied, oldest first (fs < 0: empty)
-    int pend_seg[kPend], pend_fs[kPend];
+    const int step_seg = gx / sps, step_sl = gx % sps;
+    int seg = bx / sps, sl = bx % sps;
+    const int bw = warp - kAWarps;
+    int cb[MelBank::kClasses + 1];
 #pragma unroll
-    for (int k = 0; k < kPend; ++k) { pend_seg[k] = 0; pend_fs[k] = -1; }
-    const bool ovec = p.vec_out != 0;                    // output rows 16-byte aligned, n_frames % 4 == 0
-    const int m_begin = sm.row_begin[bw], m_end = sm.row_begin[bw + 1];
-    // lane = frame pair: frames fl and fl + 16 of the tile
+    for (int c = 0; c <= MelBank::kClasses; ++c) cb[c] = sm.cls_begin[bw][c];
+    // stage B: lane = (q2, frame pair of the half); stage C: lane = frame pair of the tile, frames fl and fl + 16
+    const int bq = min(2 * bw + (lane >> 4), 12);
+    const bool b_active = 2 * bw + (lane >> 4) < 13;
     const int fl = 32 * (lane >> 4) + (lane & 15);
+    const char* pbase = reinterpret_cast<const char*>(sm.P + lane);
+    const char* wbase = reinterpret_cast<const char*>(sm.w);
     unsigned k = 0;
     for (int slice = blockIdx.x; slice < p.total_slices; slice += gridDim.x, ++k) {
         const int fs = sl * kTW;                         // first frame of the tile
         const int nf = min(kTW, p.n_frames - fs);
         int nseg = seg + step_seg, nsl = sl + step_sl;
         if (nsl >= p.slices_per_seg) { nsl -= p.slices_per_seg; ++nseg; }
-        // has the oldest pending slice's segment completed?  The answer is asked for here and looked at after stage B,
-        // so that the round trip to L2 is off every warp's critical path.
-        int poll_a = 0, poll_b = 0;
-        if (FUSED && bw == kBWarps - 1 && pend_fs[0] >= 0) {
-            const int* slots = p.slice_max + (int64_t)pend_seg[0] * p.slices_per_seg;
-            if (lane < p.slices_per_seg) poll_a = ld_relaxed(slots + lane);
-            if (lane + 32 < p.slices_per_seg) poll_b = ld_relaxed(slots + lane + 32);
-        }
-        mbar_wait(&sm.y_full, k & 1u);
 
-        // ---- stage B: 13 items (q) over 8 warps: warps 0-4 take q and q + 8, warps 5-7 take one
-        {
+        // ---- stage B, half by half
+#pragma unroll 1
+        for (int h = 0; h < 2; ++h) {
             cx<f32x2> z[16];
-            stage_b_load(sm, bw, lane, z);
-            if (bw >= 5) { __syncwarp(); if (lane == 0) mbar_arrive(&sm.y_empty); }
-            bar_bc();                                    // every BC warp has finished stage C of the previous tile: P is free
-            stage_b_store(sm, bw, lane, z);
-            if (bw < 5) {
-                stage_b_load(sm, bw + 8, lane, z);
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&sm.y_empty);
-                stage_b_store(sm, bw + 8, lane, z);
-            }
+            mbar_wait_park(&sm.y_full[h], k & 1u);
+            stage_b_load(sm, bq, 16 * h + (lane & 15), z);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sm.y_empty[h]);  // this half of Y is in registers: A may overwrite it
+#ifndef WRS_EXP_NO_BMATH
+            cdft16(z);
+#endif
+            if (h == 0) bar_bc();                        // every BC warp has finished stage C of the previous tile: P is free
+            stage_b_store(sm, bq, 16 * h + (lane & 15), b_active, z);
         }
-        if (FUSED && bw == kBWarps - 1) {
-            bool ready = false;
-            int key = 0;
-            if (pend_fs[0] >= 0) key = fold_slots(p, pend_seg[0], poll_a, poll_b, lane, ready);
-            if (lane == 0) {
-                if (ready) sm.seg_floor = key_float(key) - 8.0f;
-                sm.fin_ready = ready ? 1 : 0;
-            }
-        }
-        bar_bc();                                        // P complete, fin_ready / seg_floor visible
+        bar_bc();                                        // P complete
 
         // ---- stage C: banded mel projection (src/audio.rs:252), clamp + log10 (:254), raw rows -> HBM
-        const bool fin = FUSED && sm.fin_ready != 0;
-        const int fseg = pend_seg[0], ffs = pend_fs[0];
-        const int fnf = fin ? min(kTW, p.n_frames - ffs) : 0;
-        float* __restrict__ foutp = p.out + ((int64_t)fseg * WRS_N_MELS) * p.n_frames + ffs;
-        // the pending slice whose floor has just become known: its raw rows come back from L2 behind the mel arithmetic
-        constexpr int kPer = (WRS_N_MELS * (kTW / 4) + kBThreads - 1) / kBThreads;   // float4 of a [80][64] slice per thread: 5
-        const int fnf4 = fnf >> 2;
-        float4 raw[kPer];
-        if (fin && ovec) {
-#pragma unroll
-            for (int j = 0; j < kPer; ++j) {
-                const int idx = bt + j * kBThreads;
-                if ((idx & 15) < fnf4)
-                    raw[j] = __ldcg(reinterpret_cast<const float4*>(foutp + (int64_t)(idx >> 4) * p.n_frames + 4 * (idx & 15)));
-            }
-        }
         float lmax = -INFINITY;
+#ifndef WRS_EXP_NO_C
         {
-            const bool ok0 = fl < nf, ok1 = fl + 16 < nf;
-            float* __restrict__ orow = p.out + ((int64_t)seg * WRS_N_MELS + m_begin) * p.n_frames + fs + fl;
-            int4 d = sm.desc[m_begin < WRS_N_MELS ? m_begin : 0];
-#pragma unroll 1
-            for (int m = m_begin; m < m_end; ++m) {
-                const float2* pp = sm.P + d.x * 32 + lane;
-                const float2* wv = reinterpret_cast<const float2*>(sm.w + d.z);
-                const int n2 = d.y;
-                d = sm.desc[min(m + 1, WRS_N_MELS - 1)];     // the next row's description is fetched behind this row's bins
-                float2 w0 = wv[0];
-                float2 p0 = pp[0], p1 = pp[32];
-                f32x2 acc0 = mul_(pack2(p0.x, p0.y), pack2(w0.x, w0.x));
-                f32x2 acc1 = mul_(pack2(p1.x, p1.y), pack2(w0.y, w0.y));
-#pragma unroll 2
-                for (int j = 2; j < n2; j += 2) {
-                    const float2 wj = wv[j >> 1];
-                    const float2 q0 = pp[j * 32], q1 = pp[j * 32 + 32];
-                    acc0 = fma_(pack2(q0.x, q0.y), pack2(wj.x, wj.x), acc0);
-                    acc1 = fma_(pack2(q1.x, q1.y), pack2(wj.y, wj.y), acc1);
-                }
-                float a0, a1;
-                unpack2(add_(acc0, acc1), a0, a1);
-                const float v0 = log2_pos(fmax_nan(a0, 1e-10f)) * kLog10Of2, v1 = log2_pos(fmax_nan(a1, 1e-10f)) * kLog10Of2;
-                // raw row -> HBM straight from the registers (src/audio.rs:254)
-                if (ok0) { orow[0] = v0; lmax = fmax_nan(lmax, v0); }
-                if (ok1) { orow[16] = v1; lmax = fmax_nan(lmax, v1); }
-                orow += p.n_frames;
-            }
+            MelRowCtx mc;
+            mc.rows = sm.rows; mc.pbase = pbase; mc.wbase = wbase;
+            mc.obase = p.out + ((int64_t)seg * WRS_N_MELS) * p.n_frames + fs + fl;
+            mc.n_frames = p.n_frames; mc.ok0 = fl < nf; mc.ok1 = fl + 16 < nf;
+            mel_rows<2>(mc, cb[0], cb[1], lmax);
+            mel_rows<4>(mc, cb[1], cb[2], lmax);
+            mel_rows<6>(mc, cb[2], cb[3], lmax);
+            mel_rows<8>(mc, cb[3], cb[4], lmax);
+            mel_rows<12>(mc, cb[4], cb[5], lmax);
+            mel_rows<16>(mc, cb[5], cb[6], lmax);
+            mel_rows_wide(mc, cb[6], cb[7], lmax);
         }
-        if (fin) {
-            const float fl_ = sm.seg_floor;              // out = (max(raw, segmax - 8) + 4) / 4   (src/audio.rs:256-258)
-            if (ovec) {
-#pragma unroll
-                for (int j = 0; j < kPer; ++j) {
-                    const int idx = bt + j * kBThreads;
-                    if ((idx & 15) < fnf4) {
-                        float4 v = raw[j];
-                        v.x = floor_scale(v.x, fl_); v.y = floor_scale(v.y, fl_); v.z = floor_scale(v.z, fl_); v.w = floor_scale(v.w, fl_);
-                        *reinterpret_cast<float4*>(foutp + (int64_t)(idx >> 4) * p.n_frames + 4 * (idx & 15)) = v;
-                    }
-                }
-            } else {
-                floor_scale_slice<kBThreads>(foutp, p.n_frames, fnf, fl_, bt, false);   // unaligned output
-            }
-#pragma unroll
-            for (int j = 0; j + 1 < kPend; ++j) { pend_seg[j] = pend_seg[j + 1]; pend_fs[j] = pend_fs[j + 1]; }
-            pend_fs[kPend - 1] = -1;
-        }
+#endif
         // ---- per-slice max -> per-segment max (src/audio.rs:256 `log_spec.max()`); a NaN wins (its key is above +inf)
         {
             int kmax = float_key(lmax);
-            kmax = __reduce_max_sync(0xffffffffu, kmax);
-            // The last warp to add its maximum posts the slice: once the maximum is out the slice has posted (its raw
-            // rows are only ever re-read by this CTA).
+            kmax = __reduce_max_sync(0xffffffffu, kmax);   // (also orders every lane's row stores before lane 0's fence)
+            // The last warp to add its maximum posts the slice: once the word is out the slice has posted, and its raw
+            // rows are complete for the finalizer of this CTA (release at CTA scope; nobody else reads them).
             if (lane == 0) {
                 atomicMax(&sm.red_max, kmax);
                 __threadfence_block();
@@ -482,46 +540,26 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
                 }
             }
         }
-        if (FUSED) {
-            if (pend_fs[kPend - 1] >= 0) {               // queue full (a straggling segment): wait for the oldest
-                bar_bc();
-                finalize_slice_blocking(sm, p, pend_seg[0], pend_fs[0], bt);
-#pragma unroll
-                for (int j = 0; j + 1 < kPend; ++j) { pend_seg[j] = pend_seg[j + 1]; pend_fs[j] = pend_fs[j + 1]; }
-                pend_fs[kPend - 1] = -1;
-            }
-            bool placed = false;
-#pragma unroll
-            for (int j = 0; j < kPend; ++j)
-                if (!placed && pend_fs[j] < 0) { pend_seg[j] = seg; pend_fs[j] = fs; placed = true; }
-        }
         seg = nseg; sl = nsl;
-    }
-    if (FUSED) {
-        bar_bc();
-#pragma unroll
-        for (int j = 0; j < kPend; ++j)
-            if (pend_fs[j] >= 0) finalize_slice_blocking(sm, p, pend_seg[j], pend_fs[j], bt);
     }
 }
 
-// second launch of the two-pass mode: in-place max(x, segmax-8), (x+4)/4
+// second launch of the two-pass mode: the floor, in place on the scaled values: max(y, ((segmax - 8) + 4) / 4)
 __global__ void __launch_bounds__(256) logmel_finalize_kernel(float* __restrict__ out, const int* __restrict__ seg_max,
                                                               int64_t per_seg, int64_t total, int vec) {
     const int64_t stride = (int64_t)gridDim.x * blockDim.x;
     if (vec) {
         const int64_t per4 = per_seg >> 2, total4 = total >> 2;
         for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total4; i += stride) {
-            const float fl = key_float(seg_max[i / per4]) - 8.0f;
+            const float fl = scale4(key_float(seg_max[i / per4]) - 8.0f);
             float4 v = reinterpret_cast<float4*>(out)[i];
-            v.x = (fmaxf(v.x, fl) + 4.0f) * 0.25f; v.y = (fmaxf(v.y, fl) + 4.0f) * 0.25f;
-            v.z = (fmaxf(v.z, fl) + 4.0f) * 0.25f; v.w = (fmaxf(v.w, fl) + 4.0f) * 0.25f;
+            v.x = fmax_nan(v.x, fl); v.y = fmax_nan(v.y, fl); v.z = fmax_nan(v.z, fl); v.w = fmax_nan(v.w, fl);
             reinterpret_cast<float4*>(out)[i] = v;
         }
     } else {
         for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride) {
-            const float fl = key_float(seg_max[i / per_seg]) - 8.0f;
-            out[i] = (fmaxf(out[i], fl) + 4.0f) * 0.25f;
+            const float fl = scale4(key_float(seg_max[i / per_seg]) - 8.0f);
+            out[i] = fmax_nan(out[i], fl);
         }
     }
 }
@@ -540,14 +578,17 @@ static bool g_tables_ready[64] = {false};
 static int init_tables(wrs_ctx* ctx) {
     if (ctx->device < 64 && g_tables_ready[ctx->device]) return WRS_OK;
     const double PI = 3.14159265358979323846;
-    static float win[WRS_N_FFT];
-    static float2 tw[16 * 13];
-    for (int n = 0; n < WRS_N_FFT; ++n) win[n] = (float)(0.5 - 0.5 * std::cos(2.0 * PI * n / WRS_N_FFT));
-    for (int t = 0; t < 16; ++t)
-        for (int q = 0; q < 13; ++q) {
+    static float win[16 * kWinPitch];
+    static float tw[16 * kTwPitch];
+    for (int t = 0; t < 16; ++t) {
+        for (int m = 0; m < kWinPitch; ++m)
+            win[t * kWinPitch + m] = m < 25 ? (float)(0.5 - 0.5 * std::cos(2.0 * PI * (16 * m + t) / WRS_N_FFT)) : 0.0f;
+        for (int q = 1; q < 13; ++q) {
             const double a = -2.0 * PI * (double)(t * q) / 400.0;
-            tw[t * 13 + q] = make_float2((float)std::cos(a), (float)std::sin(a));
+            tw[t * kTwPitch + 2 * (q - 1)] = (float)std::cos(a);
+            tw[t * kTwPitch + 2 * (q - 1) + 1] = (float)std::sin(a);
         }
+    }
     WRS_CUDA(ctx, cudaMemcpyToSymbol(c_win, win, sizeof(win)));
     WRS_CUDA(ctx, cudaMemcpyToSymbol(c_tw, tw, sizeof(tw)));
     if (ctx->device < 64) g_tables_ready[ctx->device] = true;
@@ -569,7 +610,7 @@ int wrs_logmel_set_filter(wrs_ctx* ctx, const float* filter_host) {
     }
     wrs::MelBank bank;
     if (!wrs::build_mel_bank(filter_host, &bank))
-        return wrs::fail(ctx, WRS_ERR_UNSUPPORTED, "wrs_logmel_set_filter: filterbank is not banded (more than 768 in-band weights after padding every band to an even count)");
+        return wrs::fail(ctx, WRS_ERR_UNSUPPORTED, "wrs_logmel_set_filter: filterbank is not banded (more than 512 in-band weights after padding every band to an even count)");
     WRS_CUDA(ctx, cudaSetDevice(ctx->device));
     WRS_CUDA(ctx, cudaMemcpy(ctx->d_bank, &bank, sizeof(bank), cudaMemcpyHostToDevice));
     return WRS_OK;
@@ -660,6 +701,8 @@ static int logmel_batch_impl(wrs_ctx* ctx, const char* who_, const float* pcm, i
     // The single fused launch needs a segment's slices to be dealt within one round of the grid: then every slice is
     // posted by a CTA that has not had to wait yet, and no wait can be circular.  Longer segments (a whole clip as one
     // "segment": src/transcribe.rs:112 takes the maximum over the clip) take the two-launch form.
+    // (the in-kernel finalizer is one warp per SM: right for batches of segments; a whole clip passed as one segment,
+    // src/transcribe.rs:112, finishes all at once and is better served by the full-grid second launch)
     const bool fused = ctx->opt_logmel_fused != 0 && p.slices_per_seg <= grid;
     const int64_t need = fused ? total : n_segments;     // fused: one word per slice; two launches: one per segment
     int* seg_state = scratch;

@@ -16,16 +16,15 @@ struct MelBank {
     int lo[WRS_N_MELS];
     int n[WRS_N_MELS];
     int off[WRS_N_MELS];
-    static constexpr int kMaxPadded = 768;
     float w[kMaxWeights];
-    // the same bands padded with zero weights to even counts (the mel loop takes two bins per step, a weight is the
-    // scalar operand of a packed two-frame FMA).  Row m: n2[m] >= 2 weights from off2[m] (both even).
-    int n2[WRS_N_MELS];
-    int off2[WRS_N_MELS];
-    float wp[kMaxPadded];
-    // K1 stage C: mel rows [row_begin[w], row_begin[w+1]) belong to consumer warp w of 8, cut so that a warp's mel work
-    // plus its share of stage B (warps 0-4 take two 16-point DFT items, warps 5-7 one) comes out even
-    int row_begin[9];
+    // K1 stage C.  Every row is projected over a fixed number of bins -- classes of 2, 4, 6, 8, 12 and 16 (its band
+    // zero-padded to that length: fully unrolled, all loads up front, two rows in flight) -- or, wider than 16 bins, over
+    // its own even count (the last class).  rows[] lists the rows warp by warp and class by class; consumer warp w of 7
+    // takes rows[cls_begin[w][c] .. cls_begin[w][c+1]).  The rows are dealt so that the warps' costs come out even.
+    static constexpr int kMaxPadded = 1536, kClasses = 7, kCWarps = 7;
+    float wp[kMaxPadded];                  // the padded weights, row after row (16-byte aligned starts)
+    int4 rows[WRS_N_MELS + 2];             // {byte offset of the first bin's row of P, byte offset into wp, mel row, bins}; two spare entries (look-ahead)
+    int cls_begin[kCWarps][kClasses + 1];
     int total;
 };
 
