@@ -70,7 +70,8 @@ def pad_or_trim(audio: torch.Tensor, length: int) -> torch.Tensor:
 
 def log_mel_spectrogram_batch(pcm: torch.Tensor, mel_filter: torch.Tensor | None = None, device: int = 0) -> torch.Tensor:
     """pcm [S, n] f32 -> [S, 80, n // 160] f32; every row is treated as the reference treats one clip.
-    CUDA input: result on the same device, enqueued on the current stream, no synchronisation.
+    CUDA input: result on the same device, enqueued on the current stream, no synchronisation (device-side
+    failures -- an expired bounded wait -- surface through `_lib.context(dev).check()`, which synchronises).
     CPU input: host buffers in, host tensor out (copies inside the call)."""
     if pcm.dim() != 2 or pcm.dtype != torch.float32:
         raise TypeError("log_mel_spectrogram_batch: expected a 2-D f32 tensor")

@@ -796,7 +796,7 @@ __device__ __forceinline__ void beam_fast(const StepParams& p, int audio, const 
             }
         }
     }
-    const bool staged = k * L <= 256;
+    const bool staged = L <= 64 && k * L <= 256;          // as decode_tail_kernel staged it
     // ---- output row r = warp: the r-th live entry visited (fewer than k live candidates cannot happen with >= k+1 finite
     //      logits per row; keep the row anyway: source 0, EOT, -inf)
     {
@@ -1076,7 +1076,8 @@ __global__ void __launch_bounds__(kMaxBeam * 32) decode_tail_kernel(const StepPa
     int64_t pre_m = 0, pre_m1 = 0, pre_o[4] = {0, 0, 0, 0};
     float cand_sum = 0.0f;
     int have = 0;
-    const bool staged = fast_tail && p.beam * p.cur_len <= 256;
+    // (the prefix is staged from two registers per lane, positions lane and lane + 32: prefixes of up to 64 tokens)
+    const bool staged = fast_tail && p.cur_len <= 64 && p.beam * p.cur_len <= 256;
     if (MODE == MODE_BEAM) {
         if (lane < p.cur_len) {
             pre_m = mine[lane];

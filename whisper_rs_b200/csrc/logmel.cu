@@ -803,8 +803,8 @@ int wrs_logmel_batch_host(wrs_ctx* ctx, const float* pcm_host, int64_t n_segment
     }
     WRS_CUDA(ctx, cudaStreamSynchronize(ctx->d2h_stream));
     WRS_CUDA(ctx, cudaStreamSynchronize(ctx->h2d_stream));
-    WRS_CUDA(ctx, cudaStreamSynchronize(s));
-    return WRS_OK;
+    // a synchronous call reports what its kernels left in the status word (an expired bounded wait means wrong data)
+    return wrs_ctx_check(ctx, (wrs_stream_t)s);
 }
 
 int wrs_pad_or_trim(wrs_ctx* ctx, const float* in, int64_t rows, int64_t in_len, int64_t in_stride, float* out,
