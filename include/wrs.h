@@ -20,7 +20,7 @@
 extern "C" {
 #endif
 
-#define WRS_ABI_VERSION 1
+#define WRS_ABI_VERSION 2
 
 enum {
     WRS_OK = 0,
@@ -87,6 +87,20 @@ int wrs_logmel_batch_noalloc(wrs_ctx* ctx, const float* pcm, int64_t n_segments,
  * HOST buffers; H2D, kernel, D2H and a stream synchronise happen inside. */
 int wrs_logmel_batch_host(wrs_ctx* ctx, const float* pcm_host, int64_t n_segments, int64_t n_samples,
                           int64_t seg_stride, float* out_host);
+
+/* The step in front of the front-end, as far as the reference pins it in its own tree (src/audio.rs:116-131, SURVEY.md
+ * 8f row 4): 16-bit PCM frames (`channels` interleaved samples each) -> mono f32, device pointers.  Each sample becomes
+ * s / 32768 (symphonia's SampleBuffer<f32> conversion, exact in f32); several channels are averaged per frame, summed left
+ * to right in f32 and divided by the count (`c.iter().sum::<f32>() / c.len() as f32`, :127-131).  The resampler behind it
+ * (rubato::FftFixedIn, :73-86, 133-166) is a third-party crate absent from the reference tree: not restated. */
+int wrs_pcm_i16_to_f32(wrs_ctx* ctx, const int16_t* pcm_i16, int64_t n_frames, int32_t channels, float* out,
+                       wrs_stream_t stream);
+
+/* wrs_logmel_batch_host for a caller that holds the decoder's 16-bit mono PCM (the reference converts to f32 on the host,
+ * src/audio.rs:116-122): HOST int16 in, host log-mel out; the conversion above runs on the device, so the copy in moves
+ * half the bytes.  Results equal wrs_logmel_batch_host fed the converted samples, bit for bit. */
+int wrs_logmel_batch_host_i16(wrs_ctx* ctx, const int16_t* pcm_host, int64_t n_segments, int64_t n_samples,
+                              int64_t seg_stride, float* out_host);
 
 /* audio::pad_or_trim  src/audio.rs:213-228 on the last dimension of a [rows][in_len] f32 array:
  * out [rows][out_len] = in[:, :out_len] or in right-padded with 0.0 (src/transcribe.rs:152 pads MEL frames). */
@@ -217,11 +231,21 @@ int wrs_avg_logprob_host(const double* sum_logprobs_host, const int32_t* n_token
  * dst[i][r] = src[i][source_idx[r]], source_idx a DEVICE array [n_rows] (the one wrs_beam_step writes).
  * src != dst (ping-pong the two buffers between steps).  An index outside [0, n_rows) copies the row's own
  * source and is reported by wrs_ctx_check (WRS_ERR_INVALID).
+ *
+ * group_invariant != 0 marks a tensor whose rows are identical within every beam group -- the cross-attention K / V,
+ * projections of audio_features.repeat_interleave(k) (src/decode/mod.rs:311-313).  A beam step's source_idx never
+ * leaves a row's group (beam_search.rs:91-114), so gathering such a tensor is a bit-exact no-op (the reference does it
+ * anyway, src/model.rs:321-327): it is skipped, `dst` is ignored (may be NULL or == src) and the caller keeps using
+ * `src`.  Option "kv_verify_group" = k > 0 (wrs_ctx_set_option) checks on the device, before the gather, that every
+ * flagged tensor really has identical rows within groups of k and that source_idx stays inside them; a violation is
+ * reported by wrs_ctx_check (WRS_ERR_INVALID).
  * ---------------------------------------------------------------------------------------------- */
 typedef struct {
     const void* src;
     void* dst;
     int64_t row_bytes;
+    int32_t group_invariant;
+    int32_t reserved;
 } wrs_kv_tensor;
 
 int wrs_kv_reorder(wrs_ctx* ctx, const wrs_kv_tensor* tensors_host, int32_t n_tensors, int64_t n_rows,

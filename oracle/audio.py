@@ -104,3 +104,17 @@ def log_mel_spectrogram_f64(audio: np.ndarray, mel_filter: np.ndarray) -> np.nda
     ls = np.log10(np.maximum(mel, 1e-10))
     ls = np.maximum(ls, ls.max() - 8.0)
     return (ls + 4.0) / 4.0
+
+
+def pcm_i16_to_mono_f32(pcm: np.ndarray, channels: int = 1) -> np.ndarray:
+    """reference src/audio.rs:116-131 between the codec and the tensor: symphonia's SampleBuffer<f32> conversion of
+    16-bit samples (s / 32768, exact in f32) and the downmix `c.iter().sum::<f32>() / c.len() as f32` of every
+    interleaved frame -- summed left to right in f32.  pcm: int16 [n_frames * channels] interleaved."""
+    x = pcm.astype(np.float32) * np.float32(1.0 / 32768.0)
+    if channels == 1:
+        return x
+    fr = x.reshape(-1, channels)
+    acc = np.zeros(fr.shape[0], dtype=np.float32)
+    for c in range(channels):
+        acc = (acc + fr[:, c]).astype(np.float32)
+    return (acc / np.float32(channels)).astype(np.float32)

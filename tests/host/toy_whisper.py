@@ -152,12 +152,15 @@ class _Decoder:
 
 class ToyWhisper:
     def __init__(self, dims: ModelDims, device="cuda", seed=0, cache_backend="wrs", logit_scale=3.0, eot=50257,
-                 eot_bias=0.0, eot_after=4):
+                 eot_bias=0.0, eot_after=4, flag_cross_invariant=False):
         gen = torch.Generator().manual_seed(seed)
         self.dims, self.device, self.cache_backend = dims, torch.device(device), cache_backend
         self.encoder = _Encoder(gen, dims, self.device)
         self.decoder = _Decoder(gen, dims, self.device, logit_scale, eot, eot_bias, eot_after)
         self.reorders = 0
+        # cross-attention K / V are projections of audio_features.repeat_interleave(k): identical within a beam group, so
+        # their gather is a no-op that the library can skip (wrs_kv_tensor.group_invariant)
+        self.flag_cross_invariant = flag_cross_invariant
 
     def _attentions(self):
         for b in self.decoder.blocks:
@@ -170,7 +173,10 @@ class ToyWhisper:
             return
         if self.cache_backend == "wrs":
             from whisper_rs_b200.cache import update_cache
-            new = update_cache(caches, source_indices)
+            flags = None
+            if self.flag_cross_invariant:
+                flags = [a is b.cross for b in self.decoder.blocks for a in (b.attn, b.cross) for _ in a.caches()]
+            new = update_cache(caches, source_indices, group_invariant=flags)
         else:
             from oracle.cache import update_cache
             new = update_cache(caches, source_indices.to(caches[0].device))

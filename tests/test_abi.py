@@ -27,7 +27,7 @@ def test_library_exports_every_declared_symbol(built_lib):
         assert hasattr(handle, s), f"{s} declared in wrs.h but not exported"
     from whisper_rs_b200 import _lib
     assert sorted(_lib.SIGNATURES) == syms          # the ctypes binding covers the whole header
-    assert _lib.lib().wrs_abi_version() == 1
+    assert _lib.lib().wrs_abi_version() == 2
 
 
 def test_cubin_is_sm_100a(built_lib):

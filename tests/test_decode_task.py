@@ -58,13 +58,14 @@ def test_config1_cpu_oracle_pipeline():
 
 # ------------------------------------------------------------------------------------------------- GPU
 def run_both(dims, ids, n_audio, *, beam=5, greedy=False, patience=1.0, prompt=None, sample_len=10, fused=True,
-             eot_bias=12.0, eot_after=4, seed=3, mel=None, len_penalty=None):
+             eot_bias=12.0, eot_after=4, seed=3, mel=None, len_penalty=None, flag_cross=False):
     from whisper_rs_b200 import decode as wd
     from whisper_rs_b200.decode.task import DecodeTask
     if mel is None:
         g = torch.Generator().manual_seed(seed)
         mel = torch.randn(n_audio, 80, 3000, generator=g).cuda()
-    mk = lambda backend: tw.ToyWhisper(dims, "cuda", seed, backend, eot=ids.eot, eot_bias=eot_bias, eot_after=eot_after)
+    mk = lambda backend: tw.ToyWhisper(dims, "cuda", seed, backend, eot=ids.eot, eot_bias=eot_bias, eot_after=eot_after,
+                                       flag_cross_invariant=flag_cross and backend == "wrs")
     mode = wd.TokenExtractMode.Greedy(1) if greedy else wd.TokenExtractMode.BeamSearch(beam, patience)
     task = DecodeTask(mk("wrs"), ids, wd.DecodeOptions(token_extract_mode=mode, sample_len=sample_len, len_penalty=len_penalty),
                       prompt=prompt, max_audio=n_audio, fused=fused)
@@ -94,6 +95,25 @@ def test_beam_task_matches_oracle(fused, prompt):
     assert task.model.reorders == omodel.reorders > 0                  # the KV reorder ran on the device every step
     for g in got:
         assert timestamp_grammar_ok(g.tokens, ids)
+
+
+@pytest.mark.gpu
+def test_beam_task_with_cross_caches_flagged_group_invariant():
+    """The cross-attention K / V never change under the beam reorder (identical rows within a beam group): flagged, the
+    library skips them -- same tokens, same scores as the oracle backend that gathers everything; the device-side
+    verification (option kv_verify_group) finds nothing to object to."""
+    from whisper_rs_b200 import _lib
+    ids = C.MULTILINGUAL
+    ctx = _lib.context(0)
+    ctx.set_option("kv_verify_group", 5)
+    try:
+        got, want, task, omodel = run_both(tw.ModelDims(), ids, 4, sample_len=12, flag_cross=True)
+        torch.cuda.synchronize()
+        ctx.check()
+    finally:
+        ctx.set_option("kv_verify_group", 0)
+    assert_same(got, want)
+    assert task.model.reorders == omodel.reorders > 0
 
 
 @pytest.mark.gpu

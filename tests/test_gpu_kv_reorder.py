@@ -103,3 +103,40 @@ def test_bad_index_is_reported():
     ctx = _lib.context(0)
     with pytest.raises(_lib.WrsError):
         ctx.check(torch.cuda.current_stream().cuda_stream)
+
+
+def test_group_invariant_tensors_are_skipped_and_verified():
+    """wrs_kv_tensor.group_invariant: the tensor is returned as it is (no traffic); option kv_verify_group checks the
+    claim on the device and reports a violation -- differing rows inside a group, or an index that leaves its group."""
+    from whisper_rs_b200 import _lib, cache
+    n_audio, beam = 4, 5
+    rows = n_audio * beam
+    g = torch.Generator().manual_seed(9)
+    cross = torch.randn((n_audio, 30, 16), generator=g).repeat_interleave(beam, 0).contiguous()     # identical within groups
+    own = torch.randn((rows, 7, 16), generator=g)
+    src = _beam_sources(n_audio, beam, seed=4)
+    ctx = _lib.context(0)
+    ctx.set_option("kv_verify_group", beam)
+    try:
+        dc, do = cross.cuda(), own.cuda()
+        got = cache.update_cache([dc, do], src.cuda(), group_invariant=[True, False])
+        torch.cuda.synchronize()
+        ctx.check()
+        assert got[0] is dc                                                  # skipped: the very same buffer
+        assert torch.equal(got[0].cpu(), oc.update_cache([cross], src)[0])    # ... which is what the gather would give
+        assert torch.equal(got[1].cpu(), oc.update_cache([own], src)[0])
+        # a tensor that is not group-invariant, flagged: reported
+        cache.update_cache([do], src.cuda(), group_invariant=[True])
+        torch.cuda.synchronize()
+        with pytest.raises(_lib.WrsError) as e:
+            ctx.check()
+        assert e.value.code == _lib.WRS_ERR_INVALID
+        # an index that leaves its group: reported
+        bad = src.clone(); bad[3] = 7
+        cache.update_cache([dc], bad.cuda(), group_invariant=[True])
+        torch.cuda.synchronize()
+        with pytest.raises(_lib.WrsError):
+            ctx.check()
+        ctx.check()                                                           # the status word was re-armed
+    finally:
+        ctx.set_option("kv_verify_group", 0)

@@ -187,3 +187,26 @@ def test_config2_batch64_properties():
     assert torch.equal(alone[0], got[17])
     rng_ = got.amax(dim=(1, 2)) - got.amin(dim=(1, 2))
     assert torch.all(rng_ <= 2.0 + 1e-6)                             # max-8 floor then /4
+
+
+@pytest.mark.parametrize("channels", [1, 2, 3, 6])
+def test_pcm_i16_conversion_and_downmix_bit_exact(channels):
+    """src/audio.rs:116-131: s / 32768 and the per-frame mean summed left to right in f32 -- integer input, bit-exact."""
+    rng = np.random.default_rng(channels)
+    for n in (1, 7, 4096 + 3, 160000):
+        pcm = rng.integers(-32768, 32768, size=n * channels, dtype=np.int16)
+        pcm[:channels] = -32768
+        pcm[-channels:] = 32767
+        got = audio.pcm_i16_to_f32(torch.from_numpy(pcm).cuda(), channels).cpu().numpy()
+        assert np.array_equal(got, oa.pcm_i16_to_mono_f32(pcm, channels))
+    odd = torch.from_numpy(rng.integers(-3000, 3000, size=1001, dtype=np.int16)).cuda()[1:]       # 2-byte aligned only
+    assert np.array_equal(audio.pcm_i16_to_f32(odd, 1).cpu().numpy(), oa.pcm_i16_to_mono_f32(odd.cpu().numpy(), 1))
+
+
+def test_host_i16_entry_point_matches_f32_entry_point():
+    pcm = synth.audio_batch(6, seed=41, n_samples=160 * 500 + 80)
+    i16 = np.round(np.clip(pcm, -1, 1) * 32767.0).astype(np.int16)
+    got = audio.log_mel_spectrogram_batch_i16(torch.from_numpy(i16))
+    conv = np.stack([oa.pcm_i16_to_mono_f32(r) for r in i16])
+    assert np.array_equal(got.numpy(), run_cuda(conv))                      # same samples -> same bits
+    assert np.abs(got.numpy() - oracle_batch(conv)).max() <= TOL

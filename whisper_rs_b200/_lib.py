@@ -33,7 +33,8 @@ class StepDebug(C.Structure):
 
 class KvTensor(C.Structure):
     """wrs_kv_tensor (include/wrs.h): one cached K or V array, rows contiguous."""
-    _fields_ = [("src", C.c_void_p), ("dst", C.c_void_p), ("row_bytes", C.c_int64)]
+    _fields_ = [("src", C.c_void_p), ("dst", C.c_void_p), ("row_bytes", C.c_int64), ("group_invariant", C.c_int32),
+                ("reserved", C.c_int32)]
 
 
 # name -> (restype, argtypes); every symbol declared in include/wrs.h
@@ -49,6 +50,8 @@ SIGNATURES = {
     "wrs_logmel_batch": (C.c_int, [_P, _P, _I64, _I64, _I64, _P, _P]),
     "wrs_logmel_batch_noalloc": (C.c_int, [_P, _P, _I64, _I64, _I64, _P, _P]),
     "wrs_logmel_batch_host": (C.c_int, [_P, _P, _I64, _I64, _I64, _P]),
+    "wrs_pcm_i16_to_f32": (C.c_int, [_P, _P, _I64, _I32, _P, _P]),
+    "wrs_logmel_batch_host_i16": (C.c_int, [_P, _P, _I64, _I64, _I64, _P]),
     "wrs_pad_or_trim": (C.c_int, [_P, _P, _I64, _I64, _I64, _P, _I64, _P]),
     "wrs_ctx_set_option": (C.c_int, [_P, C.c_char_p, _I64]),
     "wrs_ctx_get_stat": (_I64, [_P, C.c_char_p]),

@@ -101,3 +101,33 @@ def log_mel_spectrogram(audio: torch.Tensor, mel_filter: torch.Tensor) -> torch.
     if audio.dim() != 1:
         raise ValueError("log_mel_spectrogram: 1-D audio only (the reference's frame slice assumes it, SURVEY.md §0.6)")
     return log_mel_spectrogram_batch(audio.unsqueeze(0), mel_filter)[0]
+
+
+def pcm_i16_to_f32(pcm: torch.Tensor, channels: int = 1) -> torch.Tensor:
+    """16-bit interleaved PCM (CUDA int16 tensor, n_frames * channels samples) -> mono f32 [n_frames]: the conversion and
+    downmix of reference src/audio.rs:116-131 on the device (wrs_pcm_i16_to_f32)."""
+    if pcm.dtype != torch.int16 or not pcm.is_cuda or pcm.dim() != 1:
+        raise TypeError("pcm_i16_to_f32: expected a 1-D CUDA int16 tensor")
+    if channels < 1 or pcm.numel() % channels:
+        raise ValueError("pcm_i16_to_f32: the sample count is not a multiple of the channel count")
+    pcm = pcm.contiguous()
+    n = pcm.numel() // channels
+    out = torch.empty(n, dtype=torch.float32, device=pcm.device)
+    ctx = _lib.context(pcm.device.index or 0)
+    _lib.check(_lib.lib().wrs_pcm_i16_to_f32(ctx.handle, pcm.data_ptr(), n, channels, out.data_ptr(), _stream_of(pcm)), ctx.handle)
+    return out
+
+
+def log_mel_spectrogram_batch_i16(pcm: torch.Tensor, mel_filter: torch.Tensor | None = None, device: int = 0) -> torch.Tensor:
+    """Host int16 mono PCM [S, n] -> host log-mel [S, 80, n // 160] (wrs_logmel_batch_host_i16: half the bytes on the way in)."""
+    if pcm.dim() != 2 or pcm.dtype != torch.int16 or pcm.is_cuda:
+        raise TypeError("log_mel_spectrogram_batch_i16: expected a 2-D CPU int16 tensor")
+    S, n = pcm.shape
+    if n < N_FFT:
+        raise ValueError("log_mel_spectrogram_batch_i16: need at least 400 samples (reflect padding)")
+    pcm = pcm.contiguous()
+    ctx = _lib.context(device)
+    _ensure_filter(ctx, mel_filter)
+    out = torch.empty(S, N_MELS, n // HOP_LENGTH, dtype=torch.float32)
+    _lib.check(_lib.lib().wrs_logmel_batch_host_i16(ctx.handle, pcm.data_ptr(), S, n, n, out.data_ptr()), ctx.handle)
+    return out

@@ -20,8 +20,13 @@ def _stream_of(t: torch.Tensor) -> int:
 
 
 def update_cache(caches: Sequence[torch.Tensor], source_indices: torch.Tensor,
-                 out: Sequence[torch.Tensor] | None = None) -> list[torch.Tensor]:
+                 out: Sequence[torch.Tensor] | None = None,
+                 group_invariant: Sequence[bool] | None = None) -> list[torch.Tensor]:
     """`[c.index_select(0, source_indices) for c in caches]` in one launch.
+
+    group_invariant[i] marks a cache whose rows are identical within each beam group (the cross-attention K / V:
+    projections of `audio_features.repeat_interleave(k)`, src/decode/mod.rs:311-313): the gather cannot change it, it is
+    skipped and returned as it is (`wrs_kv_tensor.group_invariant`, include/wrs.h).
 
     caches: CUDA tensors whose dim 0 is the row (n_audio * beam) dimension, each contiguous; source_indices: CUDA
     int32/int64 `[rows]` (src/decode/extractor/beam_search.rs:111-114).  `out` (same shapes, different storage) is
@@ -36,14 +41,18 @@ def update_cache(caches: Sequence[torch.Tensor], source_indices: torch.Tensor,
     idx = source_indices.to(device=dev, dtype=torch.int32).contiguous()
     if idx.numel() != rows:
         raise _lib.WrsError(_lib.WRS_ERR_INVALID, "update_cache: one source index per row")
+    inv = [bool(f) for f in group_invariant] if group_invariant is not None else [False] * len(caches)
     if out is None:
-        out = [torch.empty_like(c) for c in caches]
+        out = [c if f else torch.empty_like(c) for c, f in zip(caches, inv)]
+    else:
+        out = [c if f else o for c, o, f in zip(caches, out, inv)]
     descs = (_lib.KvTensor * len(caches))()
     for i, (c, o) in enumerate(zip(caches, out)):
         if c.shape[0] != rows or not c.is_contiguous() or not o.is_contiguous() or o.shape != c.shape or o.dtype != c.dtype:
             raise _lib.WrsError(_lib.WRS_ERR_INVALID, "update_cache: caches must be contiguous [rows, ...] with matching outputs")
         descs[i].src, descs[i].dst = c.data_ptr(), o.data_ptr()
         descs[i].row_bytes = (c.numel() // rows) * c.element_size() if rows else 0
+        descs[i].group_invariant = 1 if inv[i] else 0
     ctx = _lib.context(dev.index or 0)
     _lib.check(_lib.lib().wrs_kv_reorder(ctx.handle, descs, len(caches), rows, idx.data_ptr(), _stream_of(caches[0])),
                ctx.handle)
@@ -57,8 +66,9 @@ class KVCache:
         self.tensors: list[torch.Tensor] = []
         self._spare: list[torch.Tensor] | None = None
 
-    def set(self, tensors: Sequence[torch.Tensor]):
+    def set(self, tensors: Sequence[torch.Tensor], group_invariant: Sequence[bool] | None = None):
         self.tensors = [t.contiguous() for t in tensors]
+        self.group_invariant = list(group_invariant) if group_invariant is not None else None
         self._spare = None
 
     def update_cache(self, source_indices: torch.Tensor):
@@ -68,7 +78,7 @@ class KVCache:
         spare = self._spare
         if spare is None or any(s.shape != t.shape or s.dtype != t.dtype for s, t in zip(spare, self.tensors)):
             spare = None
-        new = update_cache(self.tensors, source_indices, spare)
+        new = update_cache(self.tensors, source_indices, spare, getattr(self, "group_invariant", None))
         self._spare, self.tensors = self.tensors, new
 
     def clear_cache(self):

@@ -160,6 +160,7 @@ void wrs_ctx_destroy(wrs_ctx* ctx) {
     cudaFree(ctx->d_status);
     cudaFree(ctx->d_stage_in);
     cudaFree(ctx->d_stage_out);
+    cudaFree(ctx->d_stage_i16);
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     if (ctx->h2d_stream) cudaStreamDestroy(ctx->h2d_stream);
     if (ctx->d2h_stream) cudaStreamDestroy(ctx->d2h_stream);
@@ -175,10 +176,11 @@ int wrs_ctx_check(wrs_ctx* ctx, wrs_stream_t stream) {
     wrs::DevStatus st;
     WRS_CUDA(ctx, cudaMemcpyAsync(&st, ctx->d_status, sizeof(st), cudaMemcpyDeviceToHost, (cudaStream_t)stream));
     WRS_CUDA(ctx, cudaStreamSynchronize((cudaStream_t)stream));
-    if (st.timeout || st.nan_rows || st.bad_index) {
+    if (st.timeout || st.nan_rows || st.bad_index || st.group_violation) {
         WRS_CUDA(ctx, cudaMemsetAsync(ctx->d_status, 0, sizeof(st), (cudaStream_t)stream));
         if (st.timeout) return wrs::fail(ctx, WRS_ERR_TIMEOUT, "device-side bounded wait expired");
         if (st.bad_index) return wrs::fail(ctx, WRS_ERR_INVALID, "wrs_kv_reorder: a source index was outside [0, n_rows)");
+        if (st.group_violation) return wrs::fail(ctx, WRS_ERR_INVALID, "wrs_kv_reorder: a tensor flagged group_invariant has differing rows within a beam group, or a source index leaves its group");
         return wrs::fail(ctx, WRS_ERR_NUMERIC, "NaN reached the softmax (the reference panics here)");
     }
     return WRS_OK;
@@ -187,6 +189,7 @@ int wrs_ctx_check(wrs_ctx* ctx, wrs_stream_t stream) {
 int wrs_ctx_set_option(wrs_ctx* ctx, const char* key, int64_t value) {
     if (!ctx || !key) return wrs::fail(ctx, WRS_ERR_INVALID, "wrs_ctx_set_option: null argument");
     if (!strcmp(key, "logmel_fused")) { ctx->opt_logmel_fused = (int)value; return WRS_OK; }
+    if (!strcmp(key, "kv_verify_group")) { ctx->opt_kv_verify_group = (int)value; return WRS_OK; }
     return wrs::fail(ctx, WRS_ERR_INVALID, std::string("unknown option ") + key);
 }
 

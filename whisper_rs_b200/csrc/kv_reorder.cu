@@ -71,6 +71,25 @@ __global__ void __launch_bounds__(kKvThreads) kv_reorder_kernel(const __grid_con
     }
 }
 
+// Debug check of a tensor flagged group-invariant (option kv_verify_group): every row equals the first row of its beam
+// group, and every source index stays inside its row's group.
+__global__ void __launch_bounds__(256) kv_verify_kernel(const unsigned char* __restrict__ t, long long row_bytes, int n_rows, int group,
+                                                        const int* __restrict__ source_idx, DevStatus* status) {
+    bool bad = false;
+    for (int r = blockIdx.y; r < n_rows; r += gridDim.y) {
+        const int lead = r - r % group;
+        if (blockIdx.x == 0 && threadIdx.x == 0) {
+            const int s = source_idx[r];
+            bad |= s < lead || s >= lead + group;
+        }
+        if (r == lead) continue;
+        const unsigned char* a = t + (long long)r * row_bytes;
+        const unsigned char* b = t + (long long)lead * row_bytes;
+        for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < row_bytes; i += (long long)gridDim.x * blockDim.x) bad |= a[i] != b[i];
+    }
+    if (bad) atomicExch(&status->group_violation, 1);
+}
+
 }  // namespace wrs
 
 extern "C" int wrs_kv_reorder(wrs_ctx* ctx, const wrs_kv_tensor* tensors_host, int32_t n_tensors, int64_t n_rows,
@@ -84,11 +103,29 @@ extern "C" int wrs_kv_reorder(wrs_ctx* ctx, const wrs_kv_tensor* tensors_host, i
     WRS_CUDA(ctx, cudaSetDevice(ctx->device));
     for (int32_t i = 0; i < n_tensors; ++i) {
         const wrs_kv_tensor& t = tensors_host[i];
-        if (t.row_bytes < 0 || (t.row_bytes > 0 && (!t.src || !t.dst)))
+        if (t.row_bytes < 0 || (t.row_bytes > 0 && !t.src))
             return fail(ctx, WRS_ERR_INVALID, "wrs_kv_reorder: tensor with null pointer or negative row size");
+        if (t.group_invariant) {                          // skipped: the gather would reproduce src bit for bit
+            const int g = ctx->opt_kv_verify_group;
+            if (g > 0 && t.row_bytes > 0) {
+                if (n_rows % g != 0) return fail(ctx, WRS_ERR_INVALID, "wrs_kv_reorder: kv_verify_group does not divide n_rows");
+                const dim3 grid((unsigned)std::min<int64_t>(64, (t.row_bytes + 255) / 256), (unsigned)std::min<int64_t>(n_rows, 1024));
+                kv_verify_kernel<<<grid, 256, 0, stream>>>(static_cast<const unsigned char*>(t.src), t.row_bytes, (int)n_rows, g, source_idx, ctx->d_status);
+                WRS_CUDA(ctx, cudaGetLastError());
+            }
+            continue;
+        }
+        if (t.row_bytes > 0 && !t.dst) return fail(ctx, WRS_ERR_INVALID, "wrs_kv_reorder: tensor with null dst");
         if (t.row_bytes > 0 && t.src == t.dst)
             return fail(ctx, WRS_ERR_INVALID, "wrs_kv_reorder: src and dst must be different buffers (the reference's index() allocates too)");
     }
+    // the tensors that do move
+    std::vector<wrs_kv_tensor> moving;
+    moving.reserve(n_tensors);
+    for (int32_t i = 0; i < n_tensors; ++i)
+        if (!tensors_host[i].group_invariant) moving.push_back(tensors_host[i]);
+    tensors_host = moving.data();
+    n_tensors = (int32_t)moving.size();
     for (int32_t base = 0; base < n_tensors; base += kKvMaxTensors) {
         KvParams p;
         p.n_tensors = std::min<int32_t>(kKvMaxTensors, n_tensors - base);

@@ -573,6 +573,30 @@ __global__ void pad_or_trim_kernel(const float* __restrict__ in, int64_t rows, i
     }
 }
 
+// 16-bit PCM -> f32 mono: what the reference's decode loop does between the codec and the tensor (src/audio.rs:116-131):
+// SampleBuffer<f32> conversion (s / 32768, exact) and, for several channels, the mean of each interleaved frame summed
+// left to right in f32.
+__global__ void __launch_bounds__(256) pcm_i16_kernel(const short* __restrict__ in, long long n_frames, int channels, float* __restrict__ out) {
+    const long long stride = (long long)gridDim.x * blockDim.x, i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    constexpr float k = 1.0f / 32768.0f;
+    if (channels == 1) {
+        const bool vec = ((reinterpret_cast<uintptr_t>(in) & 7) | (reinterpret_cast<uintptr_t>(out) & 15)) == 0;
+        const long long n4 = vec ? n_frames >> 2 : 0;
+        for (long long i = i0; i < n4; i += stride) {
+            const short4 v = reinterpret_cast<const short4*>(in)[i];
+            reinterpret_cast<float4*>(out)[i] = make_float4(v.x * k, v.y * k, v.z * k, v.w * k);
+        }
+        for (long long i = (n4 << 2) + i0; i < n_frames; i += stride) out[i] = in[i] * k;
+    } else {
+        for (long long i = i0; i < n_frames; i += stride) {
+            const short* f = in + i * channels;
+            float sum = 0.0f;
+            for (int c = 0; c < channels; ++c) sum += f[c] * k;
+            out[i] = sum / (float)channels;
+        }
+    }
+}
+
 static bool g_tables_ready[64] = {false};
 
 static int init_tables(wrs_ctx* ctx) {
@@ -804,6 +828,79 @@ int wrs_logmel_batch_host(wrs_ctx* ctx, const float* pcm_host, int64_t n_segment
     WRS_CUDA(ctx, cudaStreamSynchronize(ctx->d2h_stream));
     WRS_CUDA(ctx, cudaStreamSynchronize(ctx->h2d_stream));
     // a synchronous call reports what its kernels left in the status word (an expired bounded wait means wrong data)
+    return wrs_ctx_check(ctx, (wrs_stream_t)s);
+}
+
+int wrs_pcm_i16_to_f32(wrs_ctx* ctx, const int16_t* pcm_i16, int64_t n_frames, int32_t channels, float* out, wrs_stream_t stream) {
+    using namespace wrs;
+    if (!ctx) return fail(nullptr, WRS_ERR_INVALID, "wrs_pcm_i16_to_f32: null ctx");
+    if (n_frames == 0) return WRS_OK;
+    if (!pcm_i16 || !out || n_frames < 0 || channels < 1) return fail(ctx, WRS_ERR_INVALID, "wrs_pcm_i16_to_f32: bad arguments");
+    WRS_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int grid = (int)std::min<int64_t>((n_frames / (channels == 1 ? 4 : 1) + 255) / 256 + 1, (int64_t)ctx->sm_count * 16);
+    pcm_i16_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(pcm_i16, n_frames, channels, out);
+    WRS_CUDA(ctx, cudaGetLastError());
+    return WRS_OK;
+}
+
+int wrs_logmel_batch_host_i16(wrs_ctx* ctx, const int16_t* pcm_host, int64_t n_segments, int64_t n_samples,
+                              int64_t seg_stride, float* out_host) {
+    using namespace wrs;
+    if (!ctx) return fail(nullptr, WRS_ERR_INVALID, "wrs_logmel_batch_host_i16: null ctx");
+    if (n_segments == 0) return WRS_OK;
+    if (!pcm_host || !out_host || n_segments < 0 || n_samples < WRS_N_FFT || seg_stride < n_samples)
+        return fail(ctx, WRS_ERR_INVALID, "wrs_logmel_batch_host_i16: bad arguments");
+    WRS_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int64_t n_frames = n_samples / WRS_HOP_LENGTH;
+    const size_t n_in = (size_t)((n_segments - 1) * seg_stride + n_samples);
+    const size_t out_bytes = sizeof(float) * n_segments * WRS_N_MELS * n_frames;
+    if (n_in * sizeof(int16_t) > ctx->stage_i16_bytes) {
+        cudaFree(ctx->d_stage_i16); ctx->d_stage_i16 = nullptr; ctx->stage_i16_bytes = 0;
+        WRS_CUDA(ctx, cudaMalloc(&ctx->d_stage_i16, n_in * sizeof(int16_t)));
+        ctx->stage_i16_bytes = n_in * sizeof(int16_t);
+    }
+    if (n_in * sizeof(float) > ctx->stage_in_bytes) {
+        cudaFree(ctx->d_stage_in); ctx->d_stage_in = nullptr; ctx->stage_in_bytes = 0;
+        WRS_CUDA(ctx, cudaMalloc(&ctx->d_stage_in, n_in * sizeof(float)));
+        ctx->stage_in_bytes = n_in * sizeof(float);
+    }
+    if (out_bytes > ctx->stage_out_bytes) {
+        cudaFree(ctx->d_stage_out); ctx->d_stage_out = nullptr; ctx->stage_out_bytes = 0;
+        WRS_CUDA(ctx, cudaMalloc(&ctx->d_stage_out, out_bytes));
+        ctx->stage_out_bytes = out_bytes;
+    }
+    if (!ctx->h2d_stream) {
+        WRS_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->h2d_stream, cudaStreamNonBlocking));
+        WRS_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->d2h_stream, cudaStreamNonBlocking));
+        for (int i = 0; i < wrs_ctx::kHostChunks; ++i) {
+            WRS_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_in[i], cudaEventDisableTiming));
+            WRS_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_done[i], cudaEventDisableTiming));
+        }
+    }
+    // the same three-stream pipeline as wrs_logmel_batch_host, with half the bytes on the way in and one small conversion
+    // launch per chunk in front of the log-mel launch
+    const int64_t per_chunk = std::max<int64_t>(4, (n_segments + wrs_ctx::kHostChunks - 1) / wrs_ctx::kHostChunks);
+    const int64_t out_per_seg = (int64_t)WRS_N_MELS * n_frames;
+    cudaStream_t s = ctx->own_stream;
+    int c = 0;
+    for (int64_t s0 = 0; s0 < n_segments; s0 += per_chunk, ++c) {
+        const int64_t ns = std::min(per_chunk, n_segments - s0);
+        const int64_t n_el = (ns - 1) * seg_stride + n_samples;
+        WRS_CUDA(ctx, cudaMemcpyAsync(ctx->d_stage_i16 + s0 * seg_stride, pcm_host + s0 * seg_stride, sizeof(int16_t) * n_el,
+                                      cudaMemcpyHostToDevice, ctx->h2d_stream));
+        WRS_CUDA(ctx, cudaEventRecord(ctx->ev_in[c], ctx->h2d_stream));
+        WRS_CUDA(ctx, cudaStreamWaitEvent(s, ctx->ev_in[c], 0));
+        int rc = wrs_pcm_i16_to_f32(ctx, ctx->d_stage_i16 + s0 * seg_stride, n_el, 1, ctx->d_stage_in + s0 * seg_stride, (wrs_stream_t)s);
+        if (rc == WRS_OK)
+            rc = wrs_logmel_batch(ctx, ctx->d_stage_in + s0 * seg_stride, ns, n_samples, seg_stride, ctx->d_stage_out + s0 * out_per_seg, s);
+        if (rc != WRS_OK) { cudaDeviceSynchronize(); return rc; }
+        WRS_CUDA(ctx, cudaEventRecord(ctx->ev_done[c], s));
+        WRS_CUDA(ctx, cudaStreamWaitEvent(ctx->d2h_stream, ctx->ev_done[c], 0));
+        WRS_CUDA(ctx, cudaMemcpyAsync(out_host + s0 * out_per_seg, ctx->d_stage_out + s0 * out_per_seg,
+                                      sizeof(float) * ns * out_per_seg, cudaMemcpyDeviceToHost, ctx->d2h_stream));
+    }
+    WRS_CUDA(ctx, cudaStreamSynchronize(ctx->d2h_stream));
+    WRS_CUDA(ctx, cudaStreamSynchronize(ctx->h2d_stream));
     return wrs_ctx_check(ctx, (wrs_stream_t)s);
 }
 

@@ -33,7 +33,7 @@ struct DevStatus {
     int timeout;
     int nan_rows;
     int bad_index;      // K3: a source index outside [0, n_rows)
-    int pad;
+    int group_violation;   // K3 (option kv_verify_group): a tensor flagged group-invariant is not, or an index leaves its group
 };
 
 }  // namespace wrs
@@ -48,12 +48,14 @@ struct wrs_ctx {
     int64_t seg_cap = 0;
     wrs::DevStatus* d_status = nullptr;
     int opt_logmel_fused = -1;             // -1 auto, 0 two-pass, 1 fused
+    int opt_kv_verify_group = 0;           // > 0: beam size to verify group-invariant KV tensors against (debug)
     int64_t stat_last_logmel_mode = -1;
     int64_t stat_last_logmel_grid = 0;
     int logmel_max_ctas_per_sm = 0;
     // host staging for *_host entry points
     float* d_stage_in = nullptr; size_t stage_in_bytes = 0;
     float* d_stage_out = nullptr; size_t stage_out_bytes = 0;
+    int16_t* d_stage_i16 = nullptr; size_t stage_i16_bytes = 0;
     cudaStream_t own_stream = nullptr;
     // *_host pipeline: copy-in and copy-out streams beside own_stream, one event pair per chunk in flight
     cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
