@@ -84,6 +84,7 @@ struct StepParams {
     // unit dealing of the scan launch (run_in_row), set by launch_step: every row is cut into rt text runs and rs
     // timestamp runs of consecutive units; a run never crosses a partition
     int rt, rs, rpr, n_runs, t_base, t_rem, s_base, s_rem; unsigned long long rpr_magic;
+    int npw;                                             // runs per warp of the scan launch: warp w takes runs [w npw, (w + 1) npw)
     RuleCfg rc;
     int ts_split, n_text_units, n_ts_units, upr, bm_words;
     const uint32_t* bm;
@@ -833,9 +834,9 @@ __device__ __forceinline__ void beam_fast(const StepParams& p, int audio, const 
 
 // ---- where the units of a warp's runs live.  A run's units are consecutive units of one partition of one row: the
 //      walker steps through them with one addition and recomputes everything else only when the next run begins
-//      (run g + stride of the same warp; beyond n_runs the walker is exhausted)
+//      (run g + 1 of the same warp; at g_end the walker is exhausted)
 struct Walk {
-    int g;               // run
+    int g, g_end;        // run, and the run behind the warp's last one
     int row, part, pe;   // the run's row, partition (0 text, 1 timestamps) and the id the partition's ids end at
     int j, j0, j_end;    // current unit in row, the run's first unit and the unit behind its last one
     int a0;              // id of the unit's first element slot: 16-byte aligned in memory, up to 3 ids in front of the partition
@@ -854,10 +855,9 @@ __device__ __forceinline__ void walk_enter(const StepParams& p, Walk& w) {    //
         w.a0 = p.ts_split + (w.j - p.n_text_units) * kUnit - (int)((reinterpret_cast<uintptr_t>(w.rp + p.ts_split) >> 2) & 3);
     }
 }
-__device__ __forceinline__ void walk_step(const StepParams& p, Walk& w, int stride) {
+__device__ __forceinline__ void walk_step(const StepParams& p, Walk& w) {
     if (++w.j < w.j_end) { w.a0 += kUnit; return; }
-    w.g += stride;
-    if (w.g < p.n_runs) walk_enter(p, w);
+    if (++w.g < w.g_end) walk_enter(p, w);
 }
 // 16-byte chunks [c_lo, c_hi) of the unit that are bulk-copied: those that hold ids of the partition, except a chunk that
 // would reach outside the logits buffer (before row 0, behind the last row), whose <= 3 ids are read one by one instead
@@ -879,22 +879,20 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const Step
     unsigned long long* bars = reinterpret_cast<unsigned long long*>(slice + kStages * kStageBytes + kScanScratch);
     auto stage_of = [&](int s) { return reinterpret_cast<float4*>(s == 0 ? slice : slice + kScanScratch + s * kStageBytes); };
 
-    // Runs are dealt to the grid's warps round-robin over the CTAs: consecutive runs belong to the same row, and rows whose
-    // rules mask most of a partition cost next to nothing -- interleaved, every SM gets the same mix of cheap and full runs
-    const int stride = (int)gridDim.x * kStepWarps;
-#ifdef WRS_DEAL_BLOCKED
-    const int gw = (int)blockIdx.x * kStepWarps + warp;
-#else
+    // Every warp takes a block of npw consecutive runs (one run when the rows allow it); consecutive blocks go to
+    // different CTAs: consecutive runs belong to the same row, and rows whose rules mask most of a partition cost next to
+    // nothing -- interleaved, every SM gets the same mix of cheap and full runs.  (A block, not a stride: with text and
+    // timestamp runs alternating, a stride would hand some warps nothing but long text runs.)
     const int gw = warp * (int)gridDim.x + (int)blockIdx.x;
-#endif
-    if (gw >= p.n_runs) return;
+    if (gw * p.npw >= p.n_runs) return;
 #ifdef WRS_TRACE
     if (lane == 0) for (int q = 0; q < 8; ++q) g_trace[gw * 8 + q] = 0;
 #endif
     WRS_TR(0);
 
     Walk wi;                                              // the next unit to request
-    wi.g = gw;
+    wi.g = gw * p.npw;
+    wi.g_end = min(wi.g + p.npw, p.n_runs);
     walk_enter(p, wi);
     Walk wf = wi;                                         // the unit being folded
     // start the flight of the next unit not yet requested into the next stage: one bulk copy, completion by byte
@@ -913,7 +911,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const Step
                 mbar_arrive(bar);
             }
         }
-        walk_step(p, wi, stride);
+        walk_step(p, wi);
         stage_issue = stage_issue + 1 == kStages ? 0 : stage_issue + 1;
     };
     if (lane == 0) {
@@ -933,7 +931,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const Step
         pen = p.cur_len >= 2 ? rt[p.cur_len - 2] : 0;
     };
     int64_t tk_last, tk_pen;
-    load_tokens(gw, tk_last, tk_pen);
+    load_tokens(wi.g, tk_last, tk_pen);
     // lane l takes bitmap word (first id of the unit >> 5) + l: 29 words cover the unit
     auto bitmap_of = [&](const Walk& q) { return __ldg(p.bm + min((max(q.a0, 0) >> 5) + lane, p.bm_words - 1)); };
     // bring the unit into registers; slot j of a lane holds ids a0 + 4 (lane + 32 j) ..+3, everything outside [lo, hi)
@@ -991,20 +989,21 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const Step
     RowRules rules;
     rules.t_lo = rules.t_hi = rules.s_lo = rules.s_hi = 0; rules.flags = 0;
 
-    while (wf.g < p.n_runs) {
+    const int g_end = wi.g_end;
+    while (wf.g < g_end) {
         const Walk q = wf;
         const uint32_t bmw = bm_c;
         if (q.j == q.j0) {                               // a run begins: its row's rules; request the next run's tokens
             rules = row_rules_from(p.rc, tk_last, tk_pen, p.cur_len, p.sample_begin);
-            if (q.g + stride < p.n_runs) load_tokens(q.g + stride, tk_last, tk_pen);
+            if (q.g + 1 < g_end) load_tokens(q.g + 1, tk_last, tk_pen);
         }
         // ids of the unit that survive the row's rules
         Geom g;
         g.row = q.row; g.part = q.part; g.a0 = q.a0;
         g.lo = max(max(q.a0, q.part ? p.ts_split : 0), q.part ? rules.s_lo : rules.t_lo);
         g.hi = min(min(q.a0 + kUnit, q.pe), q.part ? rules.s_hi : rules.t_hi);
-        walk_step(p, wf, stride);
-        if (wf.g < p.n_runs) bm_c = bitmap_of(wf);
+        walk_step(p, wf);
+        if (wf.g < g_end) bm_c = bitmap_of(wf);
 #ifdef WRS_TRACE
         const unsigned long long tw0 = gtime();
 #endif
@@ -1020,7 +1019,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const Step
             WRS_TR(1);
 #pragma unroll
             for (int k2 = 1; k2 < kStages; ++k2)
-                if (wi.g < p.n_runs) issue_next();
+                if (wi.g < g_end) issue_next();
         }
         if (g.hi > g.lo) {
             float x[kNV][4];
@@ -1031,7 +1030,7 @@ __global__ void __launch_bounds__(kStepThreads, 1) decode_scan_kernel(const Step
 #ifdef WRS_TRACE
         WRS_TR_ADD(5, gtime() - tw1);
 #endif
-        if (wi.g < p.n_runs) issue_next();
+        if (wi.g < g_end) issue_next();
         if (++stage == kStages) { stage = 0; phase ^= 1u; }
         WRS_TR(2);
         if (q.j + 1 < q.j_end) continue;
@@ -1252,6 +1251,7 @@ int launch_step(wrs_decoder* dec, StepParams p, cudaStream_t stream) {
         if (n_runs >= (1ll << 31) || n_runs * (p.rpr - 1) >= (1ll << 40))
             return fail(ctx, WRS_ERR_UNSUPPORTED, "decode step: n_rows x runs per row too large for the unit dealing");
         p.n_runs = (int)n_runs;
+        p.npw = (int)((n_runs + Wt - 1) / Wt);
         p.rpr_magic = ((1ull << 40) + (uint64_t)p.rpr - 1) / (uint64_t)p.rpr;
     }
 #ifdef WRS_TRACE
