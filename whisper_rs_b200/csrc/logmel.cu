@@ -244,7 +244,7 @@ __device__ __forceinline__ void finalizer_warp(const LogmelParams& p, int lane) 
             bool complete;
             key = fold_slots(p, seg, lane, complete);
             if (complete) break;
-            __nanosleep(spins < 8 ? 256 : 1024);
+            __nanosleep(1500);
             if (++spins > (1 << 21)) { if (lane == 0) atomicExch(&p.status->timeout, 1); break; }
         }
         // the slice's rows were stored by this CTA's BC warps before they posted its word: acquire at CTA scope
