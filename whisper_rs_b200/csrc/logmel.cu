@@ -774,6 +774,11 @@ static int logmel_batch_impl(wrs_ctx* ctx, const char* who_, const float* pcm, i
 
 extern "C" {
 
+// segments per chunk of the *_host pipelines (option "host_chunk_segments" overrides): small enough that copy-in,
+// kernel and copy-out of different chunks overlap, large enough that the per-chunk API calls do not bound the call
+// (tools/host_chunks.py: f32 23.0 / 25.8 / 25.6 / 24.4 / 22.0 k segments/s at 2 / 4 / 8 / 16 / 32 segments per chunk)
+constexpr int64_t kHostChunkSegments = 4;
+
 int wrs_logmel_batch_host(wrs_ctx* ctx, const float* pcm_host, int64_t n_segments, int64_t n_samples,
                           int64_t seg_stride, float* out_host) {
     using namespace wrs;
@@ -806,7 +811,8 @@ int wrs_logmel_batch_host(wrs_ctx* ctx, const float* pcm_host, int64_t n_segment
             WRS_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_done[i], cudaEventDisableTiming));
         }
     }
-    const int64_t per_chunk = std::max<int64_t>(4, (n_segments + wrs_ctx::kHostChunks - 1) / wrs_ctx::kHostChunks);
+    const int64_t per_chunk = std::max<int64_t>(ctx->opt_host_chunk_segments > 0 ? ctx->opt_host_chunk_segments : kHostChunkSegments,
+                                                (n_segments + wrs_ctx::kHostChunks - 1) / wrs_ctx::kHostChunks);
     const int64_t out_per_seg = (int64_t)WRS_N_MELS * n_frames;
     cudaStream_t s = ctx->own_stream;
     int c = 0;
@@ -879,7 +885,10 @@ int wrs_logmel_batch_host_i16(wrs_ctx* ctx, const int16_t* pcm_host, int64_t n_s
     }
     // the same three-stream pipeline as wrs_logmel_batch_host, with half the bytes on the way in and one small conversion
     // launch per chunk in front of the log-mel launch
-    const int64_t per_chunk = std::max<int64_t>(4, (n_segments + wrs_ctx::kHostChunks - 1) / wrs_ctx::kHostChunks);
+    // (larger chunks than the f32 call: with half the bytes per segment the per-chunk API calls weigh twice as much --
+    // measured 32.3 k segments/s at 4 segments per chunk, 37.7 k at 16)
+    const int64_t per_chunk = std::max<int64_t>(ctx->opt_host_chunk_segments > 0 ? ctx->opt_host_chunk_segments : 4 * kHostChunkSegments,
+                                                (n_segments + wrs_ctx::kHostChunks - 1) / wrs_ctx::kHostChunks);
     const int64_t out_per_seg = (int64_t)WRS_N_MELS * n_frames;
     cudaStream_t s = ctx->own_stream;
     int c = 0;
