@@ -189,6 +189,30 @@ def test_config2_batch64_properties():
     assert torch.all(rng_ <= 2.0 + 1e-6)                             # max-8 floor then /4
 
 
+def test_fused_floor_skipping_is_bit_identical_to_the_unconditional_floor():
+    """The fused kernel leaves a slice alone when its minimum is already at or above max - 8 (src/audio.rs:256 would
+    not change it); the two-launch form floors every element.  Same bits, on a batch deep enough (110 x 47 slices over
+    148 CTAs = 35 per CTA) to wrap the per-CTA ring of slice minima, with kinds that skip (gaussian, zeros) and kinds
+    that do not (tone, burst, chirp) interleaved."""
+    ctx = _lib.context(0)
+    pcm = synth.audio_batch(110, seed=7)
+    x = torch.from_numpy(pcm).cuda()
+    fused = audio.log_mel_spectrogram_batch(x)
+    assert ctx.get_stat("logmel_mode") == 1
+    ctx.set_option("logmel_fused", 0)
+    try:
+        plain = audio.log_mel_spectrogram_batch(x)
+        assert ctx.get_stat("logmel_mode") == 0
+    finally:
+        ctx.set_option("logmel_fused", 1)
+    torch.cuda.synchronize()
+    ctx.check()
+    assert torch.equal(fused, plain)
+    for s in (0, 1, 2, 3, 4, 5, 109):
+        want = oa.log_mel_spectrogram(torch.from_numpy(pcm[s]), oa.mel_filter())
+        assert (fused[s].cpu() - want).abs().max().item() <= TOL, s
+
+
 @pytest.mark.parametrize("channels", [1, 2, 3, 6])
 def test_pcm_i16_conversion_and_downmix_bit_exact(channels):
     """src/audio.rs:116-131: s / 32768 and the per-frame mean summed left to right in f32 -- integer input, bit-exact."""

@@ -78,7 +78,11 @@ struct LogmelSmem {
     unsigned long long y_full[2], y_empty[2];        // mbarriers: half h of Y written by all A warps / read by all BC warps
     int cls_begin[kBWarps][MelBank::kClasses + 1];   // MelBank::cls_begin
     int red_max;                                     // max key of the slice in progress (reset by the last warp to add to it)
+    int red_min;                                     // min key likewise (never a NaN: fminf drops them)
     int warps_done;
+    // The finalizer of this CTA reads the minimum of its k-th slice here ({k, key}; 32 slices deep, an entry that has
+    // been overwritten by a later slice just means "take the floor unconditionally").
+    unsigned long long min_ring[32];                 // (k << 32 | key): one 8-byte word, read and written whole
 };
 static_assert(sizeof(LogmelSmem) <= 227 * 1024, "log-mel working set exceeds the 227 KB a CTA can own");
 
@@ -234,11 +238,12 @@ __device__ __forceinline__ void floor_slice(float* __restrict__ outp, int64_t n_
 // is known.  Every slice of a segment is owned by a CTA that is running or has finished (persistent grid no larger
 // than what is co-resident: cooperative launch), and the warps that produce slices never wait for a finalizer, so the
 // wait ends; the bound is a safety net (WRS_ERR_TIMEOUT through wrs_ctx_check).
-__device__ __forceinline__ void finalizer_warp(const LogmelParams& p, int lane) {
+__device__ __forceinline__ void finalizer_warp(LogmelSmem& sm, const LogmelParams& p, int lane) {
     const int step_seg = (int)gridDim.x / p.slices_per_seg, step_sl = (int)gridDim.x % p.slices_per_seg;
     int seg = (int)blockIdx.x / p.slices_per_seg, sl = (int)blockIdx.x % p.slices_per_seg;
     const bool ovec = p.vec_out != 0;
-    for (int slice = blockIdx.x; slice < p.total_slices; slice += gridDim.x) {
+    int kf = 0;
+    for (int slice = blockIdx.x; slice < p.total_slices; slice += gridDim.x, ++kf) {
         int spins = 0, key;
         for (;;) {
             bool complete;
@@ -249,8 +254,12 @@ __device__ __forceinline__ void finalizer_warp(const LogmelParams& p, int lane) 
         }
         // the slice's rows were stored by this CTA's BC warps before they posted its word: acquire at CTA scope
         __threadfence_block();
+        // a slice whose smallest value is already at or above the floor has nothing to change (a NaN maximum compares
+        // false and takes the floor everywhere, as torch.maximum does)
+        const unsigned long long mn = *reinterpret_cast<const volatile unsigned long long*>(&sm.min_ring[kf & 31]);
+        const bool untouched = (int)(mn >> 32) == kf && key_float((int)(unsigned)mn) >= key_float(key) - 8.0f;
         const int fs = sl * kTW, nf = min(kTW, p.n_frames - fs);
-        floor_slice(p.out + ((int64_t)seg * WRS_N_MELS) * p.n_frames + fs, p.n_frames, nf, scale4(key_float(key) - 8.0f), lane, ovec);
+        if (!untouched) floor_slice(p.out + ((int64_t)seg * WRS_N_MELS) * p.n_frames + fs, p.n_frames, nf, scale4(key_float(key) - 8.0f), lane, ovec);
         seg += step_seg; sl += step_sl;
         if (sl >= p.slices_per_seg) { sl -= p.slices_per_seg; ++seg; }
     }
@@ -328,7 +337,7 @@ __device__ __forceinline__ void stage_b_store(LogmelSmem& sm, int q, int fp, boo
 struct MelRowCtx {
     const int4* rows; const char* pbase; const char* wbase; float* obase; int n_frames; bool ok0, ok1;
 };
-__device__ __forceinline__ void mel_flush(const MelRowCtx& mc, f32x2 acc, int m, float& lmax) {
+__device__ __forceinline__ void mel_flush(const MelRowCtx& mc, f32x2 acc, int m, float& lmax, float& lmin) {
     float a0, a1;
     unpack2(acc, a0, a1);
 #ifdef WRS_EXP_NO_LOG
@@ -343,8 +352,8 @@ __device__ __forceinline__ void mel_flush(const MelRowCtx& mc, f32x2 acc, int m,
     if (mc.ok0) lmax = fmax_nan(lmax, scale4(v0));
     if (mc.ok1) lmax = fmax_nan(lmax, scale4(v1));
 #else
-    if (mc.ok0) { orow[0] = scale4(v0); lmax = fmax_nan(lmax, v0); }
-    if (mc.ok1) { orow[16] = scale4(v1); lmax = fmax_nan(lmax, v1); }
+    if (mc.ok0) { orow[0] = scale4(v0); lmax = fmax_nan(lmax, v0); lmin = fminf(lmin, v0); }
+    if (mc.ok1) { orow[16] = scale4(v1); lmax = fmax_nan(lmax, v1); lmin = fminf(lmin, v1); }
 #endif
 }
 // one row of a fixed-length class in flight: its description, N power values and N weights
@@ -361,7 +370,7 @@ __device__ __forceinline__ void mel_row_load(const MelRowCtx& mc, int idx, MelRo
     for (int j = 0; j < N; ++j) r.q[j] = pp[j * 32];
 }
 template <int N>
-__device__ __forceinline__ void mel_row_finish(const MelRowCtx& mc, const MelRowRegs<N>& r, float& lmax) {
+__device__ __forceinline__ void mel_row_finish(const MelRowCtx& mc, const MelRowRegs<N>& r, float& lmax, float& lmin) {
     f32x2 acc0 = mul_(pack2(r.q[0].x, r.q[0].y), pack2(r.w2[0].x, r.w2[0].x));
     f32x2 acc1 = mul_(pack2(r.q[1].x, r.q[1].y), pack2(r.w2[0].y, r.w2[0].y));
 #pragma unroll
@@ -369,20 +378,20 @@ __device__ __forceinline__ void mel_row_finish(const MelRowCtx& mc, const MelRow
         acc0 = fma_(pack2(r.q[2 * j].x, r.q[2 * j].y), pack2(r.w2[j].x, r.w2[j].x), acc0);
         acc1 = fma_(pack2(r.q[2 * j + 1].x, r.q[2 * j + 1].y), pack2(r.w2[j].y, r.w2[j].y), acc1);
     }
-    mel_flush(mc, add_(acc0, acc1), r.m, lmax);
+    mel_flush(mc, add_(acc0, acc1), r.m, lmax, lmin);
 }
 // rows [b, e) of class N (N bins each): a row's loads all go out before its arithmetic
 template <int N>
-__device__ __forceinline__ void mel_rows(const MelRowCtx& mc, int b, int e, float& lmax) {
+__device__ __forceinline__ void mel_rows(const MelRowCtx& mc, int b, int e, float& lmax, float& lmin) {
 #pragma unroll 1
     for (int i = b; i < e; ++i) {
         MelRowRegs<N> r;
         mel_row_load<N>(mc, i, r);
-        mel_row_finish<N>(mc, r, lmax);
+        mel_row_finish<N>(mc, r, lmax, lmin);
     }
 }
 // rows wider than the largest class: their own (even) number of bins
-__device__ __forceinline__ void mel_rows_wide(const MelRowCtx& mc, int b, int e, float& lmax) {
+__device__ __forceinline__ void mel_rows_wide(const MelRowCtx& mc, int b, int e, float& lmax, float& lmin) {
 #pragma unroll 1
     for (int i = b; i < e; ++i) {
         const int4 c = mc.rows[i];
@@ -396,7 +405,7 @@ __device__ __forceinline__ void mel_rows_wide(const MelRowCtx& mc, int b, int e,
             acc0 = fma_(pack2(q0.x, q0.y), pack2(wj.x, wj.x), acc0);
             acc1 = fma_(pack2(q1.x, q1.y), pack2(wj.y, wj.y), acc1);
         }
-        mel_flush(mc, add_(acc0, acc1), c.z, lmax);
+        mel_flush(mc, add_(acc0, acc1), c.z, lmax, lmin);
     }
 }
 
@@ -408,7 +417,7 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
 
     if (warp == kAWarps + kBWarps) {                     // the finalizer touches no shared memory: it starts at once
 #ifndef WRS_EXP_NO_F
-        if (FUSED) finalizer_warp(p, lane);
+        if (FUSED) finalizer_warp(sm, p, lane);
 #endif
         return;
     }
@@ -425,7 +434,7 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
             mbar_init(&sm.pcm_full[h], kAWarps); mbar_init(&sm.pcm_empty[h], kAWarps);
             mbar_init(&sm.y_full[h], kAWarps); mbar_init(&sm.y_empty[h], kBWarps);
         }
-        sm.red_max = float_key(-INFINITY); sm.warps_done = 0;
+        sm.red_max = float_key(-INFINITY); sm.red_min = float_key(INFINITY); sm.warps_done = 0;
     }
     asm volatile("bar.sync 2, %0;" ::"n"(kSetup) : "memory");   // the only barrier A and BC warps share: the roles part here
 
@@ -506,35 +515,42 @@ __global__ void __launch_bounds__(kThreads, 1) logmel_kernel(const LogmelParams 
         bar_bc();                                        // P complete
 
         // ---- stage C: banded mel projection (src/audio.rs:252), clamp + log10 (:254), raw rows -> HBM
-        float lmax = -INFINITY;
+        float lmax = -INFINITY, lmin = INFINITY;
 #ifndef WRS_EXP_NO_C
         {
             MelRowCtx mc;
             mc.rows = sm.rows; mc.pbase = pbase; mc.wbase = wbase;
             mc.obase = p.out + ((int64_t)seg * WRS_N_MELS) * p.n_frames + fs + fl;
             mc.n_frames = p.n_frames; mc.ok0 = fl < nf; mc.ok1 = fl + 16 < nf;
-            mel_rows<2>(mc, cb[0], cb[1], lmax);
-            mel_rows<4>(mc, cb[1], cb[2], lmax);
-            mel_rows<6>(mc, cb[2], cb[3], lmax);
-            mel_rows<8>(mc, cb[3], cb[4], lmax);
-            mel_rows<12>(mc, cb[4], cb[5], lmax);
-            mel_rows<16>(mc, cb[5], cb[6], lmax);
-            mel_rows_wide(mc, cb[6], cb[7], lmax);
+            mel_rows<2>(mc, cb[0], cb[1], lmax, lmin);
+            mel_rows<4>(mc, cb[1], cb[2], lmax, lmin);
+            mel_rows<6>(mc, cb[2], cb[3], lmax, lmin);
+            mel_rows<8>(mc, cb[3], cb[4], lmax, lmin);
+            mel_rows<12>(mc, cb[4], cb[5], lmax, lmin);
+            mel_rows<16>(mc, cb[5], cb[6], lmax, lmin);
+            mel_rows_wide(mc, cb[6], cb[7], lmax, lmin);
         }
 #endif
         // ---- per-slice max -> per-segment max (src/audio.rs:256 `log_spec.max()`); a NaN wins (its key is above +inf)
         {
-            int kmax = float_key(lmax);
+            int kmax = float_key(lmax), kmin = float_key(lmin);
             kmax = __reduce_max_sync(0xffffffffu, kmax);   // (also orders every lane's row stores before lane 0's fence)
+            kmin = __reduce_min_sync(0xffffffffu, kmin);
             // The last warp to add its maximum posts the slice: once the word is out the slice has posted, and its raw
             // rows are complete for the finalizer of this CTA (release at CTA scope; nobody else reads them).
             if (lane == 0) {
                 atomicMax(&sm.red_max, kmax);
+                atomicMin(&sm.red_min, kmin);
                 __threadfence_block();
                 if (atomicAdd(&sm.warps_done, 1) == kBWarps - 1) {
                     __threadfence_block();
                     const int key = atomicExch(&sm.red_max, float_key(-INFINITY));
+                    const int kmn = atomicExch(&sm.red_min, float_key(INFINITY));
                     atomicExch(&sm.warps_done, 0);
+                    if (FUSED) {
+                        *reinterpret_cast<volatile unsigned long long*>(&sm.min_ring[k & 31u]) = ((unsigned long long)k << 32) | (unsigned)kmn;
+                        __threadfence_block();
+                    }
                     if (FUSED) st_relaxed(p.slice_max + (int64_t)seg * p.slices_per_seg + sl, key);
                     else atomicMax(p.seg_max + seg, key);
                 }
