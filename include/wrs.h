@@ -198,6 +198,32 @@ int wrs_greedy_step(wrs_decoder* dec, const float* logits, int64_t row_stride, i
                     int64_t* next_tokens, int64_t next_stride, float* sum_logprobs_out, int32_t* completed,
                     const wrs_step_debug* dbg, wrs_stream_t stream);
 
+/* ---- the logits projection with the decode step as its epilogue.
+ * Reference: `x.matmul(&self.token_emb.ws.transpose(0, 1))` (src/model.rs:521), whose [n_rows, n_vocab] f32 result
+ * is what src/decode/mod.rs:257-270 then filters and extracts from.  Here the product runs on the tensor cores
+ * (tcgen05, bf16 hi/lo splits of both f32 operands, three products, f32 accumulation) and the decode step's row scan
+ * is the epilogue of each tile: the logits never reach HBM.  Accuracy: a logit differs from the f32 product sum by
+ * about 2^-16 of sum |x_i w_i| (NOT f32-faithful; the tolerance is stated in tests/test_gpu_project.py).
+ *
+ * wrs_projection_create packs `token_emb` (DEVICE [n_vocab][emb_stride] f32, the rows of TextDecoder::token_emb,
+ * src/model.rs:463) for `dec`'s vocabulary geometry; n_state a multiple of 32.  The packed copy (4 bytes per weight)
+ * belongs to the projection; token_emb may be freed once `stream` has run the packing. */
+typedef struct wrs_projection wrs_projection;
+int wrs_projection_create(wrs_decoder* dec, const float* token_emb, int64_t emb_stride, int32_t n_state, wrs_stream_t stream,
+                          wrs_projection** out);
+void wrs_projection_destroy(wrs_projection* proj);
+
+/* The projection alone: logits[r][v] = sum_i x[r][i] token_emb[v][i]  (src/model.rs:521).  x DEVICE [n_rows][x_stride]
+ * f32 (the output of TextDecoder::ln, src/model.rs:519), 16-byte aligned, x_stride a multiple of 4. */
+int wrs_project_logits(wrs_projection* proj, const float* x, int64_t x_stride, int64_t n_rows, float* logits,
+                       int64_t row_stride, wrs_stream_t stream);
+
+/* src/model.rs:521 + wrs_beam_step in one pass: same outputs and semantics as wrs_beam_step on the projected logits. */
+int wrs_project_beam_step(wrs_projection* proj, const float* x, int64_t x_stride, int64_t n_rows, const int64_t* tokens,
+                          int64_t tok_stride, int64_t cur_len, int64_t sample_begin, const float* sum_logprobs_in,
+                          int64_t* next_tokens, int64_t next_stride, int32_t* source_idx, float* sum_logprobs_out,
+                          int32_t* completed, const wrs_step_debug* dbg, wrs_stream_t stream);
+
 /* BeamSearchTokenExtractor::finalize  src/decode/extractor/beam_search.rs:151-206.  Synchronises `stream`,
  * copies the finished store and the live beams to the host and returns, per audio, exactly
  * max(beam, stored) candidates ordered (score desc, sequence lexicographic):

@@ -20,6 +20,7 @@
 
 #include "async_copy.cuh"
 #include "decode_scan.cuh"
+#include "decode_proj.cuh"
 #include "logmel_fft.cuh"   // packed FP32 helpers (f32x2)
 #include "wrs_internal.cuh"
 
@@ -46,6 +47,16 @@ struct wrs_decoder {
     int32_t* d_fin_n = nullptr;       // [max_audio]
     int32_t* d_sync = nullptr;        // [2] arrive counter, full counter
     bool smem_attr_set = false;
+};
+
+// the token embedding of one model packed for proj_kernel, bound to a decoder's vocab geometry
+struct wrs_projection {
+    wrs_decoder* dec = nullptr;
+    int n_state = 0, n_tiles = 0, n_text_tiles = 0, n_kstages = 0, max_mtiles = 0;
+    unsigned char* d_wp = nullptr;    // packed weights
+    unsigned char* d_xp = nullptr;    // packed x of the step in flight, [max_mtiles]
+    unsigned char* d_parts = nullptr; // [max_rows][n_tiles] records of the largest K
+    bool attr_set = false;
 };
 
 namespace wrs {
@@ -93,6 +104,7 @@ struct StepParams {
     const float* sum_in; float* sum_out;
     int64_t* next_tokens; int64_t next_stride; int32_t* source_idx; int32_t* completed;
     int64_t* fin_tokens; int32_t* fin_len; double* fin_score; int32_t* fin_n; int32_t* sync;
+    const unsigned char* proj_parts; int proj_tiles, proj_text_tiles, proj_rec;   // projection mode: the tail merges proj_kernel's records
     float* dbg_lp; int32_t* dbg_tok; uint8_t* dbg_flags; int32_t* dbg_fin_count; int32_t* dbg_fin_source; double* dbg_fin_score;
     DevStatus* status;
 };
@@ -535,6 +547,101 @@ __device__ __forceinline__ RowOut merge_row(const StepParams& p, int row, const 
         }
     }
     if (rescan) rescan_row(p, row, rr, ts_over_text, wb, ov, oi);
+    r.tok = oi;
+    r.lp = (ov - Mx) - logtot;
+    return r;
+}
+
+
+// Projection mode (decode_proj.cuh): the row's list is one record per vocab tile, {max, sum, -, -} v[Kp] id[Kp], whose
+// v / id are the tile's exact best IDS in (value desc, id asc) order -- so the best K of their union are the row's best K,
+// ties included, and there is nothing to read again.  Lane l takes tiles l, l + 32, ...
+__device__ __forceinline__ RowOut merge_row_proj(const StepParams& p, int row, WarpBuf& wb) {
+    const int lane = threadIdx.x & 31;
+    const int K = p.K, Kp = (K + 1) & ~1;
+    const unsigned char* __restrict__ recs = p.proj_parts + (int64_t)row * p.proj_tiles * p.proj_rec;
+    // ---- pass A: partition maxima and sums, folded lane-locally first
+    float am0 = -CUDART_INF_F, am1 = -CUDART_INF_F, as0 = 0.0f, as1 = 0.0f;
+    bool nan_seen = false;
+    for (int t = lane; t < p.proj_tiles; t += 32) {
+        const float4 h = __ldcg(reinterpret_cast<const float4*>(recs + (int64_t)t * p.proj_rec));
+        if (h.y != h.y) { nan_seen = true; continue; }
+        float& am = t < p.proj_text_tiles ? am0 : am1;
+        float& as = t < p.proj_text_tiles ? as0 : as1;
+        if (h.x > am) { as = as * exp_diff(am, h.x) + h.y; am = h.x; }
+        else as += h.y * exp_diff(h.x, am);
+    }
+    float M[2], S[2];
+    {
+        M[0] = warp_max(am0); M[1] = warp_max(am1);
+        float s0 = as0 * exp_diff(am0, M[0]), s1 = as1 * exp_diff(am1, M[1]);
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { s0 += __shfl_xor_sync(0xffffffffu, s0, o); s1 += __shfl_xor_sync(0xffffffffu, s1, o); }
+        S[0] = s0; S[1] = s1;
+    }
+    nan_seen = __any_sync(0xffffffffu, nan_seen);
+    RowOut r;
+    r.flags = 0u;
+    if (nan_seen) r.flags |= 128u;
+    float Tm = M[0], Ts = S[0];
+    const float Sm = M[1], Ss = S[1];
+    const float lse_s = (Ss > 0.0f) ? Sm + logf(Ss) : -CUDART_INF_F;
+    const bool ts_over_text = p.rc.timestamps && (lse_s > Tm);          // timestamp_tokens.rs:80-96
+    if (ts_over_text) { r.flags |= 8u; Tm = -CUDART_INF_F; Ts = 0.0f; }
+    const float Mx = fmaxf(Tm, Sm);
+    const float tot = Ts * exp_diff(Tm, Mx) + Ss * exp_diff(Sm, Mx);
+    const float logtot = nan_seen ? CUDART_NAN_F : logf(tot);
+    if (Mx == -CUDART_INF_F) r.flags |= 128u;
+#ifdef WRS_TRACE
+    r.t_sums = gtime(); r.t_cells = r.t_loaded = 0;
+#endif
+    // ---- pass B: a value at least K candidates reach (K rounds over the lanes' best heads), then everything at or above it
+    const int t_first = ts_over_text ? p.proj_text_tiles : 0;
+    float head = -CUDART_INF_F;
+    for (int t = lane; t < p.proj_tiles; t += 32)
+        if (t >= t_first) head = fmaxf(head, __ldcg(reinterpret_cast<const float*>(recs + (int64_t)t * p.proj_rec + 16)));
+    const float tau = kth_threshold(head, K);
+    for (int t = lane; t < p.proj_tiles; t += 32) {
+        if (t < t_first) continue;
+        const float* rv = reinterpret_cast<const float*>(recs + (int64_t)t * p.proj_rec + 16);
+        const int* ri = reinterpret_cast<const int*>(rv + Kp);
+        for (int e = 0; e < K; ++e) {
+            const float v = __ldcg(rv + e);
+            if (!(v >= tau) || v == -CUDART_INF_F) break;               // (lists are sorted)
+            const int slot = atomicAdd(&wb.n, 1);
+            if (slot < kCandCap) { wb.v[slot] = v; wb.id[slot] = __ldcg(ri + e); }
+        }
+    }
+    __syncwarp();
+    const int n = wb.n;
+    float ov = -CUDART_INF_F; int oi = INT32_MAX;
+    if (n <= kCandCap) {
+        bool dropped = false;
+        const int kept = warp_compact(wb, n, K, dropped);
+        if (lane < kept) { ov = wb.v[lane]; oi = wb.id[lane]; }
+    } else {
+        // massive ties: K rounds of "the best entry strictly after the previous pick" over the lane's lists
+        float pv = CUDART_INF_F; int pi = -1;
+        for (int rnd = 0; rnd < K; ++rnd) {
+            float bv = -CUDART_INF_F; int bi = INT32_MAX;
+            for (int t = lane; t < p.proj_tiles; t += 32) {
+                if (t < t_first) continue;
+                const float* rv = reinterpret_cast<const float*>(recs + (int64_t)t * p.proj_rec + 16);
+                const int* ri = reinterpret_cast<const int*>(rv + Kp);
+                for (int e = 0; e < K; ++e) {
+                    const float v = __ldcg(rv + e); const int id = __ldcg(ri + e);
+                    if (v == -CUDART_INF_F || !(v == v)) break;
+                    const bool after = v < pv || (v == pv && id > pi);
+                    if (after) { if (better(v, id, bv, bi)) { bv = v; bi = id; } break; }   // the first entry after the pick is the list's best
+                }
+            }
+            warp_pick(bv, bi);
+            if (bi == INT32_MAX) break;
+            if (lane == rnd) { ov = bv; oi = bi; }
+            pv = bv; pi = bi;
+        }
+    }
+    __syncwarp();
     r.tok = oi;
     r.lp = (ov - Mx) - logtot;
     return r;
@@ -1093,7 +1200,7 @@ __global__ void __launch_bounds__(kMaxBeam * 32) decode_tail_kernel(const StepPa
     if (lane == 0) wb.n = 0;
     __syncwarp();
     const RowRules rr_row = row_rules_from(p.rc, tk_last, tk_pen, p.cur_len, p.sample_begin);
-    RowOut r = merge_row(p, row, rr_row, wb, slice, glist);
+    RowOut r = p.proj_parts ? merge_row_proj(p, row, wb) : merge_row(p, row, rr_row, wb, slice, glist);
     r.flags |= rr_row.flags;
     unsigned same = 0u;
     if (MODE == MODE_BEAM) {
@@ -1214,18 +1321,50 @@ StepParams step_params(wrs_decoder* dec, const float* logits, int64_t row_stride
     return p;
 }
 
+// ---- projection mode (decode_proj.cuh): pack x, project + fold, then the same tail launch
+int proj_check(wrs_projection* pj, const char* who, const float* x, int64_t x_stride, int64_t n_rows) {
+    if (!pj) return fail(nullptr, WRS_ERR_INVALID, std::string(who) + ": null projection");
+    wrs_ctx* ctx = pj->dec->ctx;
+    if (!x) return fail(ctx, WRS_ERR_INVALID, std::string(who) + ": null x");
+    if (n_rows <= 0 || n_rows > pj->dec->max_rows) return fail(ctx, WRS_ERR_INVALID, std::string(who) + ": n_rows outside 1..max_rows");
+    if (x_stride < pj->n_state || (x_stride & 3) != 0 || (reinterpret_cast<uintptr_t>(x) & 15) != 0)
+        return fail(ctx, WRS_ERR_INVALID, std::string(who) + ": x needs x_stride >= n_state, a multiple of 4, and a 16-byte aligned base");
+    return WRS_OK;
+}
+
+template <int EPI>
+int launch_proj(wrs_projection* pj, ProjParams q, const float* x, int64_t x_stride, cudaStream_t stream) {
+    wrs_decoder* dec = pj->dec;
+    wrs_ctx* ctx = dec->ctx;
+    const size_t smem = sizeof(ProjSmem) + sizeof(uint32_t) * (dec->bm_words + 2);
+    if (!pj->attr_set) {
+        WRS_CUDA(ctx, cudaFuncSetAttribute(proj_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        WRS_CUDA(ctx, cudaFuncSetAttribute(proj_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        pj->attr_set = true;
+    }
+    q.wp = pj->d_wp; q.xp = pj->d_xp;
+    q.n_tiles = pj->n_tiles; q.n_text_tiles = pj->n_text_tiles; q.n_kstages = pj->n_kstages;
+    q.n_mtiles = (q.n_rows + kPM - 1) / kPM;
+    q.n_vocab = dec->cfg.n_vocab; q.ts_split = dec->ts_split;
+    const int64_t groups = (int64_t)q.n_mtiles * q.n_kstages * 4 * kPM;
+    proj_pack_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, stream>>>(x, x_stride, q.n_rows, pj->n_state, q.n_mtiles, kPM, 0, 0, 0, pj->d_xp);
+    WRS_CUDA(ctx, cudaGetLastError());
+    proj_kernel<EPI><<<std::min(ctx->sm_count, pj->n_tiles), kPThreads, smem, stream>>>(q);
+    WRS_CUDA(ctx, cudaGetLastError());
+    return WRS_OK;
+}
+
+int ensure_tail_attrs(wrs_decoder* dec);
+
 // Launch 1: one 512-thread CTA per SM at most, every warp gets at least one unit.  Launch 2: one CTA per group, one warp
 // per row.
 template <int MODE>
 int launch_step(wrs_decoder* dec, StepParams p, cudaStream_t stream) {
     wrs_ctx* ctx = dec->ctx;
-    const size_t smem = (size_t)kStepWarps * kWarpSmem, smem_tail = (size_t)kTailHead + (size_t)kMaxBeam * kTailBytes;
-    if (!dec->smem_attr_set) {
-        WRS_CUDA(ctx, cudaFuncSetAttribute(decode_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        WRS_CUDA(ctx, cudaFuncSetAttribute(decode_tail_kernel<MODE_BEAM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tail));
-        WRS_CUDA(ctx, cudaFuncSetAttribute(decode_tail_kernel<MODE_GREEDY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tail));
-        WRS_CUDA(ctx, cudaFuncSetAttribute(decode_tail_kernel<MODE_FILTER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tail));
-        dec->smem_attr_set = true;
+    const size_t smem = (size_t)kStepWarps * kWarpSmem;
+    {
+        const int rc_attr = ensure_tail_attrs(dec);
+        if (rc_attr != WRS_OK) return rc_attr;
     }
     const int64_t units = (int64_t)p.n_rows * p.upr;
     const int grid = (int)std::max<int64_t>(1, std::min<int64_t>(ctx->sm_count, (units + kStepWarps - 1) / kStepWarps));
@@ -1268,6 +1407,19 @@ int launch_step(wrs_decoder* dec, StepParams p, cudaStream_t stream) {
     // (programmatic dependent launch, measured twice: 2 us slower per step -- tail CTAs placed early only wait)
     decode_tail_kernel<MODE><<<p.n_rows / rows_per_group, rows_per_group * 32, (size_t)kTailHead + (size_t)rows_per_group * kTailBytes, stream>>>(p);
     WRS_CUDA(ctx, cudaGetLastError());
+    return WRS_OK;
+}
+
+int ensure_tail_attrs(wrs_decoder* dec) {
+    wrs_ctx* ctx = dec->ctx;
+    const size_t smem = (size_t)kStepWarps * kWarpSmem, smem_tail = (size_t)kTailHead + (size_t)kMaxBeam * kTailBytes;
+    if (!dec->smem_attr_set) {
+        WRS_CUDA(ctx, cudaFuncSetAttribute(decode_scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        WRS_CUDA(ctx, cudaFuncSetAttribute(decode_tail_kernel<MODE_BEAM>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tail));
+        WRS_CUDA(ctx, cudaFuncSetAttribute(decode_tail_kernel<MODE_GREEDY>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tail));
+        WRS_CUDA(ctx, cudaFuncSetAttribute(decode_tail_kernel<MODE_FILTER>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tail));
+        dec->smem_attr_set = true;
+    }
     return WRS_OK;
 }
 
@@ -1447,6 +1599,99 @@ int wrs_greedy_step(wrs_decoder* dec, const float* logits, int64_t row_stride, i
     p.sum_in = sum_in; p.sum_out = sum_out; p.next_tokens = next_tokens; p.next_stride = next_stride; p.completed = completed;
     set_debug(p, dbg);
     return launch_step<MODE_GREEDY>(dec, p, stream);
+}
+
+// ---- projection + decode step (reference src/model.rs:521 then src/decode/mod.rs:257-270)
+int wrs_projection_create(wrs_decoder* dec, const float* token_emb, int64_t emb_stride, int32_t n_state, wrs_stream_t stream_,
+                          wrs_projection** out) {
+    if (!dec || !out) return fail(dec ? dec->ctx : nullptr, WRS_ERR_INVALID, "wrs_projection_create: null argument");
+    *out = nullptr;
+    wrs_ctx* ctx = dec->ctx;
+    if (!token_emb || n_state < kPK || n_state % kPK != 0 || emb_stride < n_state || (emb_stride & 3) != 0 ||
+        (reinterpret_cast<uintptr_t>(token_emb) & 15) != 0)
+        return fail(ctx, WRS_ERR_INVALID, "wrs_projection_create: need n_state a positive multiple of 32, emb_stride >= n_state and a multiple of 4, a 16-byte aligned base");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    WRS_CUDA(ctx, cudaSetDevice(ctx->device));
+    wrs_projection* pj = new wrs_projection();
+    pj->dec = dec; pj->n_state = n_state; pj->n_kstages = n_state / kPK;
+    const int V = dec->cfg.n_vocab;
+    pj->n_text_tiles = (dec->ts_split + kPN - 1) / kPN;
+    pj->n_tiles = pj->n_text_tiles + (V - dec->ts_split + kPN - 1) / kPN;
+    pj->max_mtiles = (dec->max_rows + kPM - 1) / kPM;
+    const size_t wbytes = (size_t)pj->n_tiles * pj->n_kstages * 2 * kPBBytes;
+    const size_t xbytes = (size_t)pj->max_mtiles * pj->n_kstages * 2 * kPABytes;
+    const size_t pbytes = (size_t)dec->max_rows * pj->n_tiles * (16 + 8 * kMaxK);
+    cudaError_t e;
+    if ((e = cudaMalloc(&pj->d_wp, wbytes)) != cudaSuccess || (e = cudaMalloc(&pj->d_xp, xbytes)) != cudaSuccess ||
+        (e = cudaMalloc(&pj->d_parts, pbytes)) != cudaSuccess) {
+        wrs_projection_destroy(pj);
+        return cuda_fail(ctx, e, "projection buffers");
+    }
+    const int64_t groups = (int64_t)pj->n_tiles * pj->n_kstages * 4 * kPN;
+    proj_pack_kernel<<<(unsigned)std::min<int64_t>((groups + 255) / 256, 65535), 256, 0, stream>>>(
+        token_emb, emb_stride, V, n_state, pj->n_tiles, kPN, pj->n_text_tiles, dec->ts_split, 1, pj->d_wp);
+    e = cudaGetLastError();
+    if (e != cudaSuccess) { wrs_projection_destroy(pj); return cuda_fail(ctx, e, "projection packing"); }
+    *out = pj;
+    return WRS_OK;
+}
+
+void wrs_projection_destroy(wrs_projection* pj) {
+    if (!pj) return;
+    cudaSetDevice(pj->dec->ctx->device);
+    cudaFree(pj->d_wp); cudaFree(pj->d_xp); cudaFree(pj->d_parts);
+    delete pj;
+}
+
+int wrs_project_logits(wrs_projection* pj, const float* x, int64_t x_stride, int64_t n_rows, float* logits, int64_t row_stride,
+                       wrs_stream_t stream_) {
+    int rc = proj_check(pj, "wrs_project_logits", x, x_stride, n_rows);
+    if (rc != WRS_OK) return rc;
+    wrs_ctx* ctx = pj->dec->ctx;
+    if (!logits || row_stride < pj->dec->cfg.n_vocab) return fail(ctx, WRS_ERR_INVALID, "wrs_project_logits: need logits and row_stride >= n_vocab");
+    WRS_CUDA(ctx, cudaSetDevice(ctx->device));
+    ProjParams q;
+    memset(&q, 0, sizeof(q));
+    q.n_rows = (int)n_rows; q.logits = logits; q.row_stride = row_stride;
+    return launch_proj<0>(pj, q, x, x_stride, (cudaStream_t)stream_);
+}
+
+int wrs_project_beam_step(wrs_projection* pj, const float* x, int64_t x_stride, int64_t n_rows, const int64_t* tokens,
+                          int64_t tok_stride, int64_t cur_len, int64_t sample_begin, const float* sum_in, int64_t* next_tokens,
+                          int64_t next_stride, int32_t* source_idx, float* sum_out, int32_t* completed, const wrs_step_debug* dbg,
+                          wrs_stream_t stream_) {
+    int rc = proj_check(pj, "wrs_project_beam_step", x, x_stride, n_rows);
+    if (rc != WRS_OK) return rc;
+    wrs_decoder* dec = pj->dec;
+    // (the logits arguments of the common check: x stands in as the non-null, aligned buffer; there is no row_stride)
+    rc = check_step_args(dec, "wrs_project_beam_step", x, dec->cfg.n_vocab, n_rows, tokens, tok_stride, cur_len, sample_begin);
+    if (rc != WRS_OK) return rc;
+    wrs_ctx* ctx = dec->ctx;
+    const wrs_decode_cfg& c = dec->cfg;
+    if (!sum_in || !next_tokens || !source_idx || !sum_out || !completed) return fail(ctx, WRS_ERR_INVALID, "wrs_project_beam_step: null output");
+    if (n_rows % c.beam_size != 0) return fail(ctx, WRS_ERR_INVALID, "wrs_project_beam_step: n_rows not a multiple of beam_size (beam_search.rs:29)");
+    if (next_stride < cur_len + 1) return fail(ctx, WRS_ERR_INVALID, "wrs_project_beam_step: next_stride < cur_len + 1");
+    if ((const void*)next_tokens == (const void*)tokens) return fail(ctx, WRS_ERR_INVALID, "wrs_project_beam_step: next_tokens must not alias tokens");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    WRS_CUDA(ctx, cudaSetDevice(ctx->device));
+    StepParams p = step_params(dec, nullptr, c.n_vocab, n_rows, tokens, tok_stride, cur_len, sample_begin, c.beam_size + 1,
+                               c.beam_size, dec->d_bm_base, dec->d_bm_first);
+    p.sum_in = sum_in; p.sum_out = sum_out; p.next_tokens = next_tokens; p.next_stride = next_stride;
+    p.source_idx = source_idx; p.completed = completed;
+    set_debug(p, dbg);
+    const int Kp = (p.K + 1) & ~1;
+    p.proj_parts = pj->d_parts; p.proj_tiles = pj->n_tiles; p.proj_text_tiles = pj->n_text_tiles; p.proj_rec = 16 + 8 * Kp;
+    ProjParams q;
+    memset(&q, 0, sizeof(q));
+    q.n_rows = (int)n_rows; q.tokens = tokens; q.tok_stride = tok_stride; q.cur_len = p.cur_len; q.sample_begin = p.sample_begin;
+    q.K = p.K; q.rc = p.rc; q.bm = p.bm; q.bm_words = p.bm_words; q.parts = pj->d_parts; q.rec_bytes = p.proj_rec;
+    rc = ensure_tail_attrs(dec);
+    if (rc != WRS_OK) return rc;
+    rc = launch_proj<1>(pj, q, x, x_stride, stream);
+    if (rc != WRS_OK) return rc;
+    decode_tail_kernel<MODE_BEAM><<<p.n_rows / p.beam, p.beam * 32, (size_t)kTailHead + (size_t)p.beam * kTailBytes, stream>>>(p);
+    WRS_CUDA(ctx, cudaGetLastError());
+    return WRS_OK;
 }
 
 }  // extern "C"

@@ -1,0 +1,383 @@
+// the logits projection with the decode step's row scan as its epilogue.
+//
+// Replaces, together with the tail launch of decode.cu, reference src/model.rs:521
+// (`x.matmul(&self.token_emb.ws.transpose(0, 1))`, [R, n_state] x [n_state, V] in f32) followed by
+// src/decode/mod.rs:257-270 (filters + extractor): the [R, V] logits are never written to HBM.
+//
+// Arithmetic: tcgen05.mma kind::f16 on bf16 operands with f32 accumulators in tensor memory.  f32 operands are split
+// x = hi + lo (both bf16, lo = bf16(x - hi)), and hi*hi + lo*hi + hi*lo is accumulated ("bf16x3"): 16 mantissa bits per
+// operand, so a logit differs from the f32 product sum by about 2^-16 of sum |x_i w_i| -- NOT f32-faithful; the
+// tolerance this buys is written in tests/test_gpu_project.py and DESIGN.md.
+//
+// Geometry: a vocab tile is 176 consecutive ids of ONE partition (text ids below ts_split, timestamp ids from it: a
+// tile never straddles, so a tile's statistics belong to one partition); V = 51865 with timestamps gives 287 + 9 = 296
+// tiles = two per SM on 148 SMs.  Rows go 128 to an M tile (TMEM lanes).  A CTA (192 threads) takes vocab tiles
+// b, b + grid, ... and for each of them every M tile:
+//   warp 4 (one lane)  producer: cp.async.bulk of one K stage (32 of n_state) of A (x, 16 KB) and B (weights, 22 KB)
+//                      into a 4-deep ring; both operands were packed beforehand into the tensor core's canonical
+//                      K-major no-swizzle layout ([16-byte K chunk][row][8 bf16]: 8 x 16 B core matrices, rows 16 B
+//                      apart, K chunks `rows x 16 B` apart), so a stage is one contiguous block -- no tensor map.
+//   warp 5 (one lane)  issues 6 MMAs per stage (2 K steps of 16 x {hi hi, lo hi, hi lo}) into one of two 176-column
+//                      accumulators; tcgen05.commit frees the stage / publishes the accumulator.
+//   warps 0-3          epilogue, thread = row: tcgen05.ld 32 columns at a time, masks as predicates (suppress bitmap,
+//                      timestamp rules as id ranges), online {max, sum exp}, exact top-K of the tile in registers
+//                      (value desc, id asc), one record per (row, tile) to global memory for the tail launch.
+#pragma once
+
+#include <cuda_bf16.h>
+
+#include "async_copy.cuh"
+#include "decode_scan.cuh"
+
+namespace wrs {
+
+constexpr int kPM = 128;                                  // rows per M tile
+constexpr int kPN = 176;                                  // ids per vocab tile (a multiple of 16, at most 256)
+constexpr int kPK = 32;                                   // elements of n_state per pipeline stage (two MMA K steps)
+constexpr int kPStages = 4;
+constexpr int kPThreads = 192;
+constexpr int kPABytes = kPM * kPK * 2;                   // one part (hi or lo) of a stage of x: 8 KB
+constexpr int kPBBytes = kPN * kPK * 2;                   // ... of the weights: 11 KB
+constexpr int kPStageBytes = 2 * kPABytes + 2 * kPBBytes; // [A hi | A lo | B hi | B lo] = 38 912 B
+constexpr int kPAccStride = 256;                          // TMEM columns between the two accumulators
+constexpr int kPTmemCols = 512;
+
+struct ProjParams {
+    const unsigned char* wp;     // packed weights [tile][stage][hi | lo][4][176][8] bf16
+    const unsigned char* xp;     // packed x       [M tile][stage][hi | lo][4][128][8] bf16
+    int n_tiles, n_text_tiles, n_mtiles, n_kstages, n_rows, n_vocab, ts_split;
+    // EPI 0: the plain projection
+    float* logits; int64_t row_stride;
+    // EPI 1: fold
+    const int64_t* tokens; int64_t tok_stride; int cur_len, sample_begin, K;
+    RuleCfg rc; const uint32_t* bm; int bm_words;
+    unsigned char* parts; int rec_bytes;                  // records [row][tile]: {max, sum, 0, 0} v[Kp] id[Kp]
+};
+
+__host__ __device__ __forceinline__ int proj_tile_base(int tile, int n_text_tiles, int ts_split) {
+    return tile < n_text_tiles ? tile * kPN : ts_split + (tile - n_text_tiles) * kPN;
+}
+__host__ __device__ __forceinline__ int proj_tile_end(int tile, int n_text_tiles, int ts_split, int n_vocab) {
+    return tile < n_text_tiles ? min(tile * kPN + kPN, ts_split) : min(ts_split + (tile - n_text_tiles + 1) * kPN, n_vocab);
+}
+
+// ---- operand packing.  One thread per 16-byte group (8 consecutive elements of n_state of one row).
+__device__ __forceinline__ void split8(const float* v, uint4& hi, uint4& lo) {
+    unsigned h[4], l[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const __nv_bfloat16 h0 = __float2bfloat16_rn(v[2 * i]), h1 = __float2bfloat16_rn(v[2 * i + 1]);
+        const __nv_bfloat16 l0 = __float2bfloat16_rn(v[2 * i] - __bfloat162float(h0)), l1 = __float2bfloat16_rn(v[2 * i + 1] - __bfloat162float(h1));
+        h[i] = (unsigned)__bfloat16_as_ushort(h0) | ((unsigned)__bfloat16_as_ushort(h1) << 16);
+        l[i] = (unsigned)__bfloat16_as_ushort(l0) | ((unsigned)__bfloat16_as_ushort(l1) << 16);
+    }
+    hi = make_uint4(h[0], h[1], h[2], h[3]); lo = make_uint4(l[0], l[1], l[2], l[3]);
+}
+
+// rows_per_tile = 176 (weights; src row = the tile's id) or 128 (x; src row = tile * 128 + r)
+__global__ void proj_pack_kernel(const float* __restrict__ src, int64_t src_stride, int n_src_rows, int n_state, int n_tiles,
+                                 int rows_per_tile, int n_text_tiles, int ts_split, int is_w, unsigned char* __restrict__ dst) {
+    const int n_kstages = n_state / kPK;
+    const int64_t groups = (int64_t)n_tiles * n_kstages * 4 * rows_per_tile;
+    for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < groups; g += (int64_t)gridDim.x * blockDim.x) {
+        // consecutive threads take consecutive K chunks of one row: a warp reads 8 rows x 128 contiguous bytes
+        const int kc = (int)(g & 3);
+        int64_t rest = g >> 2;
+        const int s = (int)(rest % n_kstages); rest /= n_kstages;
+        const int r = (int)(rest % rows_per_tile);
+        const int tile = (int)(rest / rows_per_tile);
+        int row, end;
+        if (is_w) { row = proj_tile_base(tile, n_text_tiles, ts_split) + r; end = proj_tile_end(tile, n_text_tiles, ts_split, n_src_rows); }
+        else { row = tile * rows_per_tile + r; end = n_src_rows; }
+        float v[8];
+        if (row < end) {
+            const float4 a = *reinterpret_cast<const float4*>(src + (int64_t)row * src_stride + s * kPK + kc * 8);
+            const float4 b = *reinterpret_cast<const float4*>(src + (int64_t)row * src_stride + s * kPK + kc * 8 + 4);
+            v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+        } else {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) v[i] = 0.0f;
+        }
+        uint4 hi, lo;
+        split8(v, hi, lo);
+        const int64_t part_bytes = (int64_t)rows_per_tile * kPK * 2;
+        unsigned char* blk = dst + ((int64_t)tile * n_kstages + s) * 2 * part_bytes;
+        const int64_t off = ((int64_t)kc * rows_per_tile + r) * 16;
+        *reinterpret_cast<uint4*>(blk + off) = hi;
+        *reinterpret_cast<uint4*>(blk + part_bytes + off) = lo;
+    }
+}
+
+// mbarrier wait with a bound: a pipeline that stops (a bug, never a data condition) ends the launch with an error
+// instead of hanging the device
+__device__ __forceinline__ void mbar_wait_b(unsigned long long* bar, unsigned parity) {
+    for (unsigned spins = 0;; ++spins) {
+        unsigned done;
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n" : "=r"(done) : "r"(smem_addr(bar)), "r"(parity) : "memory");
+        if (done) return;
+        if (spins > (1u << 24)) __trap();
+    }
+}
+
+// ---- tcgen05 plumbing (PTX as the CUDA 12.9 assembler takes it for sm_100a)
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(unsigned long long* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_addr(bar)) : "memory");
+}
+// shared-memory operand descriptor, K-major, no swizzle: start address, LBO = bytes between the two 16-byte K chunks of
+// an MMA, SBO = bytes between 8-row groups; bit 46 = descriptor version 1 (Blackwell)
+__device__ __forceinline__ unsigned long long tc_desc(unsigned saddr, unsigned lbo, unsigned sbo) {
+    return (unsigned long long)((saddr & 0x3ffffu) >> 4) | ((unsigned long long)(lbo >> 4) << 16) |
+           ((unsigned long long)(sbo >> 4) << 32) | (1ull << 46);
+}
+// instruction descriptor: D f32 (bits 4-5 = 1), A and B bf16 (bits 7-9, 10-12 = 1), both K-major (bits 15, 16 = 0),
+// N / 8 at bit 17, M / 16 at bit 24
+constexpr unsigned kPIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((unsigned)(kPN >> 3) << 17) | ((unsigned)(kPM >> 4) << 24);
+__device__ __forceinline__ void tc_mma(unsigned d_tmem, unsigned long long a, unsigned long long b, unsigned accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(d_tmem), "l"(a), "l"(b), "r"(kPIdesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ void tc_ld32(unsigned taddr, float (&x)[32]) {
+    unsigned r[32];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, "
+        "%19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+        "tcgen05.wait::ld.sync.aligned;\n"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
+          "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
+          "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr)
+        : "memory");
+#pragma unroll
+    for (int i = 0; i < 32; ++i) x[i] = __uint_as_float(r[i]);
+}
+__device__ __forceinline__ void tc_ld16(unsigned taddr, float (&x)[32]) {
+    unsigned r[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
+        "tcgen05.wait::ld.sync.aligned;\n"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+          "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr)
+        : "memory");
+#pragma unroll
+    for (int i = 0; i < 16; ++i) x[i] = __uint_as_float(r[i]);
+#pragma unroll
+    for (int i = 16; i < 32; ++i) x[i] = -CUDART_INF_F;
+}
+
+// ---- epilogue (EPI 1): what a thread keeps for its row within one vocab tile
+struct ProjRow {
+    float m, s;                                          // max and sum exp(x - m) of the surviving ids so far
+    float v[kMaxK]; int id[kMaxK];                       // the best so far, (value desc, id asc); -inf / INT32_MAX = empty
+    float kth;                                           // v[K - 1]
+};
+
+__device__ __forceinline__ unsigned range_bits(int lo, int hi) {   // bits i of a 32-bit word with lo <= i < hi
+    lo = max(lo, 0); hi = min(hi, 32);
+    if (hi <= lo) return 0u;
+    return (0xffffffffu << lo) & (hi >= 32 ? 0xffffffffu : (1u << hi) - 1u);
+}
+
+// ids arrive in ascending order, so a new entry goes behind every entry of equal value: strict comparisons only
+__device__ __forceinline__ void proj_insert(ProjRow& st, float x, int nid, int K) {
+#pragma unroll
+    for (int e = kMaxK - 1; e >= 1; --e) {
+        if (x > st.v[e - 1]) { st.v[e] = st.v[e - 1]; st.id[e] = st.id[e - 1]; }
+        else if (x > st.v[e]) { st.v[e] = x; st.id[e] = nid; }
+    }
+    if (x > st.v[0]) { st.v[0] = x; st.id[0] = nid; }
+    float k = st.v[0];
+#pragma unroll
+    for (int e = 1; e < kMaxK; ++e) k = (e == K - 1) ? st.v[e] : k;
+    st.kth = k;
+}
+
+// 32 columns of the row's accumulator (ids id0 .. id0 + 31; `valid` bit i: id0 + i survives the filters)
+__device__ __forceinline__ void proj_fold32(ProjRow& st, float (&x)[32], unsigned valid, int id0, int K) {
+    if (valid != 0xffffffffu) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) x[i] = (valid & (1u << i)) ? x[i] : -CUDART_INF_F;
+    }
+    float cm = x[0];
+#pragma unroll
+    for (int i = 1; i < 32; ++i) cm = fmaxf(cm, x[i]);   // (NaN operands are ignored: handled below)
+    if (cm == -CUDART_INF_F || cm != cm) {
+        // nothing finite: the sum is unchanged unless a NaN is among the survivors (then it is NaN, as in ATen)
+        bool bad = false;
+#pragma unroll
+        for (int i = 0; i < 32; ++i) bad |= x[i] != x[i];
+        if (bad) st.s = CUDART_NAN_F;
+        return;
+    }
+    if (cm > st.m) { st.s *= ex2((st.m - cm) * kLog2e); st.m = cm; }
+    float acc0 = 0.0f, acc1 = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 32; i += 2) {
+        acc0 += ex2((x[i] - st.m) * kLog2e);
+        acc1 += ex2((x[i + 1] - st.m) * kLog2e);
+    }
+    st.s += acc0 + acc1;
+    if (cm > st.kth) {
+#pragma unroll
+        for (int i = 0; i < 32; ++i)
+            if (x[i] > st.kth) proj_insert(st, x[i], id0 + i, K);
+    }
+}
+
+struct ProjSmem {
+    unsigned char stage[kPStages][kPStageBytes];
+    unsigned long long full[kPStages], empty[kPStages], tfull[2], tempty[2];
+    unsigned tmem_base;
+    unsigned pad[3];
+    uint32_t bm[1];                                      // the suppress bitmap, bm_words + 2 words (EPI 1)
+};
+
+template <int EPI>
+__global__ void __launch_bounds__(kPThreads, 1) proj_kernel(const ProjParams p) {
+    extern __shared__ __align__(1024) unsigned char proj_smem_raw[];
+    ProjSmem& sm = *reinterpret_cast<ProjSmem*>(proj_smem_raw);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kPStages; ++s) { mbar_init(&sm.full[s], 1); mbar_init(&sm.empty[s], 1); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&sm.tfull[b], 1); mbar_init(&sm.tempty[b], 4); }
+    }
+    if (EPI == 1)
+        for (int i = threadIdx.x; i < p.bm_words + 2; i += kPThreads) sm.bm[i] = i < p.bm_words ? p.bm[i] : 0u;
+    __syncwarp();
+    if (warp == 5) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_addr(&sm.tmem_base)), "r"(kPTmemCols) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const unsigned tmem = sm.tmem_base;
+    const int my_tiles = ((int)blockIdx.x < p.n_tiles) ? (p.n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+    const int n_units = my_tiles * p.n_mtiles;           // accumulations of this CTA: unit u = (tile u / n_mtiles, M tile u % n_mtiles)
+
+    if (warp == 4) {
+        // ================================================= producer
+        if (lane == 0) {
+            unsigned it = 0;
+            for (int u = 0; u < n_units; ++u) {
+                const int tile = (int)blockIdx.x + (u / p.n_mtiles) * (int)gridDim.x, mt = u % p.n_mtiles;
+                const unsigned char* a = p.xp + (int64_t)mt * p.n_kstages * (2 * kPABytes);
+                const unsigned char* b = p.wp + (int64_t)tile * p.n_kstages * (2 * kPBBytes);
+                for (int ks = 0; ks < p.n_kstages; ++ks, ++it) {
+                    const unsigned slot = it % kPStages, round = it / kPStages;
+                    mbar_wait_b(&sm.empty[slot], (round & 1u) ^ 1u);      // (a fresh barrier passes the first round)
+                    mbar_expect_tx(&sm.full[slot], (unsigned)kPStageBytes);
+                    bulk_g2s(sm.stage[slot], a + (int64_t)ks * (2 * kPABytes), 2 * kPABytes, &sm.full[slot]);
+                    bulk_g2s(sm.stage[slot] + 2 * kPABytes, b + (int64_t)ks * (2 * kPBBytes), 2 * kPBBytes, &sm.full[slot]);
+                }
+            }
+        }
+    } else if (warp == 5) {
+        // ================================================= MMA issuer
+        if (lane == 0) {
+            unsigned it = 0;
+            for (int u = 0; u < n_units; ++u) {
+                const unsigned buf = (unsigned)u & 1u, use = (unsigned)u >> 1;
+                mbar_wait_b(&sm.tempty[buf], (use & 1u) ^ 1u);            // the epilogue has drained this accumulator
+                tc_fence_after();
+                const unsigned d = tmem + buf * kPAccStride;
+                for (int ks = 0; ks < p.n_kstages; ++ks, ++it) {
+                    const unsigned slot = it % kPStages, round = it / kPStages;
+                    mbar_wait_b(&sm.full[slot], round & 1u);
+                    tc_fence_after();
+                    const unsigned a_hi = smem_addr(sm.stage[slot]), a_lo = a_hi + kPABytes;
+                    const unsigned b_hi = a_hi + 2 * kPABytes, b_lo = b_hi + kPBBytes;
+#pragma unroll
+                    for (int j = 0; j < kPK / 16; ++j) {
+                        const unsigned ao = j * 2 * (kPM * 16), bo = j * 2 * (kPN * 16);
+                        const unsigned long long dah = tc_desc(a_hi + ao, kPM * 16, 128), dal = tc_desc(a_lo + ao, kPM * 16, 128);
+                        const unsigned long long dbh = tc_desc(b_hi + bo, kPN * 16, 128), dbl = tc_desc(b_lo + bo, kPN * 16, 128);
+                        tc_mma(d, dal, dbh, (ks | j) != 0);             // the small products first
+                        tc_mma(d, dah, dbl, 1u);
+                        tc_mma(d, dah, dbh, 1u);
+                    }
+                    tc_commit(&sm.empty[slot]);                         // the stage is free once these MMAs have read it
+                }
+                tc_commit(&sm.tfull[buf]);                              // the accumulator is complete
+            }
+        }
+    } else {
+        // ================================================= epilogue: thread = row of the M tile
+        const unsigned lane_base = (unsigned)(warp * 32) << 16;
+        for (int u = 0; u < n_units; ++u) {
+            const int tile = (int)blockIdx.x + (u / p.n_mtiles) * (int)gridDim.x, mt = u % p.n_mtiles;
+            const unsigned buf = (unsigned)u & 1u, use = (unsigned)u >> 1;
+            const int row = mt * kPM + (int)threadIdx.x;
+            const int base = proj_tile_base(tile, p.n_text_tiles, p.ts_split);
+            const int end = proj_tile_end(tile, p.n_text_tiles, p.ts_split, p.n_vocab);
+            ProjRow st;
+            RowRules rr;
+            if (EPI == 1) {
+                st.m = -CUDART_INF_F; st.s = 0.0f; st.kth = -CUDART_INF_F;
+#pragma unroll
+                for (int e = 0; e < kMaxK; ++e) { st.v[e] = -CUDART_INF_F; st.id[e] = INT32_MAX; }
+                rr.t_lo = rr.t_hi = rr.s_lo = rr.s_hi = 0; rr.flags = 0u;
+                if (row < p.n_rows) rr = row_rules(p.rc, p.tokens + (int64_t)row * p.tok_stride, p.cur_len, p.sample_begin);
+            }
+            mbar_wait_b(&sm.tfull[buf], use & 1u);
+            tc_fence_after();
+            const unsigned t0 = tmem + buf * kPAccStride + lane_base;
+#pragma unroll 1
+            for (int c = 0; c < (kPN + 31) / 32; ++c) {
+                float x[32];
+                if (32 * c + 32 <= kPN) tc_ld32(t0 + 32 * c, x);
+                else tc_ld16(t0 + 32 * c, x);
+                const int id0 = base + 32 * c;
+                if (EPI == 0) {
+                    if (row < p.n_rows) {
+                        float* o = p.logits + (int64_t)row * p.row_stride + id0;
+#pragma unroll
+                        for (int i = 0; i < 32; ++i)
+                            if (id0 + i < end) o[i] = x[i];
+                    }
+                } else if (row < p.n_rows && id0 < end) {
+                    // suppress bits of ids id0 .. id0 + 31 (two words of the bitmap), the row's ranges, the tile's end
+                    const unsigned w0 = sm.bm[id0 >> 5], w1 = sm.bm[(id0 >> 5) + 1];
+                    const unsigned supp = __funnelshift_r(w0, w1, id0 & 31);
+                    const unsigned ok = (range_bits(rr.t_lo - id0, min(rr.t_hi, end) - id0) | range_bits(rr.s_lo - id0, min(rr.s_hi, end) - id0)) & ~supp;
+                    proj_fold32(st, x, ok, id0, p.K);
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sm.tempty[buf]);
+            if (EPI == 1 && row < p.n_rows) {
+                unsigned char* rec = p.parts + ((int64_t)row * p.n_tiles + tile) * p.rec_bytes;
+                *reinterpret_cast<float4*>(rec) = make_float4(st.m, st.s, 0.0f, 0.0f);
+                const int Kp = (p.K + 1) & ~1;
+                float* rv = reinterpret_cast<float*>(rec + 16);
+                int* ri = reinterpret_cast<int*>(rec + 16 + 4 * Kp);
+#pragma unroll
+                for (int e = 0; e < kMaxK; ++e)
+                    if (e < Kp) { rv[e] = st.v[e]; ri[e] = st.id[e]; }
+            }
+        }
+    }
+    // ---- teardown: every tcgen05 operation of this CTA has completed (the epilogue waited for the last commit)
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 5) {
+        tc_fence_after();
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kPTmemCols) : "memory");
+    }
+}
+
+}  // namespace wrs

@@ -240,3 +240,66 @@ def avg_logprobs(sum_logprobs: Sequence[float], n_tokens: Sequence[int]) -> np.n
     _lib.check(_lib.lib().wrs_avg_logprob_host(lp.ctypes.data_as(C.c_void_p), nt.ctypes.data_as(C.c_void_p), len(lp),
                                                out.ctypes.data_as(C.c_void_p)))
     return out
+
+
+class Projection:
+    """`x.matmul(token_emb.T)` (reference src/model.rs:521) on the tensor cores, alone
+    (`logits`) or with the beam step as its epilogue (`beam_step`: same outputs as Decoder.beam_step, the logits never
+    reach HBM).  Bound to one Decoder (vocabulary geometry, masks, finished store)."""
+
+    def __init__(self, decoder: Decoder, token_emb: torch.Tensor):
+        if token_emb.dtype != torch.float32 or token_emb.dim() != 2 or token_emb.stride(1) != 1 or not token_emb.is_cuda:
+            raise TypeError("token_emb must be a CUDA f32 [vocab, n_state] tensor with unit inner stride")
+        if token_emb.shape[0] != decoder.cfg.n_vocab:
+            raise ValueError("token_emb rows != n_vocab")
+        self.dec = decoder
+        self.n_state = token_emb.shape[1]
+        self.handle = C.c_void_p()
+        _lib.check(_lib.lib().wrs_projection_create(decoder.handle, token_emb.data_ptr(), token_emb.stride(0), self.n_state,
+                                                    decoder._stream(), C.byref(self.handle)), decoder.ctx.handle)
+        torch.cuda.current_stream(decoder.device).synchronize()     # token_emb may go away after this
+
+    def close(self):
+        if getattr(self, "handle", None):
+            _lib.lib().wrs_projection_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check_x(self, x: torch.Tensor):
+        if x.dtype != torch.float32 or x.dim() != 2 or x.stride(1) != 1 or not x.is_cuda or x.shape[1] != self.n_state:
+            raise TypeError("x must be a CUDA f32 [rows, n_state] tensor with unit inner stride")
+
+    def logits(self, x: torch.Tensor) -> torch.Tensor:
+        self._check_x(x)
+        out = torch.empty(x.shape[0], self.dec.cfg.n_vocab, dtype=torch.float32, device=self.dec.device)
+        _lib.check(_lib.lib().wrs_project_logits(self.handle, x.data_ptr(), x.stride(0), x.shape[0], out.data_ptr(),
+                                                 out.stride(0), self.dec._stream()), self.dec.ctx.handle)
+        return out
+
+    def beam_step(self, x, tokens, sample_begin, sum_logprobs, next_tokens=None, sum_out=None, debug=False):
+        self._check_x(x)
+        d = self.dec
+        R, L = tokens.shape
+        if x.shape[0] != R:
+            raise ValueError("x and tokens disagree on the number of rows")
+        if next_tokens is None:
+            next_tokens = torch.empty(R, L + 1, dtype=torch.int64, device=d.device)
+        if sum_out is None:
+            sum_out = torch.empty(R, dtype=torch.float32, device=d.device)
+        source = torch.empty(R, dtype=torch.int32, device=d.device)
+        completed = torch.zeros(1, dtype=torch.int32, device=d.device)
+        dbg, bufs = d._debug(R, debug)
+        _lib.check(_lib.lib().wrs_project_beam_step(self.handle, x.data_ptr(), x.stride(0), R, tokens.data_ptr(),
+                                                    tokens.stride(0), L, sample_begin, sum_logprobs.data_ptr(),
+                                                    next_tokens.data_ptr(), next_tokens.stride(0), source.data_ptr(),
+                                                    sum_out.data_ptr(), completed.data_ptr(),
+                                                    C.byref(dbg) if dbg is not None else None, d._stream()), d.ctx.handle)
+        out = dict(next_tokens=next_tokens, source_idx=source, sum_logprobs=sum_out, completed=completed)
+        if bufs:
+            out.update(bufs)
+        return out
