@@ -728,6 +728,121 @@ def cpu_legs(env, dec, kv):
     return cpu, cpu_dec, parity, cpu_kv
 
 
+def bench_project(env):
+    """`x.matmul(token_emb.T)` (reference src/model.rs:521) + the decode step at config 3's shape
+    (160 rows, n_state 512 = Whisper base, V 51865), three ways: the fused tcgen05 kernel (logits never leave the SM),
+    our projection kernel writing logits + wrs_beam_step, and the library f32 GEMM (what tch runs) + wrs_beam_step."""
+    from whisper_rs_b200 import constants as C, synth
+    from whisper_rs_b200 import decode as wd
+    from whisper_rs_b200.decode.core import Projection
+    args, L, ctx, dev = env.args, env.lib, env.ctx, env.dev
+    ids = C.MULTILINGUAL
+    R, D, NB = N_AUDIO * BEAM, 512, 8
+    case = synth.decode_case(ids, N_AUDIO, BEAM, "mixed", seed=3 + env.rank)
+    prompt = wd.DecodePrompt(None, ids)
+    prompt.sample_begin = case["sample_begin"]
+    step = wd.FusedDecodeStep(wd.DecodeOptions(), ids, [prompt], max_rows=R, device=env.local)
+    step.reset()
+    dec = step.decoder
+    g = torch.Generator(device=dev).manual_seed(5 + env.rank)
+    emb = torch.empty((VOCAB, D), dtype=torch.float32, device=dev).normal_(0.0, 3.0 / D ** 0.5, generator=g)
+    # two packed copies of the embedding, alternated step by step: 2 x 107 MB > L2, so no step finds its weights cached
+    # (in the decode loop a whole decoder forward runs between two projections)
+    projs = [Projection(dec, emb), Projection(dec, emb)]
+    embs = [emb, emb.clone()]
+    xs = [torch.empty((R, D), dtype=torch.float32, device=dev).normal_(generator=g) for _ in range(NB)]
+    d_tokens = torch.from_numpy(case["tokens"]).to(dev)
+    d_sums = torch.from_numpy(case["sum_logprobs"]).to(dev)
+    Lcur = d_tokens.shape[1]
+    d_next = torch.empty((R, Lcur + 1), dtype=torch.int64, device=dev)
+    d_src = torch.empty(R, dtype=torch.int32, device=dev)
+    d_out = torch.empty(R, dtype=torch.float32, device=dev)
+    d_done = torch.empty(1, dtype=torch.int32, device=dev)
+    logits = [torch.empty((R, VOCAB), dtype=torch.float32, device=dev) for _ in range(NB)]
+    n_replays = max(50, args.steps // NB)
+    n_steps = n_replays * NB
+    cap_stream = torch.cuda.Stream(dev)
+
+    def graph_of(body):
+        gr = torch.cuda.CUDAGraph()
+        torch.cuda.synchronize()
+        with torch.cuda.graph(gr, stream=cap_stream):
+            body(torch.cuda.current_stream(dev).cuda_stream)
+        for _ in range(3):
+            gr.replay()
+        return env.max_over_ranks(timed(lambda i: gr.replay(), n_replays, env.barrier)) / n_steps
+
+    def beam(lg, cs):
+        env.check(L.wrs_beam_step(dec.handle, lg.data_ptr(), lg.stride(0), R, d_tokens.data_ptr(), d_tokens.stride(0), Lcur,
+                                  prompt.sample_begin, d_sums.data_ptr(), d_next.data_ptr(), d_next.stride(0), d_src.data_ptr(),
+                                  d_out.data_ptr(), d_done.data_ptr(), None, cs))
+
+    def fused(cs):
+        env.check(L.wrs_decoder_reset(dec.handle, cs))
+        for b in range(NB):
+            env.check(L.wrs_project_beam_step(projs[b & 1].handle, xs[b].data_ptr(), xs[b].stride(0), R, d_tokens.data_ptr(),
+                                              d_tokens.stride(0), Lcur, prompt.sample_begin, d_sums.data_ptr(), d_next.data_ptr(),
+                                              d_next.stride(0), d_src.data_ptr(), d_out.data_ptr(), d_done.data_ptr(), None, cs))
+
+    def unfused(cs):
+        env.check(L.wrs_decoder_reset(dec.handle, cs))
+        for b in range(NB):
+            env.check(L.wrs_project_logits(projs[b & 1].handle, xs[b].data_ptr(), xs[b].stride(0), R, logits[b].data_ptr(),
+                                           logits[b].stride(0), cs))
+            beam(logits[b], cs)
+
+    def proj_only(cs):
+        for b in range(NB):
+            env.check(L.wrs_project_logits(projs[b & 1].handle, xs[b].data_ptr(), xs[b].stride(0), R, logits[b].data_ptr(),
+                                           logits[b].stride(0), cs))
+
+    def library(cs):
+        env.check(L.wrs_decoder_reset(dec.handle, cs))
+        for b in range(NB):
+            torch.matmul(xs[b], embs[b & 1].t(), out=logits[b])
+            beam(logits[b], cs)
+
+    def library_gemm(cs):
+        for b in range(NB):
+            torch.matmul(xs[b], embs[b & 1].t(), out=logits[b])
+
+    t_fused = graph_of(fused)
+    t_unfused = graph_of(unfused)
+    t_proj = graph_of(proj_only)
+    prev = torch.backends.cuda.matmul.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = False
+    torch.matmul(xs[0], embs[0].t(), out=logits[0])          # (cuBLAS workspace / heuristics outside the capture)
+    t_lib, t_lib_gemm = graph_of(library), graph_of(library_gemm)
+    torch.backends.cuda.matmul.allow_tf32 = True
+    torch.matmul(xs[0], embs[0].t(), out=logits[0])
+    t_lib_tf32 = graph_of(library_gemm)
+    torch.backends.cuda.matmul.allow_tf32 = prev
+    ctx.check(env.stream)
+    mp = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    tc_peak = float(json.load(open(mp)).get("bf16_tflops", 0.0)) if os.path.exists(mp) else 0.0
+    emb_bytes = VOCAB * D * 4 + R * D * 4                    # the f32 embedding and x, read once
+    flops = 3 * 2.0 * R * D * VOCAB                          # three bf16 products per f32 product
+    roof = env.roofline(emb_bytes, t_fused, "wrs::proj_kernel<1> (tcgen05 projection + row scan; reads the packed bf16 hi/lo "
+                        "embedding, 4 B per weight) + wrs::proj_pack_kernel (x) + wrs::decode_tail_kernel<0>; achieved = bytes of the f32 "
+                        "embedding and x / time of the whole three-launch step", "proj_kernel")
+    roof["tensor"] = {"achieved": flops / t_fused / 1e12, "peak": tc_peak or None, "unit": "TFLOP/s",
+                      "frac": flops / t_fused / 1e12 / tc_peak if tc_peak else None,
+                      "note": "3 bf16 products per f32 product on the 160 real rows; the second M tile of 128 is 3/4 padding"}
+    return {"project_beam_step": {
+        "metric": "projection + beam decode row-steps/s", "value": env.world * R / t_fused, "unit": "row-steps/s",
+        "ms_per_step": 1e3 * t_fused, "steps": n_steps, "launch": f"CUDA graph of {NB} steps (+1 reset) replayed {n_replays}x",
+        "config": {"workload": f"x [160, {D}] f32 @ token_emb [{VOCAB}, {D}] f32 (src/model.rs:521, Whisper base) + config 3's decode step; "
+                               "logits never written", "arithmetic": "bf16 hi/lo x 3 products, f32 accumulate in TMEM (about 8e-5 abs on "
+                               "logits of sigma 3; an f32 matmul is near 9e-6)",
+                   "cache": "two packed embedding copies alternate (2 x 107 MB > L2); x rotates over 8 buffers"},
+        "roofline": roof,
+        "alternatives_ms_per_step": {
+            "wrs_project_logits + wrs_beam_step": 1e3 * t_unfused, "wrs_project_logits alone": 1e3 * t_proj,
+            "torch.matmul f32 (cuBLAS, TF32 off: what tch runs) + wrs_beam_step": 1e3 * t_lib,
+            "torch.matmul f32 alone": 1e3 * t_lib_gemm, "torch.matmul TF32 alone": 1e3 * t_lib_tf32},
+        "gpu_launches": 3 * n_steps}}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -735,12 +850,12 @@ def main():
     ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--only", default="", help="comma list of sections to run besides the headline: decode,kv,configs (default: all)")
+    ap.add_argument("--only", default="", help="comma list of sections to run besides the headline: decode,kv,configs,project (default: all)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args, int(os.environ.get("RANK", 0)))
     args.warmup = max(args.warmup, 3)
-    want = set(args.only.split(",")) if args.only else {"decode", "kv", "configs"}
+    want = set(args.only.split(",")) if args.only else {"decode", "kv", "configs", "project"}
     env = Env(args)
     sampler = ClockSampler(env.local) if env.rank == 0 else None
     t_gpu0 = time.time()
@@ -748,6 +863,8 @@ def main():
     dec = bench_decode(env) if "decode" in want else None
     kv = bench_kv(env) if "kv" in want else None
     cfg = bench_configs(env) if "configs" in want else {}
+    if "project" in want:
+        cfg.update(bench_project(env))
     t_gpu1 = time.time()
     clocks = sampler.stop(t_gpu0, t_gpu1) if sampler else None
     if env.rank != 0:

@@ -55,7 +55,7 @@ struct wrs_projection {
     int n_state = 0, n_tiles = 0, n_text_tiles = 0, n_kstages = 0, max_mtiles = 0;
     unsigned char* d_wp = nullptr;    // packed weights
     unsigned char* d_xp = nullptr;    // packed x of the step in flight, [max_mtiles]
-    unsigned char* d_parts = nullptr; // [max_rows][n_tiles] records of the largest K
+    float* d_parts = nullptr;         // [max_rows][2 + 2 kMaxK][tiles padded to 4] record planes
     bool attr_set = false;
 };
 
@@ -104,7 +104,7 @@ struct StepParams {
     const float* sum_in; float* sum_out;
     int64_t* next_tokens; int64_t next_stride; int32_t* source_idx; int32_t* completed;
     int64_t* fin_tokens; int32_t* fin_len; double* fin_score; int32_t* fin_n; int32_t* sync;
-    const unsigned char* proj_parts; int proj_tiles, proj_text_tiles, proj_rec;   // projection mode: the tail merges proj_kernel's records
+    const float* proj_parts; int proj_tiles, proj_text_tiles, proj_tp;   // projection mode: the tail merges proj_kernel's records (decode_proj.cuh)
     float* dbg_lp; int32_t* dbg_tok; uint8_t* dbg_flags; int32_t* dbg_fin_count; int32_t* dbg_fin_source; double* dbg_fin_score;
     DevStatus* status;
 };
@@ -553,23 +553,41 @@ __device__ __forceinline__ RowOut merge_row(const StepParams& p, int row, const 
 }
 
 
-// Projection mode (decode_proj.cuh): the row's list is one record per vocab tile, {max, sum, -, -} v[Kp] id[Kp], whose
-// v / id are the tile's exact best IDS in (value desc, id asc) order -- so the best K of their union are the row's best K,
-// ties included, and there is nothing to read again.  Lane l takes tiles l, l + 32, ...
-__device__ __forceinline__ RowOut merge_row_proj(const StepParams& p, int row, WarpBuf& wb) {
+// Projection mode (decode_proj.cuh): the row's list is one record per vocab tile, stored as planes [plane][tile] -- max,
+// sum, then the tile's best K values and their ids in (value desc, id asc) order: exact ids, so the best K of their union
+// are the row's best K, ties included, and there is nothing to read again.  The three planes every tile contributes to
+// (max, sum, best value) come into the warp's shared-memory slice with one bulk copy each; the loops over them are
+// rolled (this code runs once per launch: what it costs is its instruction fetch).
+__device__ __forceinline__ RowOut merge_row_proj(const StepParams& p, int row, WarpBuf& wb, unsigned char* slice) {
     const int lane = threadIdx.x & 31;
-    const int K = p.K, Kp = (K + 1) & ~1;
-    const unsigned char* __restrict__ recs = p.proj_parts + (int64_t)row * p.proj_tiles * p.proj_rec;
+    const int K = p.K, T = p.proj_tiles, TP = p.proj_tp;
+    const float* __restrict__ planes = p.proj_parts + (int64_t)row * (2 + 2 * K) * TP;
+    const float* pm = planes; const float* ps = planes + TP; const float* pv0 = planes + 2 * TP;
+    if (3 * TP * 4 <= kTailLists - 16) {
+        float* sm = reinterpret_cast<float*>(slice);
+        unsigned long long* bar = reinterpret_cast<unsigned long long*>(slice + kTailLists - 16);
+        if (lane == 0) {
+            mbar_init(bar, 1);
+            fence_proxy_async();
+            mbar_expect_tx(bar, 3u * TP * 4u);
+            bulk_g2s(sm, planes, 3u * TP * 4u, bar);      // the three planes are adjacent
+        }
+        __syncwarp();
+        mbar_wait(bar, 0u);
+        pm = sm; ps = sm + TP; pv0 = sm + 2 * TP;
+    }
     // ---- pass A: partition maxima and sums, folded lane-locally first
     float am0 = -CUDART_INF_F, am1 = -CUDART_INF_F, as0 = 0.0f, as1 = 0.0f;
     bool nan_seen = false;
-    for (int t = lane; t < p.proj_tiles; t += 32) {
-        const float4 h = __ldcg(reinterpret_cast<const float4*>(recs + (int64_t)t * p.proj_rec));
-        if (h.y != h.y) { nan_seen = true; continue; }
-        float& am = t < p.proj_text_tiles ? am0 : am1;
-        float& as = t < p.proj_text_tiles ? as0 : as1;
-        if (h.x > am) { as = as * exp_diff(am, h.x) + h.y; am = h.x; }
-        else as += h.y * exp_diff(h.x, am);
+#pragma unroll 1
+    for (int t = lane; t < T; t += 32) {
+        const float hm = pm[t], hs = ps[t];
+        if (hs != hs) { nan_seen = true; continue; }
+        if (t < p.proj_text_tiles) {
+            if (hm > am0) { as0 = as0 * exp_diff(am0, hm) + hs; am0 = hm; } else as0 += hs * exp_diff(hm, am0);
+        } else {
+            if (hm > am1) { as1 = as1 * exp_diff(am1, hm) + hs; am1 = hm; } else as1 += hs * exp_diff(hm, am1);
+        }
     }
     float M[2], S[2];
     {
@@ -598,18 +616,22 @@ __device__ __forceinline__ RowOut merge_row_proj(const StepParams& p, int row, W
     // ---- pass B: a value at least K candidates reach (K rounds over the lanes' best heads), then everything at or above it
     const int t_first = ts_over_text ? p.proj_text_tiles : 0;
     float head = -CUDART_INF_F;
-    for (int t = lane; t < p.proj_tiles; t += 32)
-        if (t >= t_first) head = fmaxf(head, __ldcg(reinterpret_cast<const float*>(recs + (int64_t)t * p.proj_rec + 16)));
+#pragma unroll 1
+    for (int t = lane; t < T; t += 32)
+        if (t >= t_first) head = fmaxf(head, pv0[t]);
     const float tau = kth_threshold(head, K);
-    for (int t = lane; t < p.proj_tiles; t += 32) {
+    const float* gv = planes + 2 * TP;                                   // value planes and id planes in global memory
+    const int* gi = reinterpret_cast<const int*>(planes + (2 + K) * TP);
+#pragma unroll 1
+    for (int t = lane; t < T; t += 32) {
         if (t < t_first) continue;
-        const float* rv = reinterpret_cast<const float*>(recs + (int64_t)t * p.proj_rec + 16);
-        const int* ri = reinterpret_cast<const int*>(rv + Kp);
-        for (int e = 0; e < K; ++e) {
-            const float v = __ldcg(rv + e);
-            if (!(v >= tau) || v == -CUDART_INF_F) break;               // (lists are sorted)
+        float v = pv0[t];
+#pragma unroll 1
+        for (int e = 0; e < K; ++e) {                                    // (lists are sorted: stop at the first entry below tau)
+            if (e > 0) v = __ldcg(gv + (int64_t)e * TP + t);
+            if (!(v >= tau) || v == -CUDART_INF_F) break;
             const int slot = atomicAdd(&wb.n, 1);
-            if (slot < kCandCap) { wb.v[slot] = v; wb.id[slot] = __ldcg(ri + e); }
+            if (slot < kCandCap) { wb.v[slot] = v; wb.id[slot] = __ldcg(gi + (int64_t)e * TP + t); }
         }
     }
     __syncwarp();
@@ -624,12 +646,10 @@ __device__ __forceinline__ RowOut merge_row_proj(const StepParams& p, int row, W
         float pv = CUDART_INF_F; int pi = -1;
         for (int rnd = 0; rnd < K; ++rnd) {
             float bv = -CUDART_INF_F; int bi = INT32_MAX;
-            for (int t = lane; t < p.proj_tiles; t += 32) {
+            for (int t = lane; t < T; t += 32) {
                 if (t < t_first) continue;
-                const float* rv = reinterpret_cast<const float*>(recs + (int64_t)t * p.proj_rec + 16);
-                const int* ri = reinterpret_cast<const int*>(rv + Kp);
                 for (int e = 0; e < K; ++e) {
-                    const float v = __ldcg(rv + e); const int id = __ldcg(ri + e);
+                    const float v = __ldcg(gv + (int64_t)e * TP + t); const int id = __ldcg(gi + (int64_t)e * TP + t);
                     if (v == -CUDART_INF_F || !(v == v)) break;
                     const bool after = v < pv || (v == pv && id > pi);
                     if (after) { if (better(v, id, bv, bi)) { bv = v; bi = id; } break; }   // the first entry after the pick is the list's best
@@ -1200,7 +1220,7 @@ __global__ void __launch_bounds__(kMaxBeam * 32) decode_tail_kernel(const StepPa
     if (lane == 0) wb.n = 0;
     __syncwarp();
     const RowRules rr_row = row_rules_from(p.rc, tk_last, tk_pen, p.cur_len, p.sample_begin);
-    RowOut r = p.proj_parts ? merge_row_proj(p, row, wb) : merge_row(p, row, rr_row, wb, slice, glist);
+    RowOut r = p.proj_parts ? merge_row_proj(p, row, wb, slice) : merge_row(p, row, rr_row, wb, slice, glist);
     r.flags |= rr_row.flags;
     unsigned same = 0u;
     if (MODE == MODE_BEAM) {
@@ -1339,7 +1359,12 @@ int launch_proj(wrs_projection* pj, ProjParams q, const float* x, int64_t x_stri
     const size_t smem = sizeof(ProjSmem) + sizeof(uint32_t) * (dec->bm_words + 2);
     if (!pj->attr_set) {
         WRS_CUDA(ctx, cudaFuncSetAttribute(proj_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        WRS_CUDA(ctx, cudaFuncSetAttribute(proj_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        WRS_CUDA(ctx, cudaFuncSetAttribute(proj_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        WRS_CUDA(ctx, cudaFuncSetAttribute(proj_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        WRS_CUDA(ctx, cudaFuncSetAttribute(proj_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        WRS_CUDA(ctx, cudaFuncSetAttribute(proj_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        WRS_CUDA(ctx, cudaFuncSetAttribute(proj_kernel<12>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        WRS_CUDA(ctx, cudaFuncSetAttribute(proj_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         pj->attr_set = true;
     }
     q.wp = pj->d_wp; q.xp = pj->d_xp;
@@ -1433,6 +1458,11 @@ void set_debug(StepParams& p, const wrs_step_debug* dbg) {
 
 extern "C" {
 
+#ifdef WRS_EXP_PJ_TIMES
+int wrs_debug_pj_times(unsigned long long* out_host, int n) {
+    return (int)cudaMemcpyFromSymbol(out_host, wrs::g_pj_times, sizeof(unsigned long long) * n);
+}
+#endif
 #ifdef WRS_TRACE
 int wrs_debug_trace_read(unsigned long long* out_host, int n) {
     return (int)cudaMemcpyFromSymbol(out_host, wrs::g_trace, sizeof(unsigned long long) * n);
@@ -1620,7 +1650,7 @@ int wrs_projection_create(wrs_decoder* dec, const float* token_emb, int64_t emb_
     pj->max_mtiles = (dec->max_rows + kPM - 1) / kPM;
     const size_t wbytes = (size_t)pj->n_tiles * pj->n_kstages * 2 * kPBBytes;
     const size_t xbytes = (size_t)pj->max_mtiles * pj->n_kstages * 2 * kPABytes;
-    const size_t pbytes = (size_t)dec->max_rows * pj->n_tiles * (16 + 8 * kMaxK);
+    const size_t pbytes = sizeof(float) * (size_t)dec->max_rows * (2 + 2 * kMaxK) * ((pj->n_tiles + 3) & ~3);
     cudaError_t e;
     if ((e = cudaMalloc(&pj->d_wp, wbytes)) != cudaSuccess || (e = cudaMalloc(&pj->d_xp, xbytes)) != cudaSuccess ||
         (e = cudaMalloc(&pj->d_parts, pbytes)) != cudaSuccess) {
@@ -1679,15 +1709,16 @@ int wrs_project_beam_step(wrs_projection* pj, const float* x, int64_t x_stride, 
     p.sum_in = sum_in; p.sum_out = sum_out; p.next_tokens = next_tokens; p.next_stride = next_stride;
     p.source_idx = source_idx; p.completed = completed;
     set_debug(p, dbg);
-    const int Kp = (p.K + 1) & ~1;
-    p.proj_parts = pj->d_parts; p.proj_tiles = pj->n_tiles; p.proj_text_tiles = pj->n_text_tiles; p.proj_rec = 16 + 8 * Kp;
+    p.proj_parts = pj->d_parts; p.proj_tiles = pj->n_tiles; p.proj_text_tiles = pj->n_text_tiles; p.proj_tp = (pj->n_tiles + 3) & ~3;
     ProjParams q;
     memset(&q, 0, sizeof(q));
     q.n_rows = (int)n_rows; q.tokens = tokens; q.tok_stride = tok_stride; q.cur_len = p.cur_len; q.sample_begin = p.sample_begin;
-    q.K = p.K; q.rc = p.rc; q.bm = p.bm; q.bm_words = p.bm_words; q.parts = pj->d_parts; q.rec_bytes = p.proj_rec;
+    q.K = p.K; q.rc = p.rc; q.bm = p.bm; q.bm_words = p.bm_words; q.parts = pj->d_parts; q.tiles_padded = p.proj_tp;
     rc = ensure_tail_attrs(dec);
     if (rc != WRS_OK) return rc;
-    rc = launch_proj<1>(pj, q, x, x_stride, stream);
+    rc = p.K <= 2 ? launch_proj<2>(pj, q, x, x_stride, stream) : p.K <= 4 ? launch_proj<4>(pj, q, x, x_stride, stream)
+       : p.K <= 6 ? launch_proj<6>(pj, q, x, x_stride, stream) : p.K <= 8 ? launch_proj<8>(pj, q, x, x_stride, stream)
+       : p.K <= 12 ? launch_proj<12>(pj, q, x, x_stride, stream) : launch_proj<16>(pj, q, x, x_stride, stream);
     if (rc != WRS_OK) return rc;
     decode_tail_kernel<MODE_BEAM><<<p.n_rows / p.beam, p.beam * 32, (size_t)kTailHead + (size_t)p.beam * kTailBytes, stream>>>(p);
     WRS_CUDA(ctx, cudaGetLastError());

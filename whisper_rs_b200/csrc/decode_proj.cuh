@@ -35,7 +35,9 @@ constexpr int kPM = 128;                                  // rows per M tile
 constexpr int kPN = 176;                                  // ids per vocab tile (a multiple of 16, at most 256)
 constexpr int kPK = 32;                                   // elements of n_state per pipeline stage (two MMA K steps)
 constexpr int kPStages = 4;
-constexpr int kPThreads = 192;
+constexpr int kPEpiWarps = 16;                            // warps 0-7 select (top-K), warps 8-15 sum (max, sum exp); of each
+                                                          // eight, warps {4g .. 4g+3} drain accumulator g
+constexpr int kPThreads = (kPEpiWarps + 2) * 32;
 constexpr int kPABytes = kPM * kPK * 2;                   // one part (hi or lo) of a stage of x: 8 KB
 constexpr int kPBBytes = kPN * kPK * 2;                   // ... of the weights: 11 KB
 constexpr int kPStageBytes = 2 * kPABytes + 2 * kPBBytes; // [A hi | A lo | B hi | B lo] = 38 912 B
@@ -51,7 +53,9 @@ struct ProjParams {
     // EPI 1: fold
     const int64_t* tokens; int64_t tok_stride; int cur_len, sample_begin, K;
     RuleCfg rc; const uint32_t* bm; int bm_words;
-    unsigned char* parts; int rec_bytes;                  // records [row][tile]: {max, sum, 0, 0} v[Kp] id[Kp]
+    // records, one per (row, vocab tile), as planes of 4-byte words: parts[(row * (2 + 2K) + plane) * tiles_padded + tile];
+    // planes: 0 max, 1 sum, 2 .. 2+K-1 the tile's best values (value desc, id asc), 2+K .. their ids
+    float* parts; int tiles_padded;
 };
 
 __host__ __device__ __forceinline__ int proj_tile_base(int tile, int n_text_tiles, int ts_split) {
@@ -109,18 +113,22 @@ __global__ void proj_pack_kernel(const float* __restrict__ src, int64_t src_stri
 }
 
 // mbarrier wait with a bound: a pipeline that stops (a bug, never a data condition) ends the launch with an error
-// instead of hanging the device
+// instead of hanging the device.  The hardware parks the warp (suspend-time hint) and, between tries, the warp sleeps:
+// ten of a CTA's eighteen warps are waiting at any time, and a waiting warp that spins takes issue slots from the one
+// epilogue warp of its scheduler that is working (measured: 5 cycles per instruction there, before).
+template <int SLEEP_NS>
 __device__ __forceinline__ void mbar_wait_b(unsigned long long* bar, unsigned parity) {
     for (unsigned spins = 0;; ++spins) {
         unsigned done;
         asm volatile(
             "{\n"
             ".reg .pred p;\n"
-            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n"
             "selp.u32 %0, 1, 0, p;\n"
-            "}\n" : "=r"(done) : "r"(smem_addr(bar)), "r"(parity) : "memory");
+            "}\n" : "=r"(done) : "r"(smem_addr(bar)), "r"(parity), "r"(0x989680u) : "memory");
         if (done) return;
-        if (spins > (1u << 24)) __trap();
+        if (SLEEP_NS > 0) __nanosleep(SLEEP_NS);
+        if (spins > (1u << 22)) __trap();
     }
 }
 
@@ -179,10 +187,13 @@ __device__ __forceinline__ void tc_ld16(unsigned taddr, float (&x)[32]) {
 }
 
 // ---- epilogue (EPI 1): what a thread keeps for its row within one vocab tile
+template <int KM>
 struct ProjRow {
-    float m, s;                                          // max and sum exp(x - m) of the surviving ids so far
-    float v[kMaxK]; int id[kMaxK];                       // the best so far, (value desc, id asc); -inf / INT32_MAX = empty
-    float kth;                                           // v[K - 1]
+    // the best so far, (value desc, id asc), right-aligned: the K live entries are v[KM - K .. KM) (-inf / INT32_MAX =
+    // empty), in front of them +inf sentinels that nothing displaces -- so the K-th best is always v[KM - 1]
+    float v[KM]; int id[KM];
+    float kth;                                           // max(v[KM - 1], floor)
+    float floor;                                         // nothing at or below it can be among the row's best K (see proj_kernel)
 };
 
 __device__ __forceinline__ unsigned range_bits(int lo, int hi) {   // bits i of a 32-bit word with lo <= i < hi
@@ -191,73 +202,128 @@ __device__ __forceinline__ unsigned range_bits(int lo, int hi) {   // bits i of 
     return (0xffffffffu << lo) & (hi >= 32 ? 0xffffffffu : (1u << hi) - 1u);
 }
 
-// ids arrive in ascending order, so a new entry goes behind every entry of equal value: strict comparisons only
-__device__ __forceinline__ void proj_insert(ProjRow& st, float x, int nid, int K) {
+// ids arrive in ascending order, so a new entry goes behind every entry of equal value: strict comparisons only.
+// Branch-free: every slot picks among {its own entry, its left neighbour's, the new one} from two comparisons against the
+// OLD list, so the whole insertion is one layer of selects (a value that does not beat the K-th best changes nothing).
+template <int KM>
+__device__ __forceinline__ void proj_insert(ProjRow<KM>& st, float x, int nid) {
+    x = x > st.kth ? x : -CUDART_INF_F;                  // (also keeps out what a carried floor excludes)
+    bool gt[KM];
 #pragma unroll
-    for (int e = kMaxK - 1; e >= 1; --e) {
-        if (x > st.v[e - 1]) { st.v[e] = st.v[e - 1]; st.id[e] = st.id[e - 1]; }
-        else if (x > st.v[e]) { st.v[e] = x; st.id[e] = nid; }
+    for (int e = 0; e < KM; ++e) gt[e] = x > st.v[e];
+#pragma unroll
+    for (int e = KM - 1; e >= 1; --e) {
+        st.v[e] = gt[e - 1] ? st.v[e - 1] : (gt[e] ? x : st.v[e]);
+        st.id[e] = gt[e - 1] ? st.id[e - 1] : (gt[e] ? nid : st.id[e]);
     }
-    if (x > st.v[0]) { st.v[0] = x; st.id[0] = nid; }
-    float k = st.v[0];
-#pragma unroll
-    for (int e = 1; e < kMaxK; ++e) k = (e == K - 1) ? st.v[e] : k;
-    st.kth = k;
+    st.v[0] = gt[0] ? x : st.v[0];
+    st.id[0] = gt[0] ? nid : st.id[0];
+    st.kth = fmaxf(st.v[KM - 1], st.floor);
 }
 
-// 32 columns of the row's accumulator (ids id0 .. id0 + 31; `valid` bit i: id0 + i survives the filters)
-__device__ __forceinline__ void proj_fold32(ProjRow& st, float (&x)[32], unsigned valid, int id0, int K) {
+// 32 columns of the row's accumulator (ids id0 .. id0 + 31; `valid` bit i: id0 + i survives the filters): masked ids
+// become -inf, the chunk maximum is returned (NaN operands are ignored by fmaxf: the callers look for them)
+__device__ __forceinline__ float proj_mask32(float (&x)[32], unsigned valid) {
     if (valid != 0xffffffffu) {
 #pragma unroll
         for (int i = 0; i < 32; ++i) x[i] = (valid & (1u << i)) ? x[i] : -CUDART_INF_F;
     }
-    float cm = x[0];
+    float t[8];                                          // (a tree, not a chain: one warp per scheduler lives on latency)
 #pragma unroll
-    for (int i = 1; i < 32; ++i) cm = fmaxf(cm, x[i]);   // (NaN operands are ignored: handled below)
+    for (int i = 0; i < 8; ++i) t[i] = fmaxf(fmaxf(x[4 * i], x[4 * i + 1]), fmaxf(x[4 * i + 2], x[4 * i + 3]));
+    return fmaxf(fmaxf(fmaxf(t[0], t[1]), fmaxf(t[2], t[3])), fmaxf(fmaxf(t[4], t[5]), fmaxf(t[6], t[7])));
+}
+
+// the statistics half of the epilogue: online {max, sum exp(x - max)} of the survivors
+__device__ __forceinline__ void proj_stats32(float& m, float& s, float (&x)[32], unsigned valid) {
+    const float cm = proj_mask32(x, valid);
     if (cm == -CUDART_INF_F || cm != cm) {
         // nothing finite: the sum is unchanged unless a NaN is among the survivors (then it is NaN, as in ATen)
         bool bad = false;
 #pragma unroll
         for (int i = 0; i < 32; ++i) bad |= x[i] != x[i];
-        if (bad) st.s = CUDART_NAN_F;
+        if (bad) s = CUDART_NAN_F;
         return;
     }
-    if (cm > st.m) { st.s *= ex2((st.m - cm) * kLog2e); st.m = cm; }
-    float acc0 = 0.0f, acc1 = 0.0f;
+    if (cm > m) { s *= ex2((m - cm) * kLog2e); m = cm; }
+#ifndef WRS_EXP_PJ_NOSUM
+    float acc0 = 0.0f, acc1 = 0.0f, acc2 = 0.0f, acc3 = 0.0f;
+    const float mb = -m * kLog2e;
 #pragma unroll
-    for (int i = 0; i < 32; i += 2) {
-        acc0 += ex2((x[i] - st.m) * kLog2e);
-        acc1 += ex2((x[i + 1] - st.m) * kLog2e);
+    for (int i = 0; i < 32; i += 4) {
+        acc0 += ex2(fmaf(x[i], kLog2e, mb));
+        acc1 += ex2(fmaf(x[i + 1], kLog2e, mb));
+        acc2 += ex2(fmaf(x[i + 2], kLog2e, mb));
+        acc3 += ex2(fmaf(x[i + 3], kLog2e, mb));
     }
-    st.s += acc0 + acc1;
-    if (cm > st.kth) {
-#pragma unroll
-        for (int i = 0; i < 32; ++i)
-            if (x[i] > st.kth) proj_insert(st, x[i], id0 + i, K);
-    }
+    s += (acc0 + acc1) + (acc2 + acc3);
+#endif
 }
+
+// the selection half: the chunk's survivors that beat the row's K-th best so far enter its list.  xs: the thread's
+// column of its warp's [32][32] staging tile in shared memory (element i at xs[32 i]): the few candidates are picked out
+// of it by index -- one copy of the insertion code, run about K ln(176 / K) times per fresh tile, instead of one
+// predicated copy per element.
+template <int KM>
+__device__ __forceinline__ void proj_topk32(ProjRow<KM>& st, float (&x)[32], unsigned valid, int id0, float* xs) {
+    const float cm = proj_mask32(x, valid);
+#ifndef WRS_EXP_PJ_NOINS
+    if (cm > st.kth) {
+        unsigned c4[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+        for (int i = 0; i < 32; ++i) {
+            c4[i & 3] |= (x[i] > st.kth) ? (1u << i) : 0u;
+            xs[32 * i] = x[i];
+        }
+        unsigned cand = (c4[0] | c4[1]) | (c4[2] | c4[3]);
+        // one candidate per round, the next one's value already on its way from shared memory
+        int i = __ffs((int)cand) - 1;
+        float v = xs[32 * i];
+        cand &= cand - 1u;
+        for (;;) {
+            const int i_now = i; const float v_now = v;
+            const bool more = cand != 0u;
+            if (more) { i = __ffs((int)cand) - 1; v = xs[32 * i]; cand &= cand - 1u; }
+            proj_insert<KM>(st, v_now, id0 + i_now);
+            if (!more) break;
+        }
+    }
+#endif
+}
+
+#ifdef WRS_EXP_PJ_TIMES
+// investigation aid (tools/proj_variants.py): per CTA, globaltimer stamps of [unit][mma start, mma issued, epi start, epi end]
+__device__ unsigned long long g_pj_times[148 * 32];
+__device__ __forceinline__ unsigned long long pj_now() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define WRS_PJ_T(u, k) do { if ((u) < 8) g_pj_times[blockIdx.x * 32 + (u) * 4 + (k)] = pj_now(); } while (0)
+#else
+#define WRS_PJ_T(u, k) do {} while (0)
+#endif
 
 struct ProjSmem {
     unsigned char stage[kPStages][kPStageBytes];
     unsigned long long full[kPStages], empty[kPStages], tfull[2], tempty[2];
     unsigned tmem_base;
     unsigned pad[3];
+    float xstage[kPEpiWarps / 2][32 * 32];                            // epilogue warps: [element][lane] staging of one chunk
     uint32_t bm[1];                                      // the suppress bitmap, bm_words + 2 words (EPI 1)
 };
 
+// EPI 0: store the logits; EPI 2, 4, 6, 8, 12, 16: fold, with room for K <= EPI candidates per (row, tile)
 template <int EPI>
 __global__ void __launch_bounds__(kPThreads, 1) proj_kernel(const ProjParams p) {
+    constexpr int KM = EPI == 0 ? 1 : EPI;
     extern __shared__ __align__(1024) unsigned char proj_smem_raw[];
     ProjSmem& sm = *reinterpret_cast<ProjSmem*>(proj_smem_raw);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
         for (int s = 0; s < kPStages; ++s) { mbar_init(&sm.full[s], 1); mbar_init(&sm.empty[s], 1); }
-        for (int b = 0; b < 2; ++b) { mbar_init(&sm.tfull[b], 1); mbar_init(&sm.tempty[b], 4); }
+        for (int b = 0; b < 2; ++b) { mbar_init(&sm.tfull[b], 1); mbar_init(&sm.tempty[b], 8); }
     }
-    if (EPI == 1)
+    if (EPI != 0)
         for (int i = threadIdx.x; i < p.bm_words + 2; i += kPThreads) sm.bm[i] = i < p.bm_words ? p.bm[i] : 0u;
     __syncwarp();
-    if (warp == 5) {
+    if (warp == kPEpiWarps + 1) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_addr(&sm.tmem_base)), "r"(kPTmemCols) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
@@ -268,7 +334,7 @@ __global__ void __launch_bounds__(kPThreads, 1) proj_kernel(const ProjParams p) 
     const int my_tiles = ((int)blockIdx.x < p.n_tiles) ? (p.n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
     const int n_units = my_tiles * p.n_mtiles;           // accumulations of this CTA: unit u = (tile u / n_mtiles, M tile u % n_mtiles)
 
-    if (warp == 4) {
+    if (warp == kPEpiWarps) {
         // ================================================= producer
         if (lane == 0) {
             unsigned it = 0;
@@ -276,27 +342,39 @@ __global__ void __launch_bounds__(kPThreads, 1) proj_kernel(const ProjParams p) 
                 const int tile = (int)blockIdx.x + (u / p.n_mtiles) * (int)gridDim.x, mt = u % p.n_mtiles;
                 const unsigned char* a = p.xp + (int64_t)mt * p.n_kstages * (2 * kPABytes);
                 const unsigned char* b = p.wp + (int64_t)tile * p.n_kstages * (2 * kPBBytes);
+                const int rows_real = min(kPM, p.n_rows - mt * kPM);
                 for (int ks = 0; ks < p.n_kstages; ++ks, ++it) {
                     const unsigned slot = it % kPStages, round = it / kPStages;
-                    mbar_wait_b(&sm.empty[slot], (round & 1u) ^ 1u);      // (a fresh barrier passes the first round)
-                    mbar_expect_tx(&sm.full[slot], (unsigned)kPStageBytes);
-                    bulk_g2s(sm.stage[slot], a + (int64_t)ks * (2 * kPABytes), 2 * kPABytes, &sm.full[slot]);
+                    mbar_wait_b<0>(&sm.empty[slot], (round & 1u) ^ 1u);      // (a fresh barrier passes the first round)
+                    if (rows_real <= kPM / 2) {
+                        // a mostly empty M tile: only its real rows travel (8 runs of rows x 16 B); what the other rows of
+                        // the stage hold is left over from an earlier unit and only reaches accumulator rows nobody reads
+                        const unsigned run = (unsigned)rows_real * 16u;
+                        mbar_expect_tx(&sm.full[slot], 8u * run + 2u * kPBBytes);
+#pragma unroll
+                        for (int q = 0; q < 8; ++q)
+                            bulk_g2s(sm.stage[slot] + q * (kPM * 16), a + (int64_t)ks * (2 * kPABytes) + q * (kPM * 16), run, &sm.full[slot]);
+                    } else {
+                        mbar_expect_tx(&sm.full[slot], (unsigned)kPStageBytes);
+                        bulk_g2s(sm.stage[slot], a + (int64_t)ks * (2 * kPABytes), 2 * kPABytes, &sm.full[slot]);
+                    }
                     bulk_g2s(sm.stage[slot] + 2 * kPABytes, b + (int64_t)ks * (2 * kPBBytes), 2 * kPBBytes, &sm.full[slot]);
                 }
             }
         }
-    } else if (warp == 5) {
+    } else if (warp == kPEpiWarps + 1) {
         // ================================================= MMA issuer
         if (lane == 0) {
             unsigned it = 0;
             for (int u = 0; u < n_units; ++u) {
                 const unsigned buf = (unsigned)u & 1u, use = (unsigned)u >> 1;
-                mbar_wait_b(&sm.tempty[buf], (use & 1u) ^ 1u);            // the epilogue has drained this accumulator
+                mbar_wait_b<100>(&sm.tempty[buf], (use & 1u) ^ 1u);            // the epilogue has drained this accumulator
                 tc_fence_after();
+                WRS_PJ_T(u, 0);
                 const unsigned d = tmem + buf * kPAccStride;
                 for (int ks = 0; ks < p.n_kstages; ++ks, ++it) {
                     const unsigned slot = it % kPStages, round = it / kPStages;
-                    mbar_wait_b(&sm.full[slot], round & 1u);
+                    mbar_wait_b<0>(&sm.full[slot], round & 1u);
                     tc_fence_after();
                     const unsigned a_hi = smem_addr(sm.stage[slot]), a_lo = a_hi + kPABytes;
                     const unsigned b_hi = a_hi + 2 * kPABytes, b_lo = b_hi + kPBBytes;
@@ -305,42 +383,77 @@ __global__ void __launch_bounds__(kPThreads, 1) proj_kernel(const ProjParams p) 
                         const unsigned ao = j * 2 * (kPM * 16), bo = j * 2 * (kPN * 16);
                         const unsigned long long dah = tc_desc(a_hi + ao, kPM * 16, 128), dal = tc_desc(a_lo + ao, kPM * 16, 128);
                         const unsigned long long dbh = tc_desc(b_hi + bo, kPN * 16, 128), dbl = tc_desc(b_lo + bo, kPN * 16, 128);
+#if defined(WRS_EXP_PJ_NOMMA)
+                        (void)dal; (void)dbl; (void)dah; (void)dbh; (void)d;
+#elif defined(WRS_EXP_PJ_ONEPROD)
+                        (void)dal; (void)dbl;
+                        tc_mma(d, dah, dbh, (ks | j) != 0);
+#else
                         tc_mma(d, dal, dbh, (ks | j) != 0);             // the small products first
                         tc_mma(d, dah, dbl, 1u);
                         tc_mma(d, dah, dbh, 1u);
+#endif
                     }
                     tc_commit(&sm.empty[slot]);                         // the stage is free once these MMAs have read it
                 }
                 tc_commit(&sm.tfull[buf]);                              // the accumulator is complete
+                WRS_PJ_T(u, 1);
             }
         }
     } else {
-        // ================================================= epilogue: thread = row of the M tile
-        const unsigned lane_base = (unsigned)(warp * 32) << 16;
-        for (int u = 0; u < n_units; ++u) {
+        // ================================================= epilogue: thread = row of the M tile.  Each accumulator is read by
+        // two warps per TMEM lane quarter (a quarter belongs to warp % 4): a SELECT warp (0-7) keeps the row's best K of
+        // the tile, a SUM warp (8-15) its {max, sum exp}; of each eight, warps 0-3 take the even units (accumulator 0),
+        // warps 4-7 the odd ones.  The two never talk: each writes its own planes of the row's record.
+        // A select thread that meets the same row again in a later tile of the same partition (always, with one or two M
+        // tiles) carries a floor over: the K-th best value it has seen there bounds the row's K-th best from below, so only
+        // values at or above it (ties can still win on the id) need to enter the new tile's list.
+        const bool sums = warp >= kPEpiWarps / 2;
+        const int ew = warp & (kPEpiWarps / 2 - 1);
+        const unsigned lane_base = (unsigned)((ew & 3) * 32) << 16;
+        float* const xmine = sm.xstage[ew] + lane;
+        int prev_row = -1, prev_part = -1;
+        float tau_run = -CUDART_INF_F;
+        for (int u = ew >> 2; u < n_units; u += 2) {
             const int tile = (int)blockIdx.x + (u / p.n_mtiles) * (int)gridDim.x, mt = u % p.n_mtiles;
             const unsigned buf = (unsigned)u & 1u, use = (unsigned)u >> 1;
-            const int row = mt * kPM + (int)threadIdx.x;
+            const int row = mt * kPM + (int)(threadIdx.x & 127);
             const int base = proj_tile_base(tile, p.n_text_tiles, p.ts_split);
             const int end = proj_tile_end(tile, p.n_text_tiles, p.ts_split, p.n_vocab);
-            ProjRow st;
+            ProjRow<KM> st;
+            float sm_m = -CUDART_INF_F, sm_s = 0.0f;
             RowRules rr;
-            if (EPI == 1) {
-                st.m = -CUDART_INF_F; st.s = 0.0f; st.kth = -CUDART_INF_F;
+            if (EPI != 0) {
+                const int part = tile < p.n_text_tiles ? 0 : 1;
+                if (row != prev_row || part != prev_part) tau_run = -CUDART_INF_F;
+                prev_row = row; prev_part = part;
+                // the largest float below tau_run: "x > floor" is "x >= tau_run"
+                float fl = tau_run;
+                if (fl > -CUDART_INF_F) fl = fl == 0.0f ? -1.4e-45f : __int_as_float(__float_as_int(fl) + (fl > 0.0f ? -1 : 1));
+                st.kth = fl; st.floor = fl;
 #pragma unroll
-                for (int e = 0; e < kMaxK; ++e) { st.v[e] = -CUDART_INF_F; st.id[e] = INT32_MAX; }
+                for (int e = 0; e < KM; ++e) { st.v[e] = e < KM - p.K ? CUDART_INF_F : -CUDART_INF_F; st.id[e] = INT32_MAX; }
                 rr.t_lo = rr.t_hi = rr.s_lo = rr.s_hi = 0; rr.flags = 0u;
                 if (row < p.n_rows) rr = row_rules(p.rc, p.tokens + (int64_t)row * p.tok_stride, p.cur_len, p.sample_begin);
             }
-            mbar_wait_b(&sm.tfull[buf], use & 1u);
+            mbar_wait_b<200>(&sm.tfull[buf], use & 1u);
             tc_fence_after();
+            if (warp == (int)(buf * 4) && lane == 0) WRS_PJ_T(u, 2);
             const unsigned t0 = tmem + buf * kPAccStride + lane_base;
 #pragma unroll 1
             for (int c = 0; c < (kPN + 31) / 32; ++c) {
+                if (EPI == 0 && ((c & 1) != 0) != sums) continue;      // (plain projection: the two warps share the chunks)
                 float x[32];
                 if (32 * c + 32 <= kPN) tc_ld32(t0 + 32 * c, x);
                 else tc_ld16(t0 + 32 * c, x);
                 const int id0 = base + 32 * c;
+#ifdef WRS_EXP_PJ_TIMES
+                if (warp == 0 && lane == 0 && u == 0) g_pj_times[blockIdx.x * 32 + 16 + 2 * c] = pj_now();
+#endif
+#ifdef WRS_EXP_PJ_NOEPI
+                if (x[0] == 123.456f && p.logits) p.logits[0] = 0.0f;
+                continue;
+#endif
                 if (EPI == 0) {
                     if (row < p.n_rows) {
                         float* o = p.logits + (int64_t)row * p.row_stride + id0;
@@ -353,28 +466,36 @@ __global__ void __launch_bounds__(kPThreads, 1) proj_kernel(const ProjParams p) 
                     const unsigned w0 = sm.bm[id0 >> 5], w1 = sm.bm[(id0 >> 5) + 1];
                     const unsigned supp = __funnelshift_r(w0, w1, id0 & 31);
                     const unsigned ok = (range_bits(rr.t_lo - id0, min(rr.t_hi, end) - id0) | range_bits(rr.s_lo - id0, min(rr.s_hi, end) - id0)) & ~supp;
-                    proj_fold32(st, x, ok, id0, p.K);
+                    if (sums) proj_stats32(sm_m, sm_s, x, ok);
+                    else proj_topk32<KM>(st, x, ok, id0, xmine);
                 }
+#ifdef WRS_EXP_PJ_TIMES
+                if (warp == 0 && lane == 0 && u == 0) g_pj_times[blockIdx.x * 32 + 17 + 2 * c] = pj_now();
+#endif
             }
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&sm.tempty[buf]);
-            if (EPI == 1 && row < p.n_rows) {
-                unsigned char* rec = p.parts + ((int64_t)row * p.n_tiles + tile) * p.rec_bytes;
-                *reinterpret_cast<float4*>(rec) = make_float4(st.m, st.s, 0.0f, 0.0f);
-                const int Kp = (p.K + 1) & ~1;
-                float* rv = reinterpret_cast<float*>(rec + 16);
-                int* ri = reinterpret_cast<int*>(rec + 16 + 4 * Kp);
+            if (warp == (int)(buf * 4) && lane == 0) WRS_PJ_T(u, 3);
+            if (EPI != 0 && row < p.n_rows) {
+                float* rec = p.parts + (int64_t)row * (2 + 2 * p.K) * p.tiles_padded + tile;
+                if (sums) {
+                    rec[0] = sm_m; rec[p.tiles_padded] = sm_s;
+                } else {
+                    tau_run = fmaxf(tau_run, st.v[KM - 1]);
+                    float* rv = rec + (int64_t)(2 - (KM - p.K)) * p.tiles_padded;      // plane of list entry e: 2 + e - (KM - K)
+                    int* ri = reinterpret_cast<int*>(rv + (int64_t)p.K * p.tiles_padded);
 #pragma unroll
-                for (int e = 0; e < kMaxK; ++e)
-                    if (e < Kp) { rv[e] = st.v[e]; ri[e] = st.id[e]; }
+                    for (int e = 0; e < KM; ++e)
+                        if (e >= KM - p.K) { rv[(int64_t)e * p.tiles_padded] = st.v[e]; ri[(int64_t)e * p.tiles_padded] = st.id[e]; }
+                }
             }
         }
     }
     // ---- teardown: every tcgen05 operation of this CTA has completed (the epilogue waited for the last commit)
     tc_fence_before();
     __syncthreads();
-    if (warp == 5) {
+    if (warp == kPEpiWarps + 1) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kPTmemCols) : "memory");
     }
