@@ -127,6 +127,7 @@ class DecodeOptions:
     n_text_ctxs: int = 448
     sample_len: Optional[int] = None
     greedy: bool = False
+    greedy_group: int = 1     # TokenExtractMode::Greedy(group_sze), src/decode/extractor/mod.rs:14-18
 
 
 def max_initial_timestamp_index(opt: DecodeOptions) -> Optional[int]:
@@ -403,7 +404,7 @@ def decode_task_reference(model, ids, opt: DecodeOptions, mel: torch.Tensor, pro
     p = DecodePrompt.new(prompt, ids)
     prompt_ref = [p]
     filters = build_filters(opt, ids, prompt_ref)
-    ex = GreedyTokenExtractor(ids.eot) if opt.greedy else BeamSearchTokenExtractor(opt.beam_size, ids.eot, opt.patience)
+    ex = GreedyTokenExtractor(ids.eot, opt.greedy_group) if opt.greedy else BeamSearchTokenExtractor(opt.beam_size, ids.eot, opt.patience)
     n_group = ex.group_size()
     sample_len = opt.sample_len if opt.sample_len is not None else model.dims.n_text_ctxs // 2      # :129-131
     with torch.no_grad():

@@ -43,6 +43,22 @@ fn update(&mut self, model: &Whisper, tokens: Tensor, logits: Tensor, sum_logpro
     (next, i64::from(&done) != 0)                        // the only host read per step, as in the reference loop
 }
 
+// model.rs:519-522: let TextDecoder::forward_hidden return `self.ln.forward(&x)` ([rows, n_ctx, n_state]) and keep the
+// matmul for callers that want logits.  Once per model (the embedding does not change):
+//     wrs_projection_create(dec, token_emb.ws.data_ptr(), token_emb.ws.stride()[0], n_state, stream, &mut proj)
+// decode/mod.rs:257-270: instead of `logits = model.logits(..).i((.., -1))` + filters + extractor.update
+pub fn update_from_hidden(&mut self, tokens: &Tensor, hidden_last: &Tensor /* [rows, n_state] f32, contiguous */,
+                          sum_logprobs: &mut Tensor) -> (Tensor, bool) {
+    let (r, l) = (tokens.size()[0], tokens.size()[1]);
+    let next = Tensor::empty(&[r, l + 1], (Kind::Int64, tokens.device()));
+    let done = Tensor::zeros(&[1], (Kind::Int, tokens.device()));
+    unsafe { check(self.ctx, wrs_project_beam_step(self.proj, hidden_last.data_ptr() as *const f32, hidden_last.stride()[0], r,
+        tokens.data_ptr() as *const i64, tokens.stride()[0], l, self.sample_begin, sum_logprobs.data_ptr() as *const f32,
+        next.data_ptr() as *mut i64, l + 1, self.source_idx.data_ptr() as *mut i32, sum_logprobs.data_ptr() as *mut f32,
+        done.data_ptr() as *mut i32, std::ptr::null(), stream())); }
+    (next, i64::from(&done) != 0)
+}
+
 // model.rs: instead of walking the blocks and calling cache.index() per tensor (24 ATen launches for base.en),
 // collect every `Cached<T>::cache` once and reorder them together; `spare` holds the second buffer set.
 pub fn update_cache(&self, source_idx_dev: *const i32, rows: i64) {

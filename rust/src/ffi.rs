@@ -4,6 +4,7 @@
 use std::os::raw::{c_char, c_int, c_void};
 #[repr(C)] pub struct WrsCtx { _p: [u8; 0] }
 #[repr(C)] pub struct WrsDecoder { _p: [u8; 0] }
+#[repr(C)] pub struct WrsProjection { _p: [u8; 0] }
 #[repr(C)] #[derive(Clone, Copy)]
 pub struct WrsDecodeCfg {
     pub n_vocab: i32, pub eot: i32, pub sot: i32, pub no_timestamps: i32, pub ts_begin: i32, pub no_speech: i32,
@@ -38,6 +39,15 @@ extern "C" {
                          tok_stride: i64, cur_len: i64, sample_begin: i64, sum_in: *const f32, next_tokens: *mut i64,
                          next_stride: i64, source_idx: *mut i32, sum_out: *mut f32, completed: *mut i32,
                          dbg: *const c_void, stream: *mut c_void) -> c_int;
+    pub fn wrs_projection_create(dec: *mut WrsDecoder, token_emb: *const f32, emb_stride: i64, n_state: i32,
+                                 stream: *mut c_void, out: *mut *mut WrsProjection) -> c_int;
+    pub fn wrs_projection_destroy(proj: *mut WrsProjection);
+    pub fn wrs_project_logits(proj: *mut WrsProjection, x: *const f32, x_stride: i64, n_rows: i64, logits: *mut f32,
+                              row_stride: i64, stream: *mut c_void) -> c_int;
+    pub fn wrs_project_beam_step(proj: *mut WrsProjection, x: *const f32, x_stride: i64, n_rows: i64, tokens: *const i64,
+                                 tok_stride: i64, cur_len: i64, sample_begin: i64, sum_in: *const f32,
+                                 next_tokens: *mut i64, next_stride: i64, source_idx: *mut i32, sum_out: *mut f32,
+                                 completed: *mut i32, dbg: *const c_void, stream: *mut c_void) -> c_int;
     pub fn wrs_beam_finalize(dec: *mut WrsDecoder, tokens: *const i64, tok_stride: i64, cur_len: i64, n_rows: i64,
                              sum_logprobs: *const f32, n_cand_cap: i32, out_tokens: *mut i64, out_len: *mut i32,
                              out_scores: *mut f64, out_n_cand: *mut i32, stream: *mut c_void) -> c_int;

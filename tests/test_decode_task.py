@@ -57,7 +57,7 @@ def test_config1_cpu_oracle_pipeline():
 
 
 # ------------------------------------------------------------------------------------------------- GPU
-def run_both(dims, ids, n_audio, *, beam=5, greedy=False, patience=1.0, prompt=None, sample_len=10, fused=True,
+def run_both(dims, ids, n_audio, *, beam=5, greedy=False, group=1, patience=1.0, prompt=None, sample_len=10, fused=True,
              eot_bias=12.0, eot_after=4, seed=3, mel=None, len_penalty=None, flag_cross=False):
     from whisper_rs_b200 import decode as wd
     from whisper_rs_b200.decode.task import DecodeTask
@@ -66,11 +66,11 @@ def run_both(dims, ids, n_audio, *, beam=5, greedy=False, patience=1.0, prompt=N
         mel = torch.randn(n_audio, 80, 3000, generator=g).cuda()
     mk = lambda backend: tw.ToyWhisper(dims, "cuda", seed, backend, eot=ids.eot, eot_bias=eot_bias, eot_after=eot_after,
                                        flag_cross_invariant=flag_cross and backend == "wrs")
-    mode = wd.TokenExtractMode.Greedy(1) if greedy else wd.TokenExtractMode.BeamSearch(beam, patience)
+    mode = wd.TokenExtractMode.Greedy(group) if greedy else wd.TokenExtractMode.BeamSearch(beam, patience)
     task = DecodeTask(mk("wrs"), ids, wd.DecodeOptions(token_extract_mode=mode, sample_len=sample_len, len_penalty=len_penalty),
                       prompt=prompt, max_audio=n_audio, fused=fused)
     got = task.run(mel)
-    oopt = od.DecodeOptions(beam_size=beam, patience=patience, greedy=greedy, sample_len=sample_len, len_penalty=len_penalty)
+    oopt = od.DecodeOptions(beam_size=beam, patience=patience, greedy=greedy, greedy_group=group, sample_len=sample_len, len_penalty=len_penalty)
     oprompt = None if prompt is None else torch.tensor(prompt, dtype=torch.int64)
     omodel = mk("oracle")
     want = od.decode_task_reference(omodel, ids, oopt, mel, oprompt)
@@ -129,6 +129,21 @@ def test_greedy_task_matches_oracle():
     dims = tw.ModelDims(n_vocab=ids.n_vocab)
     got, want, _, _ = run_both(dims, ids, 5, greedy=True, sample_len=9, eot_bias=25.0)
     assert_same(got, want)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("fused", [True, False])
+def test_greedy_task_with_groups_of_three(fused):
+    """TokenExtractMode::Greedy(3) (src/decode/extractor/mod.rs:14-18): three identical rows per audio; every audio must
+    get the best of ITS OWN group (finalize groups rows by audio), i.e. what Greedy(1) gives it."""
+    ids = C.GPT2_EN
+    dims = tw.ModelDims(n_vocab=ids.n_vocab)
+    got, want, _, _ = run_both(dims, ids, 4, greedy=True, group=3, sample_len=9, eot_bias=6.0, fused=fused)
+    assert_same(got, want)
+    single, _, _, _ = run_both(dims, ids, 4, greedy=True, group=1, sample_len=9, eot_bias=6.0, fused=fused)
+    assert [g.tokens for g in got] == [g.tokens for g in single]
+    assert [g.avg_logprob for g in got] == pytest.approx([g.avg_logprob for g in single], rel=1e-6)
+    assert len({(tuple(g.tokens), round(g.avg_logprob, 6)) for g in got}) > 1   # (the audios do differ: a mix-up would show)
 
 
 @pytest.mark.gpu

@@ -4,10 +4,10 @@ import json, os, subprocess, sys
 tag = sys.argv[1]
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 GO, PR = os.path.join(ROOT, "gpurun_out"), os.path.join(ROOT, "profiles")
-kernels = ["logmel_kernel", "decode_scan_kernel", "decode_tail_kernel", "no_speech_kernel", "kv_reorder_kernel"]
+kernels = ["logmel_kernel", "decode_scan_kernel", "decode_tail_kernel", "no_speech_kernel", "kv_reorder_kernel", "proj_kernel"]
 mangled = {"logmel_kernel": "logmel_kernelILb1", "decode_scan_kernel": "decode_scan_kernel", "decode_tail_kernel": "decode_tail_kernelILi0",
-           "no_speech_kernel": "no_speech_kernel", "kv_reorder_kernel": "kv_reorder_kernel"}
-traffic = {"source": f"ncu --set full --clock-control none, one launch per kernel of `python bench.py --no-cpu-baseline --only decode,kv --steps 8 "
+           "no_speech_kernel": "no_speech_kernel", "kv_reorder_kernel": "kv_reorder_kernel", "proj_kernel": "proj_kernelILi6E"}
+traffic = {"source": f"ncu --set full --clock-control none, one launch per kernel of `python bench.py --no-cpu-baseline --only decode,kv,project --steps 8 "
                      f"--warmup 3` (profiles/{tag}_<kernel>_ncu.txt): dram__bytes_read.sum + dram__bytes_write.sum", "kernels": {}}
 def num(v, unit):
     x = float(v.replace(",", ""))

@@ -75,6 +75,11 @@ else:
         if name == "times":
             buf = (C.c_ulonglong * (148 * 32))()
             lib.wrs_debug_pj_times(buf, 148 * 32)
+            clk = (C.c_longlong * (148 * 32))()
+            lib.wrs_debug_pj_clk(clk, 148 * 32)
+            for cta in (1, 73):
+                print(f"cta {cta} unit 2 select warp 0, per chunk [cycles to max, to staged, to loop end, iterations]: " +
+                      " ".join(str([clk[cta * 32 + 4 * c + k] for k in range(4)]) for c in range(6)))
             for cta in (0, 73, 147):
                 t = [buf[cta * 32 + k] for k in range(16)]
                 t0 = min(x for x in t if x)

@@ -1462,6 +1462,7 @@ extern "C" {
 int wrs_debug_pj_times(unsigned long long* out_host, int n) {
     return (int)cudaMemcpyFromSymbol(out_host, wrs::g_pj_times, sizeof(unsigned long long) * n);
 }
+int wrs_debug_pj_clk(long long* out_host, int n) { return (int)cudaMemcpyFromSymbol(out_host, wrs::g_pj_clk, sizeof(long long) * n); }
 #endif
 #ifdef WRS_TRACE
 int wrs_debug_trace_read(unsigned long long* out_host, int n) {

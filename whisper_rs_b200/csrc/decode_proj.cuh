@@ -221,6 +221,17 @@ __device__ __forceinline__ void proj_insert(ProjRow<KM>& st, float x, int nid) {
     st.kth = fmaxf(st.v[KM - 1], st.floor);
 }
 
+#ifdef WRS_EXP_PJ_TIMES
+// investigation aid (tools/proj_variants.py): per CTA, globaltimer stamps of [unit][mma start, mma issued, epi start, epi end]
+__device__ unsigned long long g_pj_times[148 * 32];
+__device__ long long g_pj_clk[148 * 32];       // clock64 stamps inside proj_topk32 of unit 2, warp 0: [chunk][after max, after staging, after loop, iterations]
+__device__ int g_pj_unit;
+__device__ __forceinline__ unsigned long long pj_now() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define WRS_PJ_T(u, k) do { if ((u) < 8) g_pj_times[blockIdx.x * 32 + (u) * 4 + (k)] = pj_now(); } while (0)
+#else
+#define WRS_PJ_T(u, k) do {} while (0)
+#endif
+
 // 32 columns of the row's accumulator (ids id0 .. id0 + 31; `valid` bit i: id0 + i survives the filters): masked ids
 // become -inf, the chunk maximum is returned (NaN operands are ignored by fmaxf: the callers look for them)
 __device__ __forceinline__ float proj_mask32(float (&x)[32], unsigned valid) {
@@ -265,8 +276,17 @@ __device__ __forceinline__ void proj_stats32(float& m, float& s, float (&x)[32],
 // of it by index -- one copy of the insertion code, run about K ln(176 / K) times per fresh tile, instead of one
 // predicated copy per element.
 template <int KM>
-__device__ __forceinline__ void proj_topk32(ProjRow<KM>& st, float (&x)[32], unsigned valid, int id0, float* xs) {
+__device__ __forceinline__ void proj_topk32(ProjRow<KM>& st, float (&x)[32], unsigned valid, int id0, float* xs, int pj_trace_unit = -1) {
+#ifdef WRS_EXP_PJ_TIMES
+    const bool tr = (threadIdx.x == 0) && pj_trace_unit >= 0;
+    long long* tc = g_pj_clk + blockIdx.x * 32 + 4 * ((id0 / 32) % 6);
+    const long long c0 = clock64();
+    int iters = 0;
+#endif
     const float cm = proj_mask32(x, valid);
+#ifdef WRS_EXP_PJ_TIMES
+    if (tr) tc[0] = clock64() - c0;
+#endif
 #ifndef WRS_EXP_PJ_NOINS
     if (cm > st.kth) {
         unsigned c4[4] = {0u, 0u, 0u, 0u};
@@ -276,6 +296,9 @@ __device__ __forceinline__ void proj_topk32(ProjRow<KM>& st, float (&x)[32], uns
             xs[32 * i] = x[i];
         }
         unsigned cand = (c4[0] | c4[1]) | (c4[2] | c4[3]);
+#ifdef WRS_EXP_PJ_TIMES
+        if (tr) tc[1] = clock64() - c0;
+#endif
         // one candidate per round, the next one's value already on its way from shared memory
         int i = __ffs((int)cand) - 1;
         float v = xs[32 * i];
@@ -285,20 +308,17 @@ __device__ __forceinline__ void proj_topk32(ProjRow<KM>& st, float (&x)[32], uns
             const bool more = cand != 0u;
             if (more) { i = __ffs((int)cand) - 1; v = xs[32 * i]; cand &= cand - 1u; }
             proj_insert<KM>(st, v_now, id0 + i_now);
+#ifdef WRS_EXP_PJ_TIMES
+            ++iters;
+#endif
             if (!more) break;
         }
+#ifdef WRS_EXP_PJ_TIMES
+        if (tr) { tc[2] = clock64() - c0; tc[3] = iters; }
+#endif
     }
 #endif
 }
-
-#ifdef WRS_EXP_PJ_TIMES
-// investigation aid (tools/proj_variants.py): per CTA, globaltimer stamps of [unit][mma start, mma issued, epi start, epi end]
-__device__ unsigned long long g_pj_times[148 * 32];
-__device__ __forceinline__ unsigned long long pj_now() { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
-#define WRS_PJ_T(u, k) do { if ((u) < 8) g_pj_times[blockIdx.x * 32 + (u) * 4 + (k)] = pj_now(); } while (0)
-#else
-#define WRS_PJ_T(u, k) do {} while (0)
-#endif
 
 struct ProjSmem {
     unsigned char stage[kPStages][kPStageBytes];
@@ -467,7 +487,7 @@ __global__ void __launch_bounds__(kPThreads, 1) proj_kernel(const ProjParams p) 
                     const unsigned supp = __funnelshift_r(w0, w1, id0 & 31);
                     const unsigned ok = (range_bits(rr.t_lo - id0, min(rr.t_hi, end) - id0) | range_bits(rr.s_lo - id0, min(rr.s_hi, end) - id0)) & ~supp;
                     if (sums) proj_stats32(sm_m, sm_s, x, ok);
-                    else proj_topk32<KM>(st, x, ok, id0, xmine);
+                    else proj_topk32<KM>(st, x, ok, id0, xmine, u == 2 ? 2 : -1);
                 }
 #ifdef WRS_EXP_PJ_TIMES
                 if (warp == 0 && lane == 0 && u == 0) g_pj_times[blockIdx.x * 32 + 17 + 2 * c] = pj_now();

@@ -117,4 +117,10 @@ class FusedDecodeStep:
 
     def finalize(self, tokens: torch.Tensor, sum_logprobs: torch.Tensor):
         n_audio, k, L = tokens.shape
+        if self.greedy:
+            # the decoder knows rows, not groups (its beam size is 1): group here, as GreedyTokenExtractor.finalize does
+            # (src/decode/extractor/greedy.rs:52-65: every sequence of the group, EOT appended)
+            eot = self.ids.eot
+            cands = [[seq.tolist() + [eot] for seq in group] for group in tokens.cpu()]
+            return cands, sum_logprobs.reshape(n_audio, k).double().cpu().numpy()
         return self.decoder.finalize(tokens.reshape(n_audio * k, L).contiguous(), sum_logprobs)

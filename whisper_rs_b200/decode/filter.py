@@ -53,8 +53,6 @@ def build_filters(opt: DecodeOptions, ids: TokenIds, prompt_ref: List[DecodeProm
                   device: int = 0) -> List[LogitFilter]:
     """src/decode/mod.rs:156-190 -- Blank, then Suppress, then Timestamp; all share one Decoder."""
     cfg = build_decoder_cfg(opt, ids, filters=True)
-    if cfg.timestamps == 0:
-        cfg.timestamps = 0
     dec = Decoder(cfg, suppress_list(opt, ids), max_rows, device)
     out: List[LogitFilter] = []
     if opt.suppress_blank:
