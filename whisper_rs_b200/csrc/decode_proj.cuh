@@ -221,6 +221,24 @@ __device__ __forceinline__ void proj_insert(ProjRow<KM>& st, float x, int nid) {
     st.kth = fmaxf(st.v[KM - 1], st.floor);
 }
 
+// The K-th largest of 12 values (K <= 12), by rank counting: 66 independent comparisons, ties ranked by position.
+__device__ __forceinline__ float kth_of_12(const float (&h)[12], int K) {
+    int rk[12];
+#pragma unroll
+    for (int i = 0; i < 12; ++i) rk[i] = 0;
+#pragma unroll
+    for (int i = 0; i < 12; ++i)
+#pragma unroll
+        for (int j = i + 1; j < 12; ++j) {
+            const bool jw = h[j] > h[i];                 // j ranks before i only if strictly greater
+            rk[i] += jw ? 1 : 0; rk[j] += jw ? 0 : 1;
+        }
+    float t = -CUDART_INF_F;
+#pragma unroll
+    for (int i = 0; i < 12; ++i) t = rk[i] == K - 1 ? h[i] : t;
+    return t;
+}
+
 #ifdef WRS_EXP_PJ_TIMES
 // investigation aid (tools/proj_variants.py): per CTA, globaltimer stamps of [unit][mma start, mma issued, epi start, epi end]
 __device__ unsigned long long g_pj_times[148 * 32];
@@ -325,7 +343,8 @@ struct ProjSmem {
     unsigned long long full[kPStages], empty[kPStages], tfull[2], tempty[2];
     unsigned tmem_base;
     unsigned pad[3];
-    float xstage[kPEpiWarps / 2][32 * 32];                            // epilogue warps: [element][lane] staging of one chunk
+    float xstage[kPEpiWarps / 2][32 * 32];
+    float tile_floor[kPEpiWarps / 2][32];                // sum warp -> select warp of the pair: a floor for the row's list in this tile                            // epilogue warps: [element][lane] staging of one chunk
     uint32_t bm[1];                                      // the suppress bitmap, bm_words + 2 words (EPI 1)
 };
 
@@ -447,10 +466,7 @@ __global__ void __launch_bounds__(kPThreads, 1) proj_kernel(const ProjParams p) 
                 const int part = tile < p.n_text_tiles ? 0 : 1;
                 if (row != prev_row || part != prev_part) tau_run = -CUDART_INF_F;
                 prev_row = row; prev_part = part;
-                // the largest float below tau_run: "x > floor" is "x >= tau_run"
-                float fl = tau_run;
-                if (fl > -CUDART_INF_F) fl = fl == 0.0f ? -1.4e-45f : __int_as_float(__float_as_int(fl) + (fl > 0.0f ? -1 : 1));
-                st.kth = fl; st.floor = fl;
+                st.kth = -CUDART_INF_F; st.floor = -CUDART_INF_F;       // (set below, once the tile's floor is known)
 #pragma unroll
                 for (int e = 0; e < KM; ++e) { st.v[e] = e < KM - p.K ? CUDART_INF_F : -CUDART_INF_F; st.id[e] = INT32_MAX; }
                 rr.t_lo = rr.t_hi = rr.s_lo = rr.s_hi = 0; rr.flags = 0u;
@@ -460,6 +476,49 @@ __global__ void __launch_bounds__(kPThreads, 1) proj_kernel(const ProjParams p) 
             tc_fence_after();
             if (warp == (int)(buf * 4) && lane == 0) WRS_PJ_T(u, 2);
             const unsigned t0 = tmem + buf * kPAccStride + lane_base;
+            if (EPI != 0) {
+                // A floor for the tile before any list is built: the sum warp runs over the accumulator once for the maxima
+                // of its twelve 16-column groups (masks applied); the K-th largest of them is reached by at least K ids of
+                // the tile, so nothing below it can be among the row's best K.  It hands the value to the select warp of its
+                // pair (named barrier, 64 threads), which would otherwise insert about K (1 + ln(176 / K)) times into a
+                // fresh list; with the floor it is about a third of that.
+                if (sums) {
+                    float h[12];
+#pragma unroll
+                    for (int g = 0; g < 12; ++g) h[g] = -CUDART_INF_F;
+                    if (p.K <= 12) {
+#pragma unroll
+                        for (int c = 0; c < (kPN + 31) / 32; ++c) {
+                            float x[32];
+                            if (32 * c + 32 <= kPN) tc_ld32(t0 + 32 * c, x);
+                            else tc_ld16(t0 + 32 * c, x);
+                            const int id0 = base + 32 * c;
+                            if (row < p.n_rows && id0 < end) {
+                                const unsigned w0 = sm.bm[id0 >> 5], w1 = sm.bm[(id0 >> 5) + 1];
+                                const unsigned supp = __funnelshift_r(w0, w1, id0 & 31);
+                                const unsigned ok = (range_bits(rr.t_lo - id0, min(rr.t_hi, end) - id0) | range_bits(rr.s_lo - id0, min(rr.s_hi, end) - id0)) & ~supp;
+                                if (ok != 0xffffffffu) {
+#pragma unroll
+                                    for (int i = 0; i < 32; ++i) x[i] = (ok & (1u << i)) ? x[i] : -CUDART_INF_F;
+                                }
+                                float a[8];
+#pragma unroll
+                                for (int i = 0; i < 8; ++i) a[i] = fmaxf(fmaxf(x[4 * i], x[4 * i + 1]), fmaxf(x[4 * i + 2], x[4 * i + 3]));
+                                h[2 * c] = fmaxf(fmaxf(a[0], a[1]), fmaxf(a[2], a[3]));
+                                h[2 * c + 1] = fmaxf(fmaxf(a[4], a[5]), fmaxf(a[6], a[7]));
+                            }
+                        }
+                    }
+                    sm.tile_floor[ew][lane] = p.K <= 12 ? kth_of_12(h, p.K) : -CUDART_INF_F;
+                    asm volatile("bar.arrive %0, 64;" ::"r"(1 + ew) : "memory");
+                } else {
+                    asm volatile("bar.sync %0, 64;" ::"r"(1 + ew) : "memory");
+                    float fl = fmaxf(tau_run, sm.tile_floor[ew][lane]);
+                    // the largest float below it: "x > floor" is "x >= the bound"
+                    if (fl > -CUDART_INF_F) fl = fl == 0.0f ? -1.4e-45f : __int_as_float(__float_as_int(fl) + (fl > 0.0f ? -1 : 1));
+                    st.kth = fl; st.floor = fl;
+                }
+            }
 #pragma unroll 1
             for (int c = 0; c < (kPN + 31) / 32; ++c) {
                 if (EPI == 0 && ((c & 1) != 0) != sums) continue;      // (plain projection: the two warps share the chunks)
