@@ -65,6 +65,14 @@ __host__ __device__ __forceinline__ int proj_tile_end(int tile, int n_text_tiles
     return tile < n_text_tiles ? min(tile * kPN + kPN, ts_split) : min(ts_split + (tile - n_text_tiles + 1) * kPN, n_vocab);
 }
 
+// rows of M tile `mt` as the operands hold them: the real rows rounded up to 8 (a core matrix), at most 128.  The MMA
+// always spans 128 rows; with fewer in memory its K chunks lie closer together (LBO = rows x 16 B) and the rows beyond them
+// alias the next chunk: they only reach accumulator rows that belong to no row of the batch and are never read.
+__host__ __device__ __forceinline__ int proj_rows8(int n_rows, int mt) {
+    const int left = n_rows - mt * kPM;
+    return left >= kPM ? kPM : ((left + 7) & ~7);
+}
+
 // ---- operand packing.  One thread per 16-byte group (8 consecutive elements of n_state of one row).
 __device__ __forceinline__ void split8(const float* v, uint4& hi, uint4& lo) {
     unsigned h[4], l[4];
@@ -90,9 +98,14 @@ __global__ void proj_pack_kernel(const float* __restrict__ src, int64_t src_stri
         const int s = (int)(rest % n_kstages); rest /= n_kstages;
         const int r = (int)(rest % rows_per_tile);
         const int tile = (int)(rest / rows_per_tile);
-        int row, end;
+        int row, end, rows_here = rows_per_tile;
         if (is_w) { row = proj_tile_base(tile, n_text_tiles, ts_split) + r; end = proj_tile_end(tile, n_text_tiles, ts_split, n_src_rows); }
-        else { row = tile * rows_per_tile + r; end = n_src_rows; }
+        else {
+            // an M tile with fewer than 128 rows is packed compactly (its rows rounded up to 8): proj_rows8()
+            row = tile * rows_per_tile + r; end = n_src_rows;
+            rows_here = proj_rows8(n_src_rows, tile);
+            if (r >= rows_here) continue;
+        }
         float v[8];
         if (row < end) {
             const float4 a = *reinterpret_cast<const float4*>(src + (int64_t)row * src_stride + s * kPK + kc * 8);
@@ -104,9 +117,10 @@ __global__ void proj_pack_kernel(const float* __restrict__ src, int64_t src_stri
         }
         uint4 hi, lo;
         split8(v, hi, lo);
-        const int64_t part_bytes = (int64_t)rows_per_tile * kPK * 2;
-        unsigned char* blk = dst + ((int64_t)tile * n_kstages + s) * 2 * part_bytes;
-        const int64_t off = ((int64_t)kc * rows_per_tile + r) * 16;
+        const int64_t slot_bytes = (int64_t)rows_per_tile * kPK * 2 * 2;       // a (tile, stage) slot; a short tile uses its front
+        const int64_t part_bytes = (int64_t)rows_here * kPK * 2;
+        unsigned char* blk = dst + ((int64_t)tile * n_kstages + s) * slot_bytes;
+        const int64_t off = ((int64_t)kc * rows_here + r) * 16;
         *reinterpret_cast<uint4*>(blk + off) = hi;
         *reinterpret_cast<uint4*>(blk + part_bytes + off) = lo;
     }
@@ -381,22 +395,12 @@ __global__ void __launch_bounds__(kPThreads, 1) proj_kernel(const ProjParams p) 
                 const int tile = (int)blockIdx.x + (u / p.n_mtiles) * (int)gridDim.x, mt = u % p.n_mtiles;
                 const unsigned char* a = p.xp + (int64_t)mt * p.n_kstages * (2 * kPABytes);
                 const unsigned char* b = p.wp + (int64_t)tile * p.n_kstages * (2 * kPBBytes);
-                const int rows_real = min(kPM, p.n_rows - mt * kPM);
+                const unsigned a_bytes = (unsigned)proj_rows8(p.n_rows, mt) * (kPK * 2 * 2);      // hi and lo of the tile's rows
                 for (int ks = 0; ks < p.n_kstages; ++ks, ++it) {
                     const unsigned slot = it % kPStages, round = it / kPStages;
                     mbar_wait_b<0>(&sm.empty[slot], (round & 1u) ^ 1u);      // (a fresh barrier passes the first round)
-                    if (rows_real <= kPM / 2) {
-                        // a mostly empty M tile: only its real rows travel (8 runs of rows x 16 B); what the other rows of
-                        // the stage hold is left over from an earlier unit and only reaches accumulator rows nobody reads
-                        const unsigned run = (unsigned)rows_real * 16u;
-                        mbar_expect_tx(&sm.full[slot], 8u * run + 2u * kPBBytes);
-#pragma unroll
-                        for (int q = 0; q < 8; ++q)
-                            bulk_g2s(sm.stage[slot] + q * (kPM * 16), a + (int64_t)ks * (2 * kPABytes) + q * (kPM * 16), run, &sm.full[slot]);
-                    } else {
-                        mbar_expect_tx(&sm.full[slot], (unsigned)kPStageBytes);
-                        bulk_g2s(sm.stage[slot], a + (int64_t)ks * (2 * kPABytes), 2 * kPABytes, &sm.full[slot]);
-                    }
+                    mbar_expect_tx(&sm.full[slot], a_bytes + 2u * kPBBytes);
+                    bulk_g2s(sm.stage[slot], a + (int64_t)ks * (2 * kPABytes), a_bytes, &sm.full[slot]);
                     bulk_g2s(sm.stage[slot] + 2 * kPABytes, b + (int64_t)ks * (2 * kPBBytes), 2 * kPBBytes, &sm.full[slot]);
                 }
             }
@@ -411,16 +415,17 @@ __global__ void __launch_bounds__(kPThreads, 1) proj_kernel(const ProjParams p) 
                 tc_fence_after();
                 WRS_PJ_T(u, 0);
                 const unsigned d = tmem + buf * kPAccStride;
+                const unsigned a_rows = (unsigned)proj_rows8(p.n_rows, u % p.n_mtiles);
                 for (int ks = 0; ks < p.n_kstages; ++ks, ++it) {
                     const unsigned slot = it % kPStages, round = it / kPStages;
                     mbar_wait_b<0>(&sm.full[slot], round & 1u);
                     tc_fence_after();
-                    const unsigned a_hi = smem_addr(sm.stage[slot]), a_lo = a_hi + kPABytes;
+                    const unsigned a_hi = smem_addr(sm.stage[slot]), a_lo = a_hi + a_rows * (kPK * 2);
                     const unsigned b_hi = a_hi + 2 * kPABytes, b_lo = b_hi + kPBBytes;
 #pragma unroll
                     for (int j = 0; j < kPK / 16; ++j) {
-                        const unsigned ao = j * 2 * (kPM * 16), bo = j * 2 * (kPN * 16);
-                        const unsigned long long dah = tc_desc(a_hi + ao, kPM * 16, 128), dal = tc_desc(a_lo + ao, kPM * 16, 128);
+                        const unsigned ao = j * 2 * (a_rows * 16), bo = j * 2 * (kPN * 16);
+                        const unsigned long long dah = tc_desc(a_hi + ao, a_rows * 16, 128), dal = tc_desc(a_lo + ao, a_rows * 16, 128);
                         const unsigned long long dbh = tc_desc(b_hi + bo, kPN * 16, 128), dbl = tc_desc(b_lo + bo, kPN * 16, 128);
 #if defined(WRS_EXP_PJ_NOMMA)
                         (void)dal; (void)dbl; (void)dah; (void)dbh; (void)d;
