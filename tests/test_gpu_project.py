@@ -107,6 +107,40 @@ def test_fused_step_equals_beam_step_on_projected_logits(step_kind, beam, n_audi
         assert (got["cand_logprob"][:, 0] == got["cand_logprob"][:, 1]).any() or step_kind == "first"
 
 
+@pytest.mark.parametrize("ids,beam,n_audio,n_state,timestamps", [
+    (C.MULTILINGUAL, 5, 60, 384, True),        # 300 rows: three M tiles, the last one 44 rows (packed compactly)
+    (C.GPT2_EN, 5, 26, 512, True),             # 130 rows: a second M tile of 2 rows; V = 51864
+    (C.MULTILINGUAL, 4, 8, 768, False),        # no timestamp rules: one partition, 295 tiles
+    (C.MULTILINGUAL, 15, 2, 512, True),        # the largest beam: K = 16 entries per list
+    (C.MULTILINGUAL, 1, 128, 512, True)])      # beam 1 (K = 2), exactly one full M tile
+def test_fused_step_geometries(ids, beam, n_audio, n_state, timestamps):
+    case = synth.decode_case(ids, n_audio, beam, "mixed", seed=23)
+    R = n_audio * beam
+    x, w = make_model(ids, n_state, R, seed=beam, dup=500)
+    opt = wd.DecodeOptions(token_extract_mode=wd.TokenExtractMode.BeamSearch(beam, 1.0), timestamps=timestamps)
+    prompt = wd.DecodePrompt(None, ids)
+    prompt.sample_begin = case["sample_begin"]
+    step = wd.FusedDecodeStep(opt, ids, [prompt], max_rows=R)
+    step.reset()
+    proj = Projection(step.decoder, torch.from_numpy(w).cuda())
+    xd = torch.from_numpy(x).cuda()
+    tokens, sums = torch.from_numpy(case["tokens"]).cuda(), torch.from_numpy(case["sum_logprobs"]).cuda()
+    logits = proj.logits(xd)
+    want = to_np(step.decoder.beam_step(logits, tokens, case["sample_begin"], sums, debug=True))
+    step.reset()
+    got = to_np(proj.beam_step(xd, tokens, case["sample_begin"], sums, debug=True))
+    torch.cuda.synchronize()
+    step.decoder.ctx.check()
+    for key in ("row_flags", "cand_token", "next_tokens", "source_idx", "fin_count"):
+        assert np.array_equal(got[key], want[key]), key
+    assert np.allclose(got["cand_logprob"], want["cand_logprob"], rtol=RTOL, atol=1e-5)
+    assert np.allclose(got["sum_logprobs"], want["sum_logprobs"], rtol=RTOL, atol=1e-5)
+    # and the projection itself on this geometry, against the f64 product
+    want64 = x.astype(np.float64) @ w.astype(np.float64).T
+    scale = np.abs(x).astype(np.float64) @ np.abs(w).astype(np.float64).T
+    assert (np.abs(logits.cpu().numpy() - want64) / scale).max() <= LOGIT_TOL
+
+
 @pytest.mark.parametrize("step_kind", ["first", "mixed"])
 def test_fused_step_against_the_oracle_on_f32_logits(step_kind):
     ids = C.MULTILINGUAL
