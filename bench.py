@@ -821,18 +821,18 @@ def bench_project(env):
     mp = os.path.join(ROOT, "MEASURED_PEAKS.json")
     tc_peak = float(json.load(open(mp)).get("bf16_tflops", 0.0)) if os.path.exists(mp) else 0.0
     emb_bytes = VOCAB * D * 4 + R * D * 4                    # the f32 embedding and x, read once
-    flops = 3 * 2.0 * R * D * VOCAB                          # three bf16 products per f32 product
-    roof = env.roofline(emb_bytes, t_fused, "wrs::proj_kernel<1> (tcgen05 projection + row scan; reads the packed bf16 hi/lo "
+    flops = 3 * 2.0 * R * D * VOCAB                          # three f16 products per f32 product
+    roof = env.roofline(emb_bytes, t_fused, "wrs::proj_kernel<1> (tcgen05 projection + row scan; reads the packed f16 hi/lo "
                         "embedding, 4 B per weight) + wrs::proj_pack_kernel (x) + wrs::decode_tail_kernel<0>; achieved = bytes of the f32 "
                         "embedding and x / time of the whole three-launch step", "proj_kernel")
     roof["tensor"] = {"achieved": flops / t_fused / 1e12, "peak": tc_peak or None, "unit": "TFLOP/s",
                       "frac": flops / t_fused / 1e12 / tc_peak if tc_peak else None,
-                      "note": "3 bf16 products per f32 product on the 160 real rows; the second M tile of 128 is 3/4 padding"}
+                      "note": "3 f16 products per f32 product on the 160 real rows; the second M tile of 128 is 3/4 padding"}
     return {"project_beam_step": {
         "metric": "projection + beam decode row-steps/s", "value": env.world * R / t_fused, "unit": "row-steps/s",
         "ms_per_step": 1e3 * t_fused, "steps": n_steps, "launch": f"CUDA graph of {NB} steps (+1 reset) replayed {n_replays}x",
         "config": {"workload": f"x [160, {D}] f32 @ token_emb [{VOCAB}, {D}] f32 (src/model.rs:521, Whisper base) + config 3's decode step; "
-                               "logits never written", "arithmetic": "bf16 hi/lo x 3 products, f32 accumulate in TMEM (about 8e-5 abs on "
+                               "logits never written", "arithmetic": "f16 hi/lo x 3 products, f32 accumulate in TMEM (about 4e-5 abs on "
                                "logits of sigma 3; an f32 matmul is near 9e-6)",
                    "cache": "two packed embedding copies alternate (2 x 107 MB > L2); x rotates over 8 buffers"},
         "roofline": roof,

@@ -201,9 +201,11 @@ int wrs_greedy_step(wrs_decoder* dec, const float* logits, int64_t row_stride, i
 /* ---- the logits projection with the decode step as its epilogue.
  * Reference: `x.matmul(&self.token_emb.ws.transpose(0, 1))` (src/model.rs:521), whose [n_rows, n_vocab] f32 result
  * is what src/decode/mod.rs:257-270 then filters and extracts from.  Here the product runs on the tensor cores
- * (tcgen05, bf16 hi/lo splits of both f32 operands, three products, f32 accumulation) and the decode step's row scan
- * is the epilogue of each tile: the logits never reach HBM.  Accuracy: a logit differs from the f32 product sum by
- * about 2^-16 of sum |x_i w_i| (NOT f32-faithful; the tolerance is stated in tests/test_gpu_project.py).
+ * (tcgen05, f16 hi/lo splits of both f32 operands -- 22 bits each --, three products, tensor-core f32 accumulation) and
+ * the decode step's row scan is the epilogue of each tile: the logits never reach HBM.  Accuracy: measured up to 1.2e-6
+ * of sum |x_i w_i| per logit (4e-5 absolute on logits of sigma 3 at n_state 512): the tensor core's accumulation is not
+ * IEEE f32, so this is four to seven times the error of an f32 matmul -- NOT f32-faithful (tests/test_gpu_project.py
+ * states the bars).  |x| must stay below 65504 (f16 range; LayerNorm output does).
  *
  * wrs_projection_create packs `token_emb` (DEVICE [n_vocab][emb_stride] f32, the rows of TextDecoder::token_emb,
  * src/model.rs:463) for `dec`'s vocabulary geometry; n_state a multiple of 32.  The packed copy (4 bytes per weight)

@@ -5,9 +5,12 @@ Two separate questions, two kinds of test:
   * the EPILOGUE (masks, softmax statistics, exact top-K, tail): wrs_project_beam_step must equal wrs_beam_step run on
     the logits the same tensor-core arithmetic materialises (wrs_project_logits) -- ids, sources, flags bit-exact,
     log-probs 1e-5 relative -- and wrs_beam_step is what tests/test_gpu_decode.py pins to the oracle;
-  * the ARITHMETIC: bf16 hi/lo splits, three products, f32 accumulation.  Not f32-faithful: the bar written here is
-    |logit - f64 product| <= LOGIT_TOL * sum_i |x_i w_i| (measured 1.8e-6 of that sum, about 8e-5 absolute on logits of sigma 3 -- nine times the error of an f32 matmul), and against the oracle
-    (numpy f32 matmul -> oracle decode step) ids must agree wherever the oracle's own margins exceed LOGPROB_TOL."""
+  * the ARITHMETIC: f16 hi/lo splits (22 bits per operand), three products, accumulation in the tensor core's f32
+    accumulators -- whose additions are not IEEE roundings: measured |logit - f64 product| up to 1.2e-6 of
+    sum_i |x_i w_i| (4e-5 absolute on logits of sigma 3 at n_state 512, 8e-5 at 1280), four to seven times the error of
+    numpy's f32 matmul and growing like sqrt(n_state); with bf16 splits it was 1.8e-6.  NOT f32-faithful.  The bar written
+    here is LOGIT_TOL of that sum, and against the oracle (numpy f32 matmul -> oracle decode step) ids must agree wherever
+    the oracle's own candidate gaps exceed 2 LOGPROB_TOL, log-probs within LOGPROB_TOL."""
 import numpy as np
 import pytest
 import torch
@@ -19,8 +22,8 @@ from whisper_rs_b200 import decode as wd
 from whisper_rs_b200.decode.core import Projection
 
 pytestmark = pytest.mark.gpu
-LOGIT_TOL = 4e-6         # of sum |x_i w_i| per logit (measured 1.8e-6; numpy f32 matmul sits near 2e-7)
-LOGPROB_TOL = 2e-3       # absolute, log-probs of the fused step against the oracle on f32-matmul logits
+LOGIT_TOL = 2.5e-6       # of sum |x_i w_i| per logit (measured up to 1.2e-6; numpy f32 matmul sits near 2e-7)
+LOGPROB_TOL = 5e-4       # absolute, log-probs of the fused step against the oracle on f32-matmul logits (measured 3e-5)
 RTOL = 1e-5
 
 

@@ -53,7 +53,8 @@ struct wrs_decoder {
 struct wrs_projection {
     wrs_decoder* dec = nullptr;
     int n_state = 0, n_tiles = 0, n_text_tiles = 0, n_kstages = 0, max_mtiles = 0;
-    unsigned char* d_wp = nullptr;    // packed weights
+    unsigned char* d_wp = nullptr;    // packed weights (f16 hi / lo of w x w_scale)
+    float w_scale = 1.0f;             // a power of two: max |w| x w_scale in [512, 1024)
     unsigned char* d_xp = nullptr;    // packed x of the step in flight, [max_mtiles]
     float* d_parts = nullptr;         // [max_rows][2 + 2 (beam + 1)][tiles padded to 4] record planes
     bool attr_set = false;
@@ -1370,9 +1371,9 @@ int launch_proj(wrs_projection* pj, ProjParams q, const float* x, int64_t x_stri
     q.wp = pj->d_wp; q.xp = pj->d_xp;
     q.n_tiles = pj->n_tiles; q.n_text_tiles = pj->n_text_tiles; q.n_kstages = pj->n_kstages;
     q.n_mtiles = (q.n_rows + kPM - 1) / kPM;
-    q.n_vocab = dec->cfg.n_vocab; q.ts_split = dec->ts_split;
+    q.n_vocab = dec->cfg.n_vocab; q.ts_split = dec->ts_split; q.inv_scale = 1.0f / pj->w_scale;
     const int64_t groups = (int64_t)q.n_mtiles * q.n_kstages * 4 * kPM;
-    proj_pack_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, stream>>>(x, x_stride, q.n_rows, pj->n_state, q.n_mtiles, kPM, 0, 0, 0, pj->d_xp);
+    proj_pack_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, stream>>>(x, x_stride, q.n_rows, pj->n_state, q.n_mtiles, kPM, 0, 0, 0, 1.0f, pj->d_xp);
     WRS_CUDA(ctx, cudaGetLastError());
     // (programmatic dependent launch behind the packing kernel -- set-up under the packing -- was measured: 63.0 against
     // 63.5 us per step, within the noise; not kept)
@@ -1660,9 +1661,26 @@ int wrs_projection_create(wrs_decoder* dec, const float* token_emb, int64_t emb_
         wrs_projection_destroy(pj);
         return cuda_fail(ctx, e, "projection buffers");
     }
+    // the power of two that puts the largest |w| in [512, 1024): one reduction over the embedding, read back here
+    // (creation is a load-time call; it synchronises `stream`)
+    {
+        unsigned* d_bits = reinterpret_cast<unsigned*>(pj->d_parts);      // (scratch: the record buffer is not in use yet)
+        unsigned bits = 0u;
+        if ((e = cudaMemsetAsync(d_bits, 0, sizeof(unsigned), stream)) == cudaSuccess) {
+            proj_absmax_kernel<<<ctx->sm_count * 4, 256, 0, stream>>>(token_emb, emb_stride, V, n_state, d_bits);
+            if ((e = cudaGetLastError()) == cudaSuccess &&
+                (e = cudaMemcpyAsync(&bits, d_bits, sizeof(unsigned), cudaMemcpyDeviceToHost, stream)) == cudaSuccess)
+                e = cudaStreamSynchronize(stream);
+        }
+        if (e != cudaSuccess) { wrs_projection_destroy(pj); return cuda_fail(ctx, e, "projection scale"); }
+        float wmax;
+        memcpy(&wmax, &bits, sizeof(float));
+        int ex = 0;
+        if (wmax > 0.0f) { std::frexp(wmax, &ex); pj->w_scale = std::ldexp(1.0f, 10 - ex); }   // wmax = f x 2^ex, f in [0.5, 1)
+    }
     const int64_t groups = (int64_t)pj->n_tiles * pj->n_kstages * 4 * kPN;
     proj_pack_kernel<<<(unsigned)std::min<int64_t>((groups + 255) / 256, 65535), 256, 0, stream>>>(
-        token_emb, emb_stride, V, n_state, pj->n_tiles, kPN, pj->n_text_tiles, dec->ts_split, 1, pj->d_wp);
+        token_emb, emb_stride, V, n_state, pj->n_tiles, kPN, pj->n_text_tiles, dec->ts_split, 1, pj->w_scale, pj->d_wp);
     e = cudaGetLastError();
     if (e != cudaSuccess) { wrs_projection_destroy(pj); return cuda_fail(ctx, e, "projection packing"); }
     *out = pj;

@@ -4,10 +4,13 @@
 // (`x.matmul(&self.token_emb.ws.transpose(0, 1))`, [R, n_state] x [n_state, V] in f32) followed by
 // src/decode/mod.rs:257-270 (filters + extractor): the [R, V] logits are never written to HBM.
 //
-// Arithmetic: tcgen05.mma kind::f16 on bf16 operands with f32 accumulators in tensor memory.  f32 operands are split
-// x = hi + lo (both bf16, lo = bf16(x - hi)), and hi*hi + lo*hi + hi*lo is accumulated ("bf16x3"): 16 mantissa bits per
-// operand, so a logit differs from the f32 product sum by about 2^-16 of sum |x_i w_i| -- NOT f32-faithful; the
-// tolerance this buys is written in tests/test_gpu_project.py and DESIGN.md.
+// Arithmetic: tcgen05.mma kind::f16 on f16 operands with f32 accumulators in tensor memory.  f32 operands are split
+// v = hi + lo (both f16, lo = f16(v - hi)), and hi*hi + lo*hi + hi*lo is accumulated: 22 mantissa bits per operand, so a
+// logit differs from the exact product sum by about 2^-22 of sum |x_i w_i| -- a smaller error than an f32 matmul's own
+// rounding.  f16 has 5 exponent bits: the embedding is multiplied by a power of two at packing time that puts its largest
+// |w| in [512, 1024) (the lo parts of all but vanishing weights stay normal numbers) and every accumulator value is
+// multiplied back; x is taken as it comes (LayerNorm output: |x| must stay below 65504, beyond that the row is reported
+// like any non-finite row).  The bars are written in tests/test_gpu_project.py and DESIGN.md.
 //
 // Geometry: a vocab tile is 176 consecutive ids of ONE partition (text ids below ts_split, timestamp ids from it: a
 // tile never straddles, so a tile's statistics belong to one partition); V = 51865 with timestamps gives 287 + 9 = 296
@@ -24,7 +27,7 @@
 //                      (value desc, id asc), one record per (row, tile) to global memory for the tail launch.
 #pragma once
 
-#include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 #include "async_copy.cuh"
 #include "decode_scan.cuh"
@@ -48,6 +51,8 @@ struct ProjParams {
     const unsigned char* wp;     // packed weights [tile][stage][hi | lo][4][176][8] bf16
     const unsigned char* xp;     // packed x       [M tile][stage][hi | lo][4][128][8] bf16
     int n_tiles, n_text_tiles, n_mtiles, n_kstages, n_rows, n_vocab, ts_split;
+    float inv_scale;             // 1 / (the power of two the packed weights were multiplied by): the epilogue works on the scaled
+                                 // accumulators and multiplies what it writes (a power of two: order and ties are untouched)
     // EPI 0: the plain projection
     float* logits; int64_t row_stride;
     // EPI 1: fold
@@ -74,21 +79,35 @@ __host__ __device__ __forceinline__ int proj_rows8(int n_rows, int mt) {
 }
 
 // ---- operand packing.  One thread per 16-byte group (8 consecutive elements of n_state of one row).
-__device__ __forceinline__ void split8(const float* v, uint4& hi, uint4& lo) {
+__device__ __forceinline__ void split8(const float* v, float scale, uint4& hi, uint4& lo) {
     unsigned h[4], l[4];
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
-        const __nv_bfloat16 h0 = __float2bfloat16_rn(v[2 * i]), h1 = __float2bfloat16_rn(v[2 * i + 1]);
-        const __nv_bfloat16 l0 = __float2bfloat16_rn(v[2 * i] - __bfloat162float(h0)), l1 = __float2bfloat16_rn(v[2 * i + 1] - __bfloat162float(h1));
-        h[i] = (unsigned)__bfloat16_as_ushort(h0) | ((unsigned)__bfloat16_as_ushort(h1) << 16);
-        l[i] = (unsigned)__bfloat16_as_ushort(l0) | ((unsigned)__bfloat16_as_ushort(l1) << 16);
+        const float a0 = v[2 * i] * scale, a1 = v[2 * i + 1] * scale;          // (scale is a power of two: exact)
+        const __half h0 = __float2half_rn(a0), h1 = __float2half_rn(a1);
+        const __half l0 = __float2half_rn(a0 - __half2float(h0)), l1 = __float2half_rn(a1 - __half2float(h1));
+        h[i] = (unsigned)__half_as_ushort(h0) | ((unsigned)__half_as_ushort(h1) << 16);
+        l[i] = (unsigned)__half_as_ushort(l0) | ((unsigned)__half_as_ushort(l1) << 16);
     }
     hi = make_uint4(h[0], h[1], h[2], h[3]); lo = make_uint4(l[0], l[1], l[2], l[3]);
 }
 
+// largest |w| of the embedding (for the power-of-two scale of its packed copy)
+__global__ void proj_absmax_kernel(const float* __restrict__ src, int64_t src_stride, int n_rows, int n_cols, unsigned* __restrict__ out_bits) {
+    float m = 0.0f;
+    const int64_t total = (int64_t)n_rows * n_cols;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+        const float v = fabsf(src[(i / n_cols) * src_stride + (i % n_cols)]);
+        m = (v == v && v < CUDART_INF_F) ? fmaxf(m, v) : m;
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) atomicMax(out_bits, __float_as_uint(m));      // (non-negative floats order like their bits)
+}
+
 // rows_per_tile = 176 (weights; src row = the tile's id) or 128 (x; src row = tile * 128 + r)
 __global__ void proj_pack_kernel(const float* __restrict__ src, int64_t src_stride, int n_src_rows, int n_state, int n_tiles,
-                                 int rows_per_tile, int n_text_tiles, int ts_split, int is_w, unsigned char* __restrict__ dst) {
+                                 int rows_per_tile, int n_text_tiles, int ts_split, int is_w, float scale, unsigned char* __restrict__ dst) {
     const int n_kstages = n_state / kPK;
     const int64_t groups = (int64_t)n_tiles * n_kstages * 4 * rows_per_tile;
     for (int64_t g = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; g < groups; g += (int64_t)gridDim.x * blockDim.x) {
@@ -116,7 +135,7 @@ __global__ void proj_pack_kernel(const float* __restrict__ src, int64_t src_stri
             for (int i = 0; i < 8; ++i) v[i] = 0.0f;
         }
         uint4 hi, lo;
-        split8(v, hi, lo);
+        split8(v, scale, hi, lo);
         const int64_t slot_bytes = (int64_t)rows_per_tile * kPK * 2 * 2;       // a (tile, stage) slot; a short tile uses its front
         const int64_t part_bytes = (int64_t)rows_here * kPK * 2;
         unsigned char* blk = dst + ((int64_t)tile * n_kstages + s) * slot_bytes;
@@ -158,9 +177,9 @@ __device__ __forceinline__ unsigned long long tc_desc(unsigned saddr, unsigned l
     return (unsigned long long)((saddr & 0x3ffffu) >> 4) | ((unsigned long long)(lbo >> 4) << 16) |
            ((unsigned long long)(sbo >> 4) << 32) | (1ull << 46);
 }
-// instruction descriptor: D f32 (bits 4-5 = 1), A and B bf16 (bits 7-9, 10-12 = 1), both K-major (bits 15, 16 = 0),
+// instruction descriptor: D f32 (bits 4-5 = 1), A and B f16 (bits 7-9, 10-12 = 0), both K-major (bits 15, 16 = 0),
 // N / 8 at bit 17, M / 16 at bit 24
-constexpr unsigned kPIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((unsigned)(kPN >> 3) << 17) | ((unsigned)(kPM >> 4) << 24);
+constexpr unsigned kPIdesc = (1u << 4) | ((unsigned)(kPN >> 3) << 17) | ((unsigned)(kPM >> 4) << 24);
 __device__ __forceinline__ void tc_mma(unsigned d_tmem, unsigned long long a, unsigned long long b, unsigned accumulate) {
     asm volatile(
         "{\n"
@@ -278,7 +297,7 @@ __device__ __forceinline__ float proj_mask32(float (&x)[32], unsigned valid) {
 }
 
 // the statistics half of the epilogue: online {max, sum exp(x - max)} of the survivors
-__device__ __forceinline__ void proj_stats32(float& m, float& s, float (&x)[32], unsigned valid) {
+__device__ __forceinline__ void proj_stats32(float& m, float& s, float (&x)[32], unsigned valid, float c) {   // c = log2(e) / scale
     const float cm = proj_mask32(x, valid);
     if (cm == -CUDART_INF_F || cm != cm) {
         // nothing finite: the sum is unchanged unless a NaN is among the survivors (then it is NaN, as in ATen)
@@ -288,16 +307,16 @@ __device__ __forceinline__ void proj_stats32(float& m, float& s, float (&x)[32],
         if (bad) s = CUDART_NAN_F;
         return;
     }
-    if (cm > m) { s *= ex2((m - cm) * kLog2e); m = cm; }
+    if (cm > m) { s *= ex2((m - cm) * c); m = cm; }
 #ifndef WRS_EXP_PJ_NOSUM
     float acc0 = 0.0f, acc1 = 0.0f, acc2 = 0.0f, acc3 = 0.0f;
-    const float mb = -m * kLog2e;
+    const float mb = -m * c;
 #pragma unroll
     for (int i = 0; i < 32; i += 4) {
-        acc0 += ex2(fmaf(x[i], kLog2e, mb));
-        acc1 += ex2(fmaf(x[i + 1], kLog2e, mb));
-        acc2 += ex2(fmaf(x[i + 2], kLog2e, mb));
-        acc3 += ex2(fmaf(x[i + 3], kLog2e, mb));
+        acc0 += ex2(fmaf(x[i], c, mb));
+        acc1 += ex2(fmaf(x[i + 1], c, mb));
+        acc2 += ex2(fmaf(x[i + 2], c, mb));
+        acc3 += ex2(fmaf(x[i + 3], c, mb));
     }
     s += (acc0 + acc1) + (acc2 + acc3);
 #endif
@@ -543,14 +562,14 @@ __global__ void __launch_bounds__(kPThreads, 1) proj_kernel(const ProjParams p) 
                         float* o = p.logits + (int64_t)row * p.row_stride + id0;
 #pragma unroll
                         for (int i = 0; i < 32; ++i)
-                            if (id0 + i < end) o[i] = x[i];
+                            if (id0 + i < end) o[i] = x[i] * p.inv_scale;
                     }
                 } else if (row < p.n_rows && id0 < end) {
                     // suppress bits of ids id0 .. id0 + 31 (two words of the bitmap), the row's ranges, the tile's end
                     const unsigned w0 = sm.bm[id0 >> 5], w1 = sm.bm[(id0 >> 5) + 1];
                     const unsigned supp = __funnelshift_r(w0, w1, id0 & 31);
                     const unsigned ok = (range_bits(rr.t_lo - id0, min(rr.t_hi, end) - id0) | range_bits(rr.s_lo - id0, min(rr.s_hi, end) - id0)) & ~supp;
-                    if (sums) proj_stats32(sm_m, sm_s, x, ok);
+                    if (sums) proj_stats32(sm_m, sm_s, x, ok, kLog2e * p.inv_scale);
                     else proj_topk32<KM>(st, x, ok, id0, xmine, u == 2 ? 2 : -1);
                 }
 #ifdef WRS_EXP_PJ_TIMES
@@ -564,14 +583,14 @@ __global__ void __launch_bounds__(kPThreads, 1) proj_kernel(const ProjParams p) 
             if (EPI != 0 && row < p.n_rows) {
                 float* rec = p.parts + (int64_t)row * (2 + 2 * p.K) * p.tiles_padded + tile;
                 if (sums) {
-                    rec[0] = sm_m; rec[p.tiles_padded] = sm_s;
+                    rec[0] = sm_m * p.inv_scale; rec[p.tiles_padded] = sm_s;
                 } else {
                     tau_run = fmaxf(tau_run, st.v[KM - 1]);
                     float* rv = rec + (int64_t)(2 - (KM - p.K)) * p.tiles_padded;      // plane of list entry e: 2 + e - (KM - K)
                     int* ri = reinterpret_cast<int*>(rv + (int64_t)p.K * p.tiles_padded);
 #pragma unroll
                     for (int e = 0; e < KM; ++e)
-                        if (e >= KM - p.K) { rv[(int64_t)e * p.tiles_padded] = st.v[e]; ri[(int64_t)e * p.tiles_padded] = st.id[e]; }
+                        if (e >= KM - p.K) { rv[(int64_t)e * p.tiles_padded] = st.v[e] * p.inv_scale; ri[(int64_t)e * p.tiles_padded] = st.id[e]; }
                 }
             }
         }
