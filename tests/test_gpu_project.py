@@ -115,7 +115,8 @@ def test_fused_step_equals_beam_step_on_projected_logits(step_kind, beam, n_audi
     (C.GPT2_EN, 5, 26, 512, True),             # 130 rows: a second M tile of 2 rows; V = 51864
     (C.MULTILINGUAL, 4, 8, 768, False),        # no timestamp rules: one partition, 295 tiles
     (C.MULTILINGUAL, 15, 2, 512, True),        # the largest beam: K = 16 entries per list
-    (C.MULTILINGUAL, 1, 128, 512, True)])      # beam 1 (K = 2), exactly one full M tile
+    (C.MULTILINGUAL, 1, 128, 512, True),       # beam 1 (K = 2), exactly one full M tile
+    (C.MULTILINGUAL, 5, 400, 384, True)])      # 2 000 rows: sixteen M tiles per vocab tile (32 units per CTA)
 def test_fused_step_geometries(ids, beam, n_audio, n_state, timestamps):
     case = synth.decode_case(ids, n_audio, beam, "mixed", seed=23)
     R = n_audio * beam
