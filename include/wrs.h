@@ -209,7 +209,9 @@ int wrs_greedy_step(wrs_decoder* dec, const float* logits, int64_t row_stride, i
  *
  * wrs_projection_create packs `token_emb` (DEVICE [n_vocab][emb_stride] f32, the rows of TextDecoder::token_emb,
  * src/model.rs:463) for `dec`'s vocabulary geometry; n_state a multiple of 32.  The packed copy (4 bytes per weight)
- * belongs to the projection; token_emb may be freed once `stream` has run the packing. */
+ * belongs to the projection; token_emb may be freed once the call returns (it synchronises `stream`: one reduction over
+ * the embedding is read back for the scale).  A projection owns per-step scratch (packed x, per-tile records): calls on one
+ * projection must be ordered on one stream, like calls on its decoder. */
 typedef struct wrs_projection wrs_projection;
 int wrs_projection_create(wrs_decoder* dec, const float* token_emb, int64_t emb_stride, int32_t n_state, wrs_stream_t stream,
                           wrs_projection** out);
