@@ -807,6 +807,9 @@ def bench_project(env):
             torch.matmul(xs[b], embs[b & 1].t(), out=logits[b])
 
     t_fused = graph_of(fused)
+    env.check(L.wrs_ctx_set_option(ctx.handle, b"proj_cluster", 0))
+    t_fused_single = graph_of(fused)          # A/B: every CTA on its own (two M tiles per vocab tile in one CTA)
+    env.check(L.wrs_ctx_set_option(ctx.handle, b"proj_cluster", 1))
     t_unfused = graph_of(unfused)
     t_proj = graph_of(proj_only)
     prev = torch.backends.cuda.matmul.allow_tf32
@@ -837,6 +840,7 @@ def bench_project(env):
                    "cache": "two packed embedding copies alternate (2 x 107 MB > L2); x rotates over 8 buffers"},
         "roofline": roof,
         "alternatives_ms_per_step": {
+            "wrs_project_beam_step without two-CTA clusters (option proj_cluster = 0)": 1e3 * t_fused_single,
             "wrs_project_logits + wrs_beam_step": 1e3 * t_unfused, "wrs_project_logits alone": 1e3 * t_proj,
             "torch.matmul f32 (cuBLAS, TF32 off: what tch runs) + wrs_beam_step": 1e3 * t_lib,
             "torch.matmul f32 alone": 1e3 * t_lib_gemm, "torch.matmul TF32 alone": 1e3 * t_lib_tf32},

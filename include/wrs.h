@@ -108,7 +108,8 @@ int wrs_pad_or_trim(wrs_ctx* ctx, const float* in, int64_t rows, int64_t in_len,
                     int64_t out_len, wrs_stream_t stream);
 
 /* Tuning / diagnostics.  key "logmel_fused": 1 = single fused launch (default when a segment's slices
- * fit co-resident), 0 = two launches (raw log-mel, then floor+scale). */
+ * fit co-resident), 0 = two launches (raw log-mel, then floor+scale).  key "proj_cluster": 0 = never launch the projection
+ * kernel as clusters of two CTAs that share the weights (the default, 1, does for 129 .. 256 rows; A/B timing). */
 int wrs_ctx_set_option(wrs_ctx* ctx, const char* key, int64_t value);
 int64_t wrs_ctx_get_stat(wrs_ctx* ctx, const char* key);
 

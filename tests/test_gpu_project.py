@@ -145,6 +145,37 @@ def test_fused_step_geometries(ids, beam, n_audio, n_state, timestamps):
     assert (np.abs(logits.cpu().numpy() - want64) / scale).max() <= LOGIT_TOL
 
 
+@pytest.mark.parametrize("R_audio,beam", [(32, 5), (26, 5), (51, 5)])     # 160, 130 and 255 rows: two M tiles
+def test_cluster_launch_is_bit_identical_to_the_single_cta_launch(R_audio, beam):
+    """129 .. 256 rows run as clusters of two CTAs that share the weights by multicast (option proj_cluster, default 1): the
+    same arithmetic per accumulator, so the same bits -- logits, records, everything the step returns."""
+    from whisper_rs_b200 import _lib
+    ids = C.MULTILINGUAL
+    case = synth.decode_case(ids, R_audio, beam, "mixed", seed=77)
+    R = R_audio * beam
+    x, w = make_model(ids, 512, R, seed=R, dup=300)
+    step = build(ids, case, beam)
+    proj = Projection(step.decoder, torch.from_numpy(w).cuda())
+    xd = torch.from_numpy(x).cuda()
+    tokens, sums = torch.from_numpy(case["tokens"]).cuda(), torch.from_numpy(case["sum_logprobs"]).cuda()
+    ctx = _lib.context(0)
+    res = {}
+    for mode in (1, 0):
+        ctx.set_option("proj_cluster", mode)
+        try:
+            step.reset()
+            logits = proj.logits(xd)
+            out = to_np(proj.beam_step(xd, tokens, case["sample_begin"], sums, debug=True))
+            torch.cuda.synchronize()
+            ctx.check()
+            res[mode] = (logits.cpu().numpy(), out)
+        finally:
+            ctx.set_option("proj_cluster", 1)
+    assert np.array_equal(res[1][0], res[0][0])
+    for key in ("row_flags", "cand_token", "cand_logprob", "next_tokens", "source_idx", "sum_logprobs", "fin_count"):
+        assert np.array_equal(res[1][1][key], res[0][1][key]), key
+
+
 @pytest.mark.parametrize("step_kind", ["first", "mixed"])
 def test_fused_step_against_the_oracle_on_f32_logits(step_kind):
     ids = C.MULTILINGUAL

@@ -191,6 +191,7 @@ int wrs_ctx_set_option(wrs_ctx* ctx, const char* key, int64_t value) {
     if (!strcmp(key, "logmel_fused")) { ctx->opt_logmel_fused = (int)value; return WRS_OK; }
     if (!strcmp(key, "kv_verify_group")) { ctx->opt_kv_verify_group = (int)value; return WRS_OK; }
     if (!strcmp(key, "host_chunk_segments")) { ctx->opt_host_chunk_segments = (int)value; return WRS_OK; }
+    if (!strcmp(key, "proj_cluster")) { ctx->opt_proj_cluster = (int)value; return WRS_OK; }
     return wrs::fail(ctx, WRS_ERR_INVALID, std::string("unknown option ") + key);
 }
 

@@ -1359,13 +1359,14 @@ int launch_proj(wrs_projection* pj, ProjParams q, const float* x, int64_t x_stri
     wrs_ctx* ctx = dec->ctx;
     const size_t smem = sizeof(ProjSmem) + sizeof(uint32_t) * (dec->bm_words + 2);
     if (!pj->attr_set) {
-        WRS_CUDA(ctx, cudaFuncSetAttribute(proj_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        WRS_CUDA(ctx, cudaFuncSetAttribute(proj_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        WRS_CUDA(ctx, cudaFuncSetAttribute(proj_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        WRS_CUDA(ctx, cudaFuncSetAttribute(proj_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        WRS_CUDA(ctx, cudaFuncSetAttribute(proj_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        WRS_CUDA(ctx, cudaFuncSetAttribute(proj_kernel<12>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        WRS_CUDA(ctx, cudaFuncSetAttribute(proj_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        auto set = [&](auto kern) { return cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); };
+        WRS_CUDA(ctx, set(proj_kernel<0, false>)); WRS_CUDA(ctx, set(proj_kernel<0, true>));
+        WRS_CUDA(ctx, set(proj_kernel<2, false>)); WRS_CUDA(ctx, set(proj_kernel<2, true>));
+        WRS_CUDA(ctx, set(proj_kernel<4, false>)); WRS_CUDA(ctx, set(proj_kernel<4, true>));
+        WRS_CUDA(ctx, set(proj_kernel<6, false>)); WRS_CUDA(ctx, set(proj_kernel<6, true>));
+        WRS_CUDA(ctx, set(proj_kernel<8, false>)); WRS_CUDA(ctx, set(proj_kernel<8, true>));
+        WRS_CUDA(ctx, set(proj_kernel<12, false>)); WRS_CUDA(ctx, set(proj_kernel<12, true>));
+        WRS_CUDA(ctx, set(proj_kernel<16, false>)); WRS_CUDA(ctx, set(proj_kernel<16, true>));
         pj->attr_set = true;
     }
     q.wp = pj->d_wp; q.xp = pj->d_xp;
@@ -1377,8 +1378,21 @@ int launch_proj(wrs_projection* pj, ProjParams q, const float* x, int64_t x_stri
     WRS_CUDA(ctx, cudaGetLastError());
     // (programmatic dependent launch behind the packing kernel -- set-up under the packing -- was measured: 63.0 against
     // 63.5 us per step, within the noise; not kept)
-    proj_kernel<EPI><<<std::min(ctx->sm_count, pj->n_tiles), kPThreads, smem, stream>>>(q);
-    WRS_CUDA(ctx, cudaGetLastError());
+    // Exactly two M tiles (129 .. 256 rows): clusters of two CTAs that share the weights (proj_kernel<.., true>).
+    const int pairs = ctx->sm_count / 2;
+    if (q.n_mtiles == 2 && pairs >= 1 && ctx->opt_proj_cluster != 0) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned)(2 * std::min(pairs, pj->n_tiles))); cfg.blockDim = dim3(kPThreads);
+        cfg.dynamicSmemBytes = smem; cfg.stream = stream;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = 2; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        WRS_CUDA(ctx, cudaLaunchKernelEx(&cfg, proj_kernel<EPI, true>, q));
+    } else {
+        proj_kernel<EPI, false><<<std::min(ctx->sm_count, pj->n_tiles), kPThreads, smem, stream>>>(q);
+        WRS_CUDA(ctx, cudaGetLastError());
+    }
     return WRS_OK;
 }
 

@@ -171,6 +171,21 @@ __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::
 __device__ __forceinline__ void tc_commit(unsigned long long* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_addr(bar)) : "memory");
 }
+// two-CTA clusters: rank, barrier across the pair, a bulk copy and a tcgen05.commit that reach both CTAs (the shared-memory
+// offsets of destination and mbarrier are the issuing CTA's; the same offsets are used in every CTA of the mask)
+__device__ __forceinline__ unsigned cluster_rank() { unsigned r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_g2s_mc(void* dst, const void* src, unsigned bytes, unsigned long long* bar, unsigned short mask) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], %2, [%3], %4;" ::"r"(smem_addr(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_addr(bar)), "h"(mask)
+                 : "memory");
+}
+__device__ __forceinline__ void tc_commit_mc(unsigned long long* bar, unsigned short mask) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(smem_addr(bar)), "h"(mask) : "memory");
+}
+
 // shared-memory operand descriptor, K-major, no swizzle: start address, LBO = bytes between the two 16-byte K chunks of
 // an MMA, SBO = bytes between 8-row groups; bit 46 = descriptor version 1 (Blackwell)
 __device__ __forceinline__ unsigned long long tc_desc(unsigned saddr, unsigned lbo, unsigned sbo) {
@@ -382,14 +397,20 @@ struct ProjSmem {
 };
 
 // EPI 0: store the logits; EPI 2, 4, 6, 8, 12, 16: fold, with room for K <= EPI candidates per (row, tile)
-template <int EPI>
+// CL: launched as clusters of two CTAs, for batches of exactly two M tiles (129 .. 256 rows): CTA r of a pair takes M tile r
+// of the pair's vocab tiles (four each for V = 51865), and the pair shares the weights -- each CTA fetches one half of a
+// stage's weights (rank 0 the hi parts, rank 1 the lo parts) and multicasts it into both CTAs' stage, so a weight leaves
+// L2 once per pair instead of once per M tile.  A stage is free when BOTH CTAs' MMAs have read it (their commits reach
+// both CTAs' barriers).  What an SM takes IN per stage is unchanged, and that, with the MMAs, is what paces the main loop:
+// the gain is the L2 traffic and that a CTA meets the same rows in all its tiles (floors carry over three times).
+template <int EPI, bool CL>
 __global__ void __launch_bounds__(kPThreads, 1) proj_kernel(const ProjParams p) {
     constexpr int KM = EPI == 0 ? 1 : EPI;
     extern __shared__ __align__(1024) unsigned char proj_smem_raw[];
     ProjSmem& sm = *reinterpret_cast<ProjSmem*>(proj_smem_raw);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     if (threadIdx.x == 0) {
-        for (int s = 0; s < kPStages; ++s) { mbar_init(&sm.full[s], 1); mbar_init(&sm.empty[s], 1); }
+        for (int s = 0; s < kPStages; ++s) { mbar_init(&sm.full[s], 1); mbar_init(&sm.empty[s], CL ? 2 : 1); }
         for (int b = 0; b < 2; ++b) { mbar_init(&sm.tfull[b], 1); mbar_init(&sm.tempty[b], 8); }
     }
     if (EPI != 0)
@@ -401,17 +422,22 @@ __global__ void __launch_bounds__(kPThreads, 1) proj_kernel(const ProjParams p) 
     }
     tc_fence_before();
     __syncthreads();
+    if (CL) cluster_sync_all();                          // the peer's barriers exist before anything of ours reaches them
     tc_fence_after();
     const unsigned tmem = sm.tmem_base;
-    const int my_tiles = ((int)blockIdx.x < p.n_tiles) ? (p.n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
-    const int n_units = my_tiles * p.n_mtiles;           // accumulations of this CTA: unit u = (tile u / n_mtiles, M tile u % n_mtiles)
+    // the vocab tiles of this CTA (of this pair): first, first + stride, ...
+    const int crank = CL ? (int)cluster_rank() : 0;
+    const int first = CL ? (int)blockIdx.x >> 1 : (int)blockIdx.x, stride = CL ? (int)gridDim.x >> 1 : (int)gridDim.x;
+    const int my_tiles = (first < p.n_tiles) ? (p.n_tiles - 1 - first) / stride + 1 : 0;
+    const int mt_per_tile = CL ? 1 : p.n_mtiles;         // M tiles this CTA takes of each of its vocab tiles
+    const int n_units = my_tiles * mt_per_tile;          // accumulations of this CTA: unit u = (tile u / mt_per_tile, M tile)
 
     if (warp == kPEpiWarps) {
         // ================================================= producer
         if (lane == 0) {
             unsigned it = 0;
             for (int u = 0; u < n_units; ++u) {
-                const int tile = (int)blockIdx.x + (u / p.n_mtiles) * (int)gridDim.x, mt = u % p.n_mtiles;
+                const int tile = first + (u / mt_per_tile) * stride, mt = CL ? crank : u % p.n_mtiles;
                 const unsigned char* a = p.xp + (int64_t)mt * p.n_kstages * (2 * kPABytes);
                 const unsigned char* b = p.wp + (int64_t)tile * p.n_kstages * (2 * kPBBytes);
                 const unsigned a_bytes = (unsigned)proj_rows8(p.n_rows, mt) * (kPK * 2 * 2);      // hi and lo of the tile's rows
@@ -420,7 +446,8 @@ __global__ void __launch_bounds__(kPThreads, 1) proj_kernel(const ProjParams p) 
                     mbar_wait_b<0>(&sm.empty[slot], (round & 1u) ^ 1u);      // (a fresh barrier passes the first round)
                     mbar_expect_tx(&sm.full[slot], a_bytes + 2u * kPBBytes);
                     bulk_g2s(sm.stage[slot], a + (int64_t)ks * (2 * kPABytes), a_bytes, &sm.full[slot]);
-                    bulk_g2s(sm.stage[slot] + 2 * kPABytes, b + (int64_t)ks * (2 * kPBBytes), 2 * kPBBytes, &sm.full[slot]);
+                    if (CL) bulk_g2s_mc(sm.stage[slot] + 2 * kPABytes + crank * kPBBytes, b + (int64_t)ks * (2 * kPBBytes) + crank * kPBBytes, kPBBytes, &sm.full[slot], 3);
+                    else bulk_g2s(sm.stage[slot] + 2 * kPABytes, b + (int64_t)ks * (2 * kPBBytes), 2 * kPBBytes, &sm.full[slot]);
                 }
             }
         }
@@ -434,7 +461,7 @@ __global__ void __launch_bounds__(kPThreads, 1) proj_kernel(const ProjParams p) 
                 tc_fence_after();
                 WRS_PJ_T(u, 0);
                 const unsigned d = tmem + buf * kPAccStride;
-                const unsigned a_rows = (unsigned)proj_rows8(p.n_rows, u % p.n_mtiles);
+                const unsigned a_rows = (unsigned)proj_rows8(p.n_rows, CL ? crank : u % p.n_mtiles);
                 for (int ks = 0; ks < p.n_kstages; ++ks, ++it) {
                     const unsigned slot = it % kPStages, round = it / kPStages;
                     mbar_wait_b<0>(&sm.full[slot], round & 1u);
@@ -457,7 +484,8 @@ __global__ void __launch_bounds__(kPThreads, 1) proj_kernel(const ProjParams p) 
                         tc_mma(d, dah, dbh, 1u);
 #endif
                     }
-                    tc_commit(&sm.empty[slot]);                         // the stage is free once these MMAs have read it
+                    if (CL) tc_commit_mc(&sm.empty[slot], 3);           // (both CTAs' producers wait for both CTAs' MMAs)
+                    else tc_commit(&sm.empty[slot]);                    // the stage is free once these MMAs have read it
                 }
                 tc_commit(&sm.tfull[buf]);                              // the accumulator is complete
                 WRS_PJ_T(u, 1);
@@ -478,7 +506,7 @@ __global__ void __launch_bounds__(kPThreads, 1) proj_kernel(const ProjParams p) 
         int prev_row = -1, prev_part = -1;
         float tau_run = -CUDART_INF_F;
         for (int u = ew >> 2; u < n_units; u += 2) {
-            const int tile = (int)blockIdx.x + (u / p.n_mtiles) * (int)gridDim.x, mt = u % p.n_mtiles;
+            const int tile = first + (u / mt_per_tile) * stride, mt = CL ? crank : u % p.n_mtiles;
             const unsigned buf = (unsigned)u & 1u, use = (unsigned)u >> 1;
             const int row = mt * kPM + (int)(threadIdx.x & 127);
             const int base = proj_tile_base(tile, p.n_text_tiles, p.ts_split);
@@ -598,6 +626,7 @@ __global__ void __launch_bounds__(kPThreads, 1) proj_kernel(const ProjParams p) 
     // ---- teardown: every tcgen05 operation of this CTA has completed (the epilogue waited for the last commit)
     tc_fence_before();
     __syncthreads();
+    if (CL) cluster_sync_all();                          // nothing of the peer's is still on its way into this CTA
     if (warp == kPEpiWarps + 1) {
         tc_fence_after();
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(kPTmemCols) : "memory");

@@ -49,6 +49,7 @@ struct wrs_ctx {
     wrs::DevStatus* d_status = nullptr;
     int opt_logmel_fused = -1;             // -1 auto, 0 two-pass, 1 fused
     int opt_host_chunk_segments = 0;       // > 0: segments per chunk of the *_host pipelines
+    int opt_proj_cluster = 1;              // 0: never launch the projection as two-CTA clusters (A/B timing, debugging)
     int opt_kv_verify_group = 0;           // > 0: beam size to verify group-invariant KV tensors against (debug)
     int64_t stat_last_logmel_mode = -1;
     int64_t stat_last_logmel_grid = 0;
