@@ -11,7 +11,7 @@ CSRC = os.path.join(HERE, "csrc")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libwrs_b200.so")
 SOURCES = ["ctx.cu", "logmel.cu", "decode.cu", "decode_host.cu", "kv_reorder.cu", "no_speech.cu"]
-HEADERS = ["logmel_fft.cuh", "decode_scan.cuh", "decode_proj.cuh", "async_copy.cuh", "wrs_internal.cuh", os.path.join("..", "..", "include", "wrs.h")]
+HEADERS = ["logmel_fft.cuh", "decode_scan.cuh", "decode_proj.cuh", "decode_proj_select.cuh", "async_copy.cuh", "wrs_internal.cuh", os.path.join("..", "..", "include", "wrs.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC",
               "--use_fast_math=false", "-Xptxas", "-v"]
 
