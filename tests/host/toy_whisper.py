@@ -139,11 +139,14 @@ class _Decoder:
         self.d, self.scale = d, logit_scale / math.sqrt(d)
         self.eot, self.eot_bias, self.eot_after = eot, eot_bias, eot_after
 
-    def forward_ext(self, tokens, xa, offset):                      # src/model.rs:488-521
+    def forward_hidden(self, tokens, xa, offset):                   # src/model.rs:488-519: everything before the projection
         x = self.token_emb[tokens] + self.pos[offset:offset + tokens.shape[-1]]
         for b in self.blocks:
             x = b(x, xa, self.mask, use_cache=True)
-        x = F.layer_norm(x, (self.d,))
+        return F.layer_norm(x, (self.d,))
+
+    def forward_ext(self, tokens, xa, offset):                      # src/model.rs:488-521
+        x = self.forward_hidden(tokens, xa, offset)
         logits = (x @ self.token_emb.T) * self.scale
         if self.eot_bias and offset >= self.eot_after:
             logits[:, :, self.eot] += self.eot_bias

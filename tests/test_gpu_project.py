@@ -223,3 +223,52 @@ def test_bad_arguments_raise():
         Projection(step.decoder, torch.zeros(ids.n_vocab, 500, device="cuda"))      # n_state not a multiple of 32
     with pytest.raises(ValueError):
         Projection(step.decoder, torch.zeros(ids.n_vocab - 1, 512, device="cuda"))
+
+
+def test_decode_loop_through_the_projection_equals_the_loop_through_its_logits():
+    """Ten steps of the reference's loop (src/decode/mod.rs:236-276) on a toy decoder, the KV caches reordered by every
+    step's source rows: once with wrs_project_beam_step on the hidden state, once with wrs_beam_step on the logits
+    wrs_project_logits materialises from the same hidden state.  Same tokens, sums and finished sequences, step by step."""
+    import sys, os
+    sys.path.insert(0, os.path.join(os.path.dirname(__file__), "host"))
+    import toy_whisper as tw
+    ids = C.MULTILINGUAL
+    n_audio, beam, n_steps = 3, 5, 10
+    mel = torch.randn(n_audio, 80, 3000, generator=torch.Generator().manual_seed(4)).cuda()
+
+    def loop(fused):
+        model = tw.ToyWhisper(tw.ModelDims(), "cuda", 5, "wrs", eot=ids.eot, eot_bias=0.0)
+        opt = wd.DecodeOptions(token_extract_mode=wd.TokenExtractMode.BeamSearch(beam, 1.0), sample_len=n_steps)
+        prompt = wd.DecodePrompt(None, ids)
+        step = wd.FusedDecodeStep(opt, ids, [prompt], max_rows=n_audio * beam)
+        step.reset()
+        proj = Projection(step.decoder, model.decoder.token_emb)
+        with torch.no_grad():
+            feats = model.encoder(mel).repeat_interleave(beam, 0)
+            tokens = torch.tensor(prompt.initial_tokens, dtype=torch.int64, device="cuda").repeat(n_audio * beam, 1)
+            sums = torch.zeros(n_audio * beam, dtype=torch.float32, device="cuda")
+            trace = []
+            for i in range(n_steps):
+                t_in = tokens[:, -1:] if tokens.shape[-1] > prompt.sample_begin else tokens
+                h = (model.decoder.forward_hidden(t_in, feats, i)[:, -1] * model.decoder.scale).contiguous()
+                if fused:
+                    out = proj.beam_step(h, tokens, prompt.sample_begin, sums)
+                else:
+                    out = step.decoder.beam_step(proj.logits(h), tokens, prompt.sample_begin, sums)
+                tokens, sums = out["next_tokens"], out["sum_logprobs"]
+                model.update_cache(out["source_idx"])
+                torch.cuda.synchronize()
+                step.decoder.ctx.check()
+                trace.append((tokens.cpu().numpy().copy(), sums.cpu().numpy().copy(), out["source_idx"].cpu().numpy().copy(),
+                              int(out["completed"].item())))
+            cands, scores = step.decoder.finalize(tokens, sums)
+        assert model.reorders == n_steps
+        return trace, cands, scores
+
+    a, ca, sa = loop(True)
+    b, cb, sb = loop(False)
+    for i, (x, y) in enumerate(zip(a, b)):
+        assert np.array_equal(x[0], y[0]) and np.array_equal(x[2], y[2]) and x[3] == y[3], i
+        assert np.allclose(x[1], y[1], rtol=RTOL, atol=1e-5), i
+    assert ca == cb and np.allclose(sa, sb, rtol=RTOL, atol=1e-5)
+    assert len({tuple(r) for r in a[-1][0].tolist()}) > n_audio         # beams diverged: the source rows were not trivial
