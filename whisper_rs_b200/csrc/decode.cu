@@ -577,17 +577,20 @@ __device__ __forceinline__ RowOut merge_row_proj(const StepParams& p, int row, W
         mbar_wait(bar, 0u);
         pm = sm; ps = sm + TP; pv0 = sm + 2 * TP;
     }
-    // ---- pass A: partition maxima and sums, folded lane-locally first
-    float am0 = -CUDART_INF_F, am1 = -CUDART_INF_F, as0 = 0.0f, as1 = 0.0f;
+    // ---- pass A: partition maxima and sums, folded lane-locally first (ten tiles per lane: exp2 on the fast path, as
+    // in the scan -- the tiles' own sums were formed the same way)
+    float am0 = -CUDART_INF_F, am1 = -CUDART_INF_F, as0 = 0.0f, as1 = 0.0f, head0 = -CUDART_INF_F, head1 = -CUDART_INF_F;
     bool nan_seen = false;
+    auto ediff = [](float a, float b) { return a == -CUDART_INF_F ? 0.0f : ex2((a - b) * kLog2e); };   // exp(a - b), exp(-inf - -inf) = 0
 #pragma unroll 1
     for (int t = lane; t < T; t += 32) {
-        const float hm = pm[t], hs = ps[t];
+        const float hm = pm[t], hs = ps[t], hv = pv0[t];
+        if (t < p.proj_text_tiles) head0 = fmaxf(head0, hv); else head1 = fmaxf(head1, hv);   // (the tiles' best values, for pass B)
         if (hs != hs) { nan_seen = true; continue; }
         if (t < p.proj_text_tiles) {
-            if (hm > am0) { as0 = as0 * exp_diff(am0, hm) + hs; am0 = hm; } else as0 += hs * exp_diff(hm, am0);
+            if (hm > am0) { as0 = as0 * ediff(am0, hm) + hs; am0 = hm; } else as0 += hs * ediff(hm, am0);
         } else {
-            if (hm > am1) { as1 = as1 * exp_diff(am1, hm) + hs; am1 = hm; } else as1 += hs * exp_diff(hm, am1);
+            if (hm > am1) { as1 = as1 * ediff(am1, hm) + hs; am1 = hm; } else as1 += hs * ediff(hm, am1);
         }
     }
     float M[2], S[2];
@@ -616,10 +619,7 @@ __device__ __forceinline__ RowOut merge_row_proj(const StepParams& p, int row, W
 #endif
     // ---- pass B: a value at least K candidates reach (K rounds over the lanes' best heads), then everything at or above it
     const int t_first = ts_over_text ? p.proj_text_tiles : 0;
-    float head = -CUDART_INF_F;
-#pragma unroll 1
-    for (int t = lane; t < T; t += 32)
-        if (t >= t_first) head = fmaxf(head, pv0[t]);
+    const float head = ts_over_text ? head1 : fmaxf(head0, head1);
     const float tau = kth_threshold(head, K);
     const float* gv = planes + 2 * TP;                                   // value planes and id planes in global memory
     const int* gi = reinterpret_cast<const int*>(planes + (2 + K) * TP);
@@ -629,10 +629,13 @@ __device__ __forceinline__ RowOut merge_row_proj(const StepParams& p, int row, W
         float v = pv0[t];
 #pragma unroll 1
         for (int e = 0; e < K; ++e) {                                    // (lists are sorted: stop at the first entry below tau)
-            if (e > 0) v = __ldcg(gv + (int64_t)e * TP + t);
             if (!(v >= tau) || v == -CUDART_INF_F) break;
+            // the entry's id and the list's next value travel together
+            const int id = __ldcg(gi + (int64_t)e * TP + t);
+            const float vn = e + 1 < K ? __ldcg(gv + (int64_t)(e + 1) * TP + t) : -CUDART_INF_F;
             const int slot = atomicAdd(&wb.n, 1);
-            if (slot < kCandCap) { wb.v[slot] = v; wb.id[slot] = __ldcg(gi + (int64_t)e * TP + t); }
+            if (slot < kCandCap) { wb.v[slot] = v; wb.id[slot] = id; }
+            v = vn;
         }
     }
     __syncwarp();
