@@ -229,6 +229,12 @@ int wrs_project_beam_step(wrs_projection* proj, const float* x, int64_t x_stride
                           int64_t* next_tokens, int64_t next_stride, int32_t* source_idx, float* sum_logprobs_out,
                           int32_t* completed, const wrs_step_debug* dbg, wrs_stream_t stream);
 
+/* src/model.rs:521 + wrs_greedy_step in one pass (TokenExtractMode::Greedy, src/decode/extractor/greedy.rs:14-51). */
+int wrs_project_greedy_step(wrs_projection* proj, const float* x, int64_t x_stride, int64_t n_rows, const int64_t* tokens,
+                            int64_t tok_stride, int64_t cur_len, int64_t sample_begin, const float* sum_logprobs_in,
+                            int64_t* next_tokens, int64_t next_stride, float* sum_logprobs_out, int32_t* completed,
+                            const wrs_step_debug* dbg, wrs_stream_t stream);
+
 /* BeamSearchTokenExtractor::finalize  src/decode/extractor/beam_search.rs:151-206.  Synchronises `stream`,
  * copies the finished store and the live beams to the host and returns, per audio, exactly
  * max(beam, stored) candidates ordered (score desc, sequence lexicographic):

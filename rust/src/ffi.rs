@@ -48,6 +48,10 @@ extern "C" {
                                  tok_stride: i64, cur_len: i64, sample_begin: i64, sum_in: *const f32,
                                  next_tokens: *mut i64, next_stride: i64, source_idx: *mut i32, sum_out: *mut f32,
                                  completed: *mut i32, dbg: *const c_void, stream: *mut c_void) -> c_int;
+    pub fn wrs_project_greedy_step(proj: *mut WrsProjection, x: *const f32, x_stride: i64, n_rows: i64, tokens: *const i64,
+                                   tok_stride: i64, cur_len: i64, sample_begin: i64, sum_in: *const f32,
+                                   next_tokens: *mut i64, next_stride: i64, sum_out: *mut f32, completed: *mut i32,
+                                   dbg: *const c_void, stream: *mut c_void) -> c_int;
     pub fn wrs_beam_finalize(dec: *mut WrsDecoder, tokens: *const i64, tok_stride: i64, cur_len: i64, n_rows: i64,
                              sum_logprobs: *const f32, n_cand_cap: i32, out_tokens: *mut i64, out_len: *mut i32,
                              out_scores: *mut f64, out_n_cand: *mut i32, stream: *mut c_void) -> c_int;

@@ -176,6 +176,32 @@ def test_cluster_launch_is_bit_identical_to_the_single_cta_launch(R_audio, beam)
         assert np.array_equal(res[1][1][key], res[0][1][key]), key
 
 
+@pytest.mark.parametrize("step_kind,R,dup", [("first", 7, 0), ("mixed", 160, 0), ("mixed", 37, 2000), ("second", 300, 0)])
+def test_fused_greedy_step_equals_greedy_step_on_projected_logits(step_kind, R, dup):
+    """TokenExtractMode::Greedy (src/decode/extractor/greedy.rs:14-51): argmax with the lowest id on ties, log-softmax
+    gather, EOT propagation -- through the projection, against wrs_greedy_step on the logits it materialises."""
+    ids = C.MULTILINGUAL
+    case = synth.decode_case(ids, R, 1, step_kind, seed=19)
+    x, w = make_model(ids, 512, R, seed=R, dup=dup)
+    opt = wd.DecodeOptions(token_extract_mode=wd.TokenExtractMode.Greedy(1))
+    prompt = wd.DecodePrompt(None, ids)
+    prompt.sample_begin = case["sample_begin"]
+    step = wd.FusedDecodeStep(opt, ids, [prompt], max_rows=R)
+    step.reset()
+    proj = Projection(step.decoder, torch.from_numpy(w).cuda())
+    xd = torch.from_numpy(x).cuda()
+    tokens, sums = torch.from_numpy(case["tokens"]).cuda(), torch.from_numpy(case["sum_logprobs"]).cuda()
+    want = to_np(step.decoder.greedy_step(proj.logits(xd), tokens, case["sample_begin"], sums, debug=True))
+    got = to_np(proj.greedy_step(xd, tokens, case["sample_begin"], sums, debug=True))
+    torch.cuda.synchronize()
+    step.decoder.ctx.check()
+    for key in ("row_flags", "cand_token", "next_tokens"):
+        assert np.array_equal(got[key], want[key]), key
+    assert np.allclose(got["cand_logprob"], want["cand_logprob"], rtol=RTOL, atol=1e-5)
+    assert np.allclose(got["sum_logprobs"], want["sum_logprobs"], rtol=RTOL, atol=1e-5)
+    assert int(got["completed"][0]) == int(want["completed"][0])
+
+
 @pytest.mark.parametrize("step_kind", ["first", "mixed"])
 def test_fused_step_against_the_oracle_on_f32_logits(step_kind):
     ids = C.MULTILINGUAL

@@ -68,6 +68,8 @@ SIGNATURES = {
     "wrs_project_logits": (C.c_int, [_P, _P, _I64, _I64, _P, _I64, _P]),
     "wrs_project_beam_step": (C.c_int, [_P, _P, _I64, _I64, _P, _I64, _I64, _I64, _P, _P, _I64, _P, _P, _P,
                                         C.POINTER(StepDebug), _P]),
+    "wrs_project_greedy_step": (C.c_int, [_P, _P, _I64, _I64, _P, _I64, _I64, _I64, _P, _P, _I64, _P, _P,
+                                          C.POINTER(StepDebug), _P]),
     "wrs_beam_finalize": (C.c_int, [_P, _P, _I64, _I64, _I64, _P, _I32, _P, _P, _P, _P, _P]),
     "wrs_rank_max_likelihood_host": (C.c_int, [_P, _P, _I32, _I32, _I32, _D, _P]),
     "wrs_kv_reorder": (C.c_int, [_P, C.POINTER(KvTensor), _I32, _I64, _P, _P]),

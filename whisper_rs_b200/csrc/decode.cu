@@ -1763,6 +1763,38 @@ int wrs_project_beam_step(wrs_projection* pj, const float* x, int64_t x_stride, 
     return WRS_OK;
 }
 
+int wrs_project_greedy_step(wrs_projection* pj, const float* x, int64_t x_stride, int64_t n_rows, const int64_t* tokens,
+                            int64_t tok_stride, int64_t cur_len, int64_t sample_begin, const float* sum_in, int64_t* next_tokens,
+                            int64_t next_stride, float* sum_out, int32_t* completed, const wrs_step_debug* dbg, wrs_stream_t stream_) {
+    int rc = proj_check(pj, "wrs_project_greedy_step", x, x_stride, n_rows);
+    if (rc != WRS_OK) return rc;
+    wrs_decoder* dec = pj->dec;
+    rc = check_step_args(dec, "wrs_project_greedy_step", x, dec->cfg.n_vocab, n_rows, tokens, tok_stride, cur_len, sample_begin);
+    if (rc != WRS_OK) return rc;
+    wrs_ctx* ctx = dec->ctx;
+    if (!sum_in || !next_tokens || !sum_out || !completed) return fail(ctx, WRS_ERR_INVALID, "wrs_project_greedy_step: null output");
+    if (next_stride < cur_len + 1) return fail(ctx, WRS_ERR_INVALID, "wrs_project_greedy_step: next_stride < cur_len + 1");
+    if ((const void*)next_tokens == (const void*)tokens) return fail(ctx, WRS_ERR_INVALID, "wrs_project_greedy_step: next_tokens must not alias tokens");
+    cudaStream_t stream = (cudaStream_t)stream_;
+    WRS_CUDA(ctx, cudaSetDevice(ctx->device));
+    StepParams p = step_params(dec, nullptr, dec->cfg.n_vocab, n_rows, tokens, tok_stride, cur_len, sample_begin, 1, 1,
+                               dec->d_bm_base, dec->d_bm_first);
+    p.sum_in = sum_in; p.sum_out = sum_out; p.next_tokens = next_tokens; p.next_stride = next_stride; p.completed = completed;
+    set_debug(p, dbg);
+    p.proj_parts = pj->d_parts; p.proj_tiles = pj->n_tiles; p.proj_text_tiles = pj->n_text_tiles; p.proj_tp = (pj->n_tiles + 3) & ~3;
+    ProjParams q;
+    memset(&q, 0, sizeof(q));
+    q.n_rows = (int)n_rows; q.tokens = tokens; q.tok_stride = tok_stride; q.cur_len = p.cur_len; q.sample_begin = p.sample_begin;
+    q.K = 1; q.rc = p.rc; q.bm = p.bm; q.bm_words = p.bm_words; q.parts = pj->d_parts; q.tiles_padded = p.proj_tp;
+    rc = ensure_tail_attrs(dec);
+    if (rc != WRS_OK) return rc;
+    rc = launch_proj<2>(pj, q, x, x_stride, stream);
+    if (rc != WRS_OK) return rc;
+    decode_tail_kernel<MODE_GREEDY><<<p.n_rows, 32, (size_t)kTailHead + (size_t)kTailBytes, stream>>>(p);
+    WRS_CUDA(ctx, cudaGetLastError());
+    return WRS_OK;
+}
+
 }  // extern "C"
 
 namespace wrs {

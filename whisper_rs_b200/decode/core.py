@@ -303,3 +303,26 @@ class Projection:
         if bufs:
             out.update(bufs)
         return out
+
+    def greedy_step(self, x, tokens, sample_begin, sum_logprobs, next_tokens=None, sum_out=None, debug=False):
+        """src/model.rs:521 + Decoder.greedy_step in one pass (the decoder must have been built for a greedy mode: K = 1)."""
+        self._check_x(x)
+        d = self.dec
+        R, L = tokens.shape
+        if x.shape[0] != R:
+            raise ValueError("x and tokens disagree on the number of rows")
+        if next_tokens is None:
+            next_tokens = torch.empty(R, L + 1, dtype=torch.int64, device=d.device)
+        if sum_out is None:
+            sum_out = torch.empty(R, dtype=torch.float32, device=d.device)
+        completed = torch.zeros(1, dtype=torch.int32, device=d.device)
+        dbg, bufs = d._debug(R, debug)
+        _lib.check(_lib.lib().wrs_project_greedy_step(self.handle, x.data_ptr(), x.stride(0), R, tokens.data_ptr(),
+                                                      tokens.stride(0), L, sample_begin, sum_logprobs.data_ptr(),
+                                                      next_tokens.data_ptr(), next_tokens.stride(0), sum_out.data_ptr(),
+                                                      completed.data_ptr(), C.byref(dbg) if dbg is not None else None,
+                                                      d._stream()), d.ctx.handle)
+        out = dict(next_tokens=next_tokens, sum_logprobs=sum_out, completed=completed)
+        if bufs:
+            out.update(bufs)
+        return out
